@@ -1,0 +1,94 @@
+"""ctypes binding of the C ABI declared in include/gpflow_b200.h (the drop-in boundary).
+
+The shared library is built in-tree (gpflow_b200/lib/libgpflow_b200.so) by `gpflow_b200.build.build()` /
+`__graft_entry__.build()`; it links only against the CUDA runtime -- no torch symbols.
+"""
+import ctypes
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "lib", "libgpflow_b200.so")
+
+GPFLOW_ABI_VERSION = 1
+GPFLOW_MAX_HIDDEN = 8
+F32, F64 = 0, 1
+OP_FORWARD, OP_TRAIN_STEP, OP_BACKWARD = 0, 1, 2
+FLAG_WRAP_GAUSS, FLAG_LAGRANGIAN, FLAG_EULER_PEN, FLAG_REVERSE, FLAG_FORCE_GENERIC = 0x1, 0x2, 0x4, 0x8, 0x10
+SCALAR_OT, SCALAR_REG, SCALAR_LAGR, NUM_SCALARS = 0, 1, 2, 3
+
+EXPORTS = [
+    "gpflow_param_count", "gpflow_query_workspace", "gpflow_forward", "gpflow_train_step", "gpflow_backward",
+    "gpflow_velocity", "gpflow_kernel_variant", "gpflow_launch_count", "gpflow_fp32_fma_burn", "gpflow_error_string",
+    "gpflow_abi_version",
+]
+
+
+class GpFlowDesc(ctypes.Structure):
+    _fields_ = [
+        ("abi_version", ctypes.c_int32),
+        ("dtype", ctypes.c_int32),
+        ("d", ctypes.c_int32),
+        ("nb", ctypes.c_int32),
+        ("n_hidden", ctypes.c_int32),
+        ("hidden", ctypes.c_int32 * GPFLOW_MAX_HIDDEN),
+        ("n_steps", ctypes.c_int32),
+        ("n_steps_nominal", ctypes.c_int32),
+        ("flags", ctypes.c_uint32),
+        ("reserved0", ctypes.c_int32),
+        ("dt", ctypes.c_double),
+        ("dt_constraint", ctypes.c_double),
+        ("sigma", ctypes.c_double),
+        ("euler_coef", ctypes.c_double),
+        ("loss_scale", ctypes.c_double),
+    ]
+
+
+_lib = None
+
+
+class GpFlowLibraryError(RuntimeError):
+    pass
+
+
+def load():
+    """Load the CUDA library; fail loudly if it has not been built (there is no fallback path)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise GpFlowLibraryError(
+            "gpflow_b200 CUDA library not built: %s is missing. Build it with "
+            "`python -c 'import __graft_entry__ as g; g.build()'` (needs nvcc). There is no CPU fallback." % LIB_PATH)
+    lib = ctypes.CDLL(LIB_PATH)
+    P, D = ctypes.c_void_p, ctypes.POINTER(GpFlowDesc)
+    lib.gpflow_param_count.restype = ctypes.c_int64
+    lib.gpflow_param_count.argtypes = [D]
+    lib.gpflow_query_workspace.restype = ctypes.c_int
+    lib.gpflow_query_workspace.argtypes = [D, ctypes.c_int64, ctypes.c_int, ctypes.POINTER(ctypes.c_size_t)]
+    lib.gpflow_forward.restype = ctypes.c_int
+    lib.gpflow_forward.argtypes = [D, ctypes.c_int64, P, P, P, P, P, P, P, P, ctypes.c_size_t, P]
+    lib.gpflow_train_step.restype = ctypes.c_int
+    lib.gpflow_train_step.argtypes = [D, ctypes.c_int64, P, P, P, P, P, P, P, P, P, ctypes.c_size_t, P]
+    lib.gpflow_backward.restype = ctypes.c_int
+    lib.gpflow_backward.argtypes = [D, ctypes.c_int64, P, P, P, P, P, P, P, P, ctypes.c_size_t, P]
+    lib.gpflow_velocity.restype = ctypes.c_int
+    lib.gpflow_velocity.argtypes = [D, ctypes.c_int64, P, P, ctypes.c_double, P, P, ctypes.c_size_t, P]
+    lib.gpflow_kernel_variant.restype = ctypes.c_int
+    lib.gpflow_kernel_variant.argtypes = [D, ctypes.c_int, ctypes.c_char_p, ctypes.c_size_t]
+    lib.gpflow_launch_count.restype = ctypes.c_int
+    lib.gpflow_launch_count.argtypes = [D, ctypes.c_int]
+    lib.gpflow_fp32_fma_burn.restype = ctypes.c_int
+    lib.gpflow_fp32_fma_burn.argtypes = [ctypes.c_int64, P, ctypes.POINTER(ctypes.c_double), P]
+    lib.gpflow_error_string.restype = ctypes.c_char_p
+    lib.gpflow_error_string.argtypes = [ctypes.c_int]
+    lib.gpflow_abi_version.restype = ctypes.c_int
+    lib.gpflow_abi_version.argtypes = []
+    if lib.gpflow_abi_version() != GPFLOW_ABI_VERSION:
+        raise GpFlowLibraryError("ABI version mismatch between %s and the Python binding" % LIB_PATH)
+    _lib = lib
+    return lib
+
+
+def check(rc):
+    if rc != 0:
+        raise RuntimeError("gpflow_b200: " + load().gpflow_error_string(rc).decode())

@@ -1,0 +1,260 @@
+// gpflow_b200 -- C ABI (include/gpflow_b200.h): descriptor validation, kernel dispatch, workspace carving.
+// No torch types, no allocation, no synchronisation: everything is enqueued on the caller's stream.
+#include "../../include/gpflow_b200.h"
+
+#include <cuda_runtime.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <mutex>
+
+#include "gpflow_dispatch.h"
+
+using namespace gpflow;
+
+namespace {
+
+struct DeviceInfo {
+  int sm_count = 148;
+  bool ok = false;
+};
+DeviceInfo device_info() {
+  static std::mutex mu;
+  static DeviceInfo cache[64];
+  static bool have[64] = {false};
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) {
+    cudaGetLastError();
+    return DeviceInfo();
+  }
+  std::lock_guard<std::mutex> lk(mu);
+  if (!have[dev]) {
+    DeviceInfo di;
+    int v = 0;
+    if (cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && v > 0) {
+      di.sm_count = v > kMaxSMs ? kMaxSMs : v;
+      di.ok = true;
+    }
+    cudaGetLastError();
+    cache[dev] = di;
+    have[dev] = true;
+  }
+  return cache[dev];
+}
+
+int validate(const GpFlowDesc* d) {
+  if (d == nullptr) return GPFLOW_ERR_NULL_POINTER;
+  if (d->abi_version != GPFLOW_ABI_VERSION) return GPFLOW_ERR_BAD_DESC;
+  if (d->dtype != GPFLOW_F32 && d->dtype != GPFLOW_F64) return GPFLOW_ERR_BAD_DESC;
+  if (d->d < 1 || d->nb < 1 || d->nb > d->d) return GPFLOW_ERR_BAD_DESC;
+  if (d->n_hidden < 1 || d->n_hidden > GPFLOW_MAX_HIDDEN) return GPFLOW_ERR_BAD_DESC;
+  for (int i = 0; i < d->n_hidden; ++i)
+    if (d->hidden[i] < 1) return GPFLOW_ERR_BAD_DESC;
+  if (d->n_steps < 1 || d->n_steps_nominal < 1) return GPFLOW_ERR_BAD_DESC;
+  if (!(d->dt > 0.0) || !(d->sigma > 0.0)) return GPFLOW_ERR_BAD_DESC;
+  if (d->d < 2) return GPFLOW_ERR_UNSUPPORTED;  // a 1-d divergence-free wall-tangent field is identically zero
+  return GPFLOW_OK;
+}
+
+// ---- the specialised small-d variants that are compiled in -------------------------------------
+struct SmallShape { int d, nb, h1, h2; };
+bool small_match(const GpFlowDesc* d, SmallShape* out) {
+  if (d->flags & GPFLOW_FLAG_FORCE_GENERIC) return false;
+  if (d->n_hidden != 2) return false;
+  static const SmallShape shapes[] = {{2, 1, 15, 15}};
+  for (const SmallShape& s : shapes)
+    if (d->d == s.d && d->nb == s.nb && d->hidden[0] == s.h1 && d->hidden[1] == s.h2) {
+      if (out) *out = s;
+      return true;
+    }
+  return false;
+}
+
+template <typename T>
+int dispatch(const GpFlowDesc* d, int op, const Ptrs<T>& p, int64_t B, void* ws, size_t wsb, cudaStream_t st);
+
+template <>
+int dispatch<float>(const GpFlowDesc* d, int op, const Ptrs<float>& p, int64_t B, void* ws, size_t wsb, cudaStream_t st) {
+  const int sm = device_info().sm_count;
+  const bool euler = (d->flags & GPFLOW_FLAG_EULER_PEN) != 0;
+  SmallShape s;
+  if (small_match(d, &s)) return euler ? small_2_1_15_15_f32_euler(d, op, &p, B, ws, wsb, st, sm) : small_2_1_15_15_f32(d, op, &p, B, ws, wsb, st, sm);
+  return (euler ? generic_f32_euler : generic_f32)(d, op, p.params, p.x_in, p.x_data, p.grad_y, p.reg_cot, p.zw, p.y_out,
+                                                 p.logdet_out, p.traj_out, p.grad_x_out, p.grads_out, p.scalars_out, B, ws,
+                                                 wsb, st, sm, nullptr, 0.0);
+}
+template <>
+int dispatch<double>(const GpFlowDesc* d, int op, const Ptrs<double>& p, int64_t B, void* ws, size_t wsb, cudaStream_t st) {
+  const int sm = device_info().sm_count;
+  const bool euler = (d->flags & GPFLOW_FLAG_EULER_PEN) != 0;
+  SmallShape s;
+  if (small_match(d, &s)) return euler ? small_2_1_15_15_f64_euler(d, op, &p, B, ws, wsb, st, sm) : small_2_1_15_15_f64(d, op, &p, B, ws, wsb, st, sm);
+  return (euler ? generic_f64_euler : generic_f64)(d, op, p.params, p.x_in, p.x_data, p.grad_y, p.reg_cot, p.zw, p.y_out,
+                                                 p.logdet_out, p.traj_out, p.grad_x_out, p.grads_out, p.scalars_out, B, ws,
+                                                 wsb, st, sm, nullptr, 0.0);
+}
+
+bool misaligned(const void* p, size_t a) { return p != nullptr && (reinterpret_cast<uintptr_t>(p) % a) != 0; }
+
+int run(const GpFlowDesc* d, int op, const void* params, const void* x_in, const void* x_data, const void* grad_y,
+        const void* reg_cot, const void* zw, void* y_out, void* logdet_out, void* traj_out, void* grad_x_out,
+        void* grads_out, void* scalars_out, int64_t B, void* ws, size_t wsb, void* stream) {
+  const int rc = validate(d);
+  if (rc != GPFLOW_OK) return rc;
+  if (B < 0) return GPFLOW_ERR_BAD_DESC;
+  if (params == nullptr || (B > 0 && x_in == nullptr)) return GPFLOW_ERR_NULL_POINTER;
+  if ((d->flags & GPFLOW_FLAG_EULER_PEN) && zw == nullptr) return GPFLOW_ERR_NULL_POINTER;
+  const size_t es = d->dtype == GPFLOW_F64 ? 8 : 4;
+  const void* all[] = {params, x_in, x_data, grad_y, reg_cot, zw, y_out, logdet_out, traj_out, grad_x_out, grads_out, scalars_out};
+  for (const void* q : all)
+    if (misaligned(q, es)) return GPFLOW_ERR_MISALIGNED;
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  if (d->dtype == GPFLOW_F32) {
+    Ptrs<float> p = {(const float*)params, (const float*)x_in, (const float*)x_data, (const float*)grad_y,
+                     (const float*)reg_cot, (const float*)zw, (float*)y_out, (float*)logdet_out, (float*)traj_out,
+                     (float*)grad_x_out, (float*)grads_out, (float*)scalars_out};
+    return dispatch<float>(d, op, p, B, ws, wsb, st);
+  }
+  Ptrs<double> p = {(const double*)params, (const double*)x_in, (const double*)x_data, (const double*)grad_y,
+                    (const double*)reg_cot, (const double*)zw, (double*)y_out, (double*)logdet_out, (double*)traj_out,
+                    (double*)grad_x_out, (double*)grads_out, (double*)scalars_out};
+  return dispatch<double>(d, op, p, B, ws, wsb, st);
+}
+
+// ---- FP32 FMA burn (roofline denominator) --------------------------------------------------------
+__global__ void __launch_bounds__(256) fma_burn_kernel(long long iters, float* sink) {
+  float a0 = threadIdx.x * 1e-3f, a1 = a0 + 1.f, a2 = a0 + 2.f, a3 = a0 + 3.f, a4 = a0 + 4.f, a5 = a0 + 5.f,
+        a6 = a0 + 6.f, a7 = a0 + 7.f;
+  const float m = 0.999f + blockIdx.x * 1e-9f, c = 1e-3f;
+  for (long long i = 0; i < iters; ++i) {
+#pragma unroll
+    for (int u = 0; u < 16; ++u) {
+      a0 = fmaf(a0, m, c); a1 = fmaf(a1, m, c); a2 = fmaf(a2, m, c); a3 = fmaf(a3, m, c);
+      a4 = fmaf(a4, m, c); a5 = fmaf(a5, m, c); a6 = fmaf(a6, m, c); a7 = fmaf(a7, m, c);
+    }
+  }
+  const float s = a0 + a1 + a2 + a3 + a4 + a5 + a6 + a7;
+  if (s == 123.456f) sink[0] = s;
+}
+
+}  // namespace
+
+extern "C" {
+
+int64_t gpflow_param_count(const GpFlowDesc* d) {
+  if (validate(d) != GPFLOW_OK) return -1;
+  int64_t n = 0, prev = d->d + 1;
+  for (int i = 0; i < d->n_hidden; ++i) {
+    n += prev * d->hidden[i] + d->hidden[i];
+    prev = d->hidden[i];
+  }
+  n += prev * ((int64_t)d->d * d->nb) + (int64_t)d->d * d->nb;
+  return n;
+}
+
+int gpflow_query_workspace(const GpFlowDesc* d, int64_t B, int op, size_t* bytes) {
+  const int rc = validate(d);
+  if (rc != GPFLOW_OK) return rc;
+  if (bytes == nullptr) return GPFLOW_ERR_NULL_POINTER;
+  if (B < 0 || op < GPFLOW_OP_FORWARD || op > GPFLOW_OP_BACKWARD) return GPFLOW_ERR_BAD_DESC;
+  const int64_t np = gpflow_param_count(d);
+  SmallShape s;
+  if (small_match(d, &s)) {
+    *bytes = small_workspace(d, B, op, (int)np);
+    return GPFLOW_OK;
+  }
+  *bytes = generic_workspace_bytes(d, B, op);
+  return GPFLOW_OK;
+}
+
+int gpflow_forward(const GpFlowDesc* d, int64_t B, const void* params, const void* x_in, const void* zw, void* y_out,
+                   void* logdet_out, void* traj_out, void* scalars_out, void* ws, size_t wsb, void* stream) {
+  if (y_out == nullptr && B > 0) return GPFLOW_ERR_NULL_POINTER;
+  return run(d, GPFLOW_OP_FORWARD, params, x_in, nullptr, nullptr, nullptr, zw, y_out, logdet_out, traj_out, nullptr,
+             nullptr, scalars_out, B, ws, wsb, stream);
+}
+
+int gpflow_train_step(const GpFlowDesc* d, int64_t B, const void* params, const void* x_data, const void* x_map,
+                      const void* zw, void* grads_out, void* scalars_out, void* y_out, void* grad_xmap_out, void* ws,
+                      size_t wsb, void* stream) {
+  if (d != nullptr && !(d->flags & GPFLOW_FLAG_WRAP_GAUSS)) return GPFLOW_ERR_BAD_DESC;
+  if (grads_out == nullptr || scalars_out == nullptr || (B > 0 && x_data == nullptr)) return GPFLOW_ERR_NULL_POINTER;
+  return run(d, GPFLOW_OP_TRAIN_STEP, params, x_map, x_data, nullptr, nullptr, zw, y_out, nullptr, nullptr,
+             grad_xmap_out, grads_out, scalars_out, B, ws, wsb, stream);
+}
+
+int gpflow_backward(const GpFlowDesc* d, int64_t B, const void* params, const void* x_in, const void* grad_y,
+                    const void* reg_cotangent, const void* zw, void* grads_out, void* grad_x_out, void* ws, size_t wsb,
+                    void* stream) {
+  if (grads_out == nullptr || (B > 0 && grad_y == nullptr)) return GPFLOW_ERR_NULL_POINTER;
+  return run(d, GPFLOW_OP_BACKWARD, params, x_in, nullptr, grad_y, reg_cotangent, zw, nullptr, nullptr, nullptr,
+             grad_x_out, grads_out, nullptr, B, ws, wsb, stream);
+}
+
+int gpflow_velocity(const GpFlowDesc* d, int64_t B, const void* params, const void* x, double t, void* v_out, void* ws,
+                    size_t wsb, void* stream) {
+  const int rc = validate(d);
+  if (rc != GPFLOW_OK) return rc;
+  if (params == nullptr || x == nullptr || v_out == nullptr) return GPFLOW_ERR_NULL_POINTER;
+  if (B <= 0) return B == 0 ? GPFLOW_OK : GPFLOW_ERR_BAD_DESC;
+  GpFlowDesc dd = *d;
+  dd.flags &= ~(uint32_t)GPFLOW_FLAG_EULER_PEN;
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  const int sm = device_info().sm_count;
+  if (d->dtype == GPFLOW_F32)
+    return generic_f32(&dd, GPFLOW_OP_FORWARD, (const float*)params, (const float*)x, nullptr, nullptr, nullptr,
+                                 nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, B, ws, wsb, st, sm,
+                                 (float*)v_out, t);
+  return generic_f64(&dd, GPFLOW_OP_FORWARD, (const double*)params, (const double*)x, nullptr, nullptr,
+                                nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, B, ws, wsb, st,
+                                sm, (double*)v_out, t);
+}
+
+int gpflow_kernel_variant(const GpFlowDesc* d, int op, char* buf, size_t n) {
+  const int rc = validate(d);
+  if (rc != GPFLOW_OK) return rc;
+  if (buf == nullptr || n == 0) return GPFLOW_ERR_NULL_POINTER;
+  const char* ty = d->dtype == GPFLOW_F64 ? "f64" : "f32";
+  const char* mode = op == GPFLOW_OP_FORWARD ? "fwd" : (op == GPFLOW_OP_TRAIN_STEP ? "train" : "bwd");
+  const char* eu = (d->flags & GPFLOW_FLAG_EULER_PEN) ? ",euler" : "";
+  SmallShape s;
+  if (small_match(d, &s))
+    snprintf(buf, n, "gpflow_small_kernel<%s,d=%d,nb=%d,H=[%d,%d],%s%s>", ty, s.d, s.nb, s.h1, s.h2, mode, eu);
+  else
+    snprintf(buf, n, "gpflow_generic_kernel<%s,%s%s>", ty, mode, eu);
+  return GPFLOW_OK;
+}
+
+int gpflow_launch_count(const GpFlowDesc* d, int op) {
+  if (validate(d) != GPFLOW_OK) return -1;
+  (void)op;
+  SmallShape s;
+  return small_match(d, &s) ? 2 : 3;  // [weight transpose +] main kernel + deterministic finalize
+}
+
+int gpflow_fp32_fma_burn(int64_t iters, void* sink, double* host_flops_out, void* stream) {
+  if (sink == nullptr || iters < 1) return GPFLOW_ERR_NULL_POINTER;
+  const DeviceInfo di = device_info();
+  const int grid = di.sm_count * 8, block = 256;
+  fma_burn_kernel<<<grid, block, 0, reinterpret_cast<cudaStream_t>(stream)>>>((long long)iters, (float*)sink);
+  if (cudaGetLastError() != cudaSuccess) return GPFLOW_ERR_CUDA;
+  if (host_flops_out) *host_flops_out = 2.0 * 128.0 * (double)iters * (double)grid * (double)block;
+  return GPFLOW_OK;
+}
+
+const char* gpflow_error_string(int status) {
+  switch (status) {
+    case GPFLOW_OK: return "ok";
+    case GPFLOW_ERR_BAD_DESC: return "bad descriptor (inconsistent or out-of-range field)";
+    case GPFLOW_ERR_UNSUPPORTED: return "configuration not supported by the CUDA kernels";
+    case GPFLOW_ERR_NULL_POINTER: return "required pointer is NULL";
+    case GPFLOW_ERR_WORKSPACE: return "workspace too small (see gpflow_query_workspace)";
+    case GPFLOW_ERR_MISALIGNED: return "buffer not aligned";
+    case GPFLOW_ERR_CUDA: return "CUDA launch failed";
+    default: return "unknown status";
+  }
+}
+
+int gpflow_abi_version(void) { return GPFLOW_ABI_VERSION; }
+
+}  // extern "C"

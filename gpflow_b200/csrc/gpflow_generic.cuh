@@ -1,0 +1,790 @@
+// gpflow_b200 -- generic GP-flow kernels (sm_100a): any d, nb, depth and widths, fp32 / fp64.
+//
+// One WARP per sample; every phase is "owner computes": lanes stride over the outputs of the phase (hidden
+// units k, input units m, coordinates j), read the previous phase's results from the warp's scratch region
+// (global memory, L1/L2 resident) and __syncwarp() separates phases.  No atomics: each warp owns one partial
+// vector [ot, reg, lagr | parameter gradients] that gpflow_finalize_kernel sums in a fixed order.
+// Activations use the layout [j][k] (tangent direction major) so that lanes over k or m are coalesced; the
+// forward contractions read a transposed copy of the weights (lanes over output units), the reverse ones the
+// original nn.Linear layout (lanes over input units).
+//
+// Same math, same reference call sites as gpflow_small.cuh; scalar type S is T or
+// Dual<T> (Euler penalization by reverse-over-forward, see gpflow_common.cuh).
+#pragma once
+#include "../../include/gpflow_b200.h"
+#include "gpflow_common.cuh"
+#include <string.h>
+#include "gpflow_small.cuh"  // MODE_*, gpflow_finalize_kernel
+
+namespace gpflow {
+
+constexpr int GMAXL = GPFLOW_MAX_HIDDEN + 1;  // linear layers
+
+struct GDims {
+  int d, nb, L, nout, P;
+  int n[GMAXL + 1];     // widths: n[0] = d+1, n[1..L] hidden, n[L+1] = nout
+  int woff[GMAXL];      // offset of W_li in the flat parameters, li = 0..L  (row-major [n[li+1]][n[li]])
+  int boff[GMAXL];
+};
+struct GLayout {         // offsets (elements of the scalar type) inside one warp's scratch
+  int h[GMAXL + 1], sp[GMAXL + 1], U[GMAXL + 1], T[GMAXL + 1], hb[GMAXL + 1], Tb[GMAXL + 1];  // hidden li = 1..L
+  int f, J, fb, Jb, x, s, Q, Qb, sb, v, vbar, xbar, SX, SQ;
+  int total;
+};
+
+inline GDims make_gdims(const GpFlowDesc* d) {
+  GDims g;
+  memset(&g, 0, sizeof(g));
+  g.d = d->d; g.nb = d->nb; g.L = d->n_hidden; g.nout = d->d * d->nb;
+  g.n[0] = d->d + 1;
+  for (int i = 0; i < g.L; ++i) g.n[i + 1] = d->hidden[i];
+  g.n[g.L + 1] = g.nout;
+  int off = 0;
+  for (int li = 0; li <= g.L; ++li) {
+    g.woff[li] = off; off += g.n[li + 1] * g.n[li];
+    g.boff[li] = off; off += g.n[li + 1];
+  }
+  g.P = off;
+  return g;
+}
+inline GLayout make_glayout(const GDims& g) {
+  GLayout l;
+  memset(&l, 0, sizeof(l));
+  int off = 0;
+  auto take = [&](int n) { int o = off; off += (n + 3) / 4 * 4; return o; };
+  for (int li = 1; li <= g.L; ++li) {
+    l.h[li] = take(g.n[li]); l.sp[li] = take(g.n[li]); l.U[li] = take(g.n[li] * g.d); l.T[li] = take(g.n[li] * g.d);
+    l.hb[li] = take(g.n[li]); l.Tb[li] = take(g.n[li] * g.d);
+  }
+  l.f = take(g.nout); l.J = take(g.nout * g.d); l.fb = take(g.nout); l.Jb = take(g.nout * g.d);
+  l.x = take(g.d); l.s = take(g.d); l.Q = take(g.d); l.Qb = take(g.d); l.sb = take(g.d); l.v = take(g.d);
+  l.vbar = take(g.d); l.xbar = take(g.d); l.SX = take(g.nb); l.SQ = take(g.nb);
+  l.total = off;
+  return l;
+}
+
+template <typename T>
+struct GArgs {
+  GDims g;
+  GLayout lay;
+  const T* params;       // flat [P]
+  const T* params_t;     // transposed weights: Wt_li [n[li]][n[li+1]] at woff[li] (biases not copied)
+  const T* x_in; const T* x_data; const T* grad_y; const T* reg_cotangent; const T* zw;
+  T* y_out; T* logdet_out; T* traj_out; T* grad_x_out; T* v_out;
+  T* partials;           // [nwarps][3 + P]
+  char* scratch;         // per-warp scratch, stride scratch_stride bytes
+  size_t scratch_stride;
+  long long B;
+  int n_steps; int npart; unsigned flags;
+  T dt, t0, dt_constraint, sigma, euler_coef, loss_scale, t_eval;
+};
+
+template <typename T>
+__global__ void gpflow_transpose_params_kernel(GDims g, const T* __restrict__ p, T* __restrict__ pt) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= g.P) return;
+  for (int li = 0; li <= g.L; ++li) {
+    const int nin = g.n[li], no = g.n[li + 1];
+    if (i >= g.woff[li] && i < g.woff[li] + nin * no) {
+      const int e = i - g.woff[li], k = e / nin, m = e % nin;
+      pt[g.woff[li] + m * no + k] = p[i];
+      return;
+    }
+  }
+  pt[i] = p[i];  // biases
+}
+
+template <typename T>
+struct Generic {
+  static constexpr int JC = 8;  // tangent directions per register chunk
+  static constexpr int KT = 4;  // output rows per weight-gradient tile
+
+  template <typename S> GPF_DEV static T eps_part(const S& a);
+
+  // ---- forward of one linear layer li (0..L) + activation, lanes over output units ----
+  // in: li == 0 -> the point x (S[d]) and time t; else hidden li (h, T)
+  template <typename S>
+  GPF_DEV static void forward_layer(const GArgs<T>& a, S* sc, int li, T t, int lane) {
+    const GDims& g = a.g;
+    const GLayout& l = a.lay;
+    const int nin = g.n[li], no = g.n[li + 1], d = g.d;
+    const T* __restrict__ Wt = a.params_t + g.woff[li];
+    const T* __restrict__ bias = a.params + g.boff[li];
+    const bool last = (li == g.L);
+    if (li == 0) {
+      const S* x = sc + l.x;
+      for (int k = lane; k < no; k += 32) {
+        S acc = S(bias[k] + Wt[d * no + k] * t);
+        for (int j = 0; j < d; ++j) acc = acc + Wt[j * no + k] * x[j];
+        if (last) {
+          sc[l.f + k] = acc;
+          for (int j = 0; j < d; ++j) sc[l.J + j * no + k] = S(Wt[j * no + k]);
+        } else {
+          const S h = act_tanh(acc);
+          sc[l.h[1] + k] = h;
+          const S sp = T(1) - h * h;
+          sc[l.sp[1] + k] = sp;
+          for (int j = 0; j < d; ++j) {
+            sc[l.U[1] + j * no + k] = S(Wt[j * no + k]);
+            sc[l.T[1] + j * no + k] = sp * Wt[j * no + k];
+          }
+        }
+      }
+      return;
+    }
+    const S* __restrict__ hin = sc + l.h[li];
+    const S* __restrict__ Tin = sc + l.T[li];
+    for (int k = lane; k < no; k += 32) {
+      int n_of_k = 0;
+      if (last) {  // pruning: row (i, n) is only used when n <= i; column j only when j >= n
+        const int i = k / g.nb;
+        n_of_k = k % g.nb;
+        if (n_of_k > i) continue;
+      }
+      S acc = S(bias[k]);
+      for (int m = 0; m < nin; ++m) acc = acc + Wt[m * no + k] * hin[m];
+      S sp = S(T(0));
+      if (last) {
+        sc[l.f + k] = acc;
+      } else {
+        const S h = act_tanh(acc);
+        sc[l.h[li + 1] + k] = h;
+        sp = T(1) - h * h;
+        sc[l.sp[li + 1] + k] = sp;
+      }
+      for (int j0 = last ? (n_of_k / JC) * JC : 0; j0 < d; j0 += JC) {
+        S u[JC];
+#pragma unroll
+        for (int q = 0; q < JC; ++q) u[q] = S(T(0));
+        for (int m = 0; m < nin; ++m) {
+          const T wv = Wt[m * no + k];
+#pragma unroll
+          for (int q = 0; q < JC; ++q)
+            if (j0 + q < d) u[q] = u[q] + wv * Tin[(j0 + q) * nin + m];
+        }
+#pragma unroll
+        for (int q = 0; q < JC; ++q)
+          if (j0 + q < d) {
+            if (last) sc[l.J + (j0 + q) * no + k] = u[q];
+            else {
+              sc[l.U[li + 1] + (j0 + q) * no + k] = u[q];
+              sc[l.T[li + 1] + (j0 + q) * no + k] = sp * u[q];
+            }
+          }
+      }
+    }
+  }
+
+  // ---- A.2 assembly: Q_i, v_i from f, J, x ----
+  template <typename S>
+  GPF_DEV static void assemble(const GArgs<T>& a, S* sc, T bnd, int lane) {
+    const GDims& g = a.g;
+    const GLayout& l = a.lay;
+    const int d = g.d, nb = g.nb, no = g.nout;
+    const S* x = sc + l.x;
+    for (int j = lane; j < d; j += 32) sc[l.s + j] = x[j] * x[j] - bnd;
+    __syncwarp();
+    for (int i = lane; i < d; i += 32) {
+      S Q = S(T(0));
+      const int nmax = i < nb - 1 ? i : nb - 1;
+      for (int n = 0; n <= nmax; ++n) {
+        const S fi = sc[l.f + i * nb + n];
+        for (int j = n; j < d; ++j) {
+          if (j == i) continue;
+          Q = Q + (T(2) * (fi - sc[l.f + j * nb + n])) * x[j] +
+              sc[l.s + j] * (sc[l.J + j * no + i * nb + n] - sc[l.J + j * no + j * nb + n]);
+        }
+      }
+      sc[l.Q + i] = Q;
+      sc[l.v + i] = sc[l.s + i] * Q;
+    }
+    __syncwarp();
+  }
+
+  // velocity at the point stored in sc[l.x], result in sc[l.v]; keeps the activations for a following reverse
+  template <typename S>
+  __device__ __noinline__ static void eval_forward(const GArgs<T>& a, S* sc, T t, T bnd, int lane) {
+    for (int li = 0; li <= a.g.L; ++li) {
+      forward_layer<S>(a, sc, li, t, lane);
+      __syncwarp();
+    }
+    assemble<S>(a, sc, bnd, lane);
+  }
+
+  // ---- weight-gradient accumulation of linear layer li: gacc[k][m] += eps/real part of
+  //      ab[k] * in[m] + sum_j Ub[j][k] * Tin[j][m];  lanes over m, KT rows per tile ----
+  template <typename S>
+  GPF_DEV static void grad_layer(const GArgs<T>& a, const S* sc, T* gacc, int li, T t, const S* ab, const S* Ub, int lane) {
+    const GDims& g = a.g;
+    const GLayout& l = a.lay;
+    const int nin = g.n[li], no = g.n[li + 1], d = g.d;
+    T* __restrict__ gw = gacc + g.woff[li];
+    T* __restrict__ gb = gacc + g.boff[li];
+    const bool last = (li == g.L);
+    for (int k = lane; k < no; k += 32) gb[k] += eps_part<S>(ab[k]);
+    if (li == 0) {
+      // W0[k][j] += ab[k] x_j + Ub[j][k];  W0[k][d] += ab[k] t      (lanes over k; rows are short)
+      const S* x = sc + l.x;
+      for (int k = lane; k < no; k += 32) {
+        const S abk = ab[k];
+        for (int j = 0; j < d; ++j) gw[k * nin + j] += eps_part<S>(abk * x[j] + Ub[j * no + k]);
+        gw[k * nin + d] += eps_part<S>(abk * t);
+      }
+      return;
+    }
+    const S* __restrict__ hin = sc + l.h[li];
+    const S* __restrict__ Tin = sc + l.T[li];
+    for (int k0 = 0; k0 < no; k0 += KT) {
+      int jmin = 0;
+      if (last) {  // rows (i, n) with n > i carry zero adjoints; columns j < n are pruned
+        bool any = false;
+        jmin = d;
+        for (int q = 0; q < KT && k0 + q < no; ++q) {
+          const int i = (k0 + q) / g.nb, n = (k0 + q) % g.nb;
+          if (n <= i) { any = true; jmin = n < jmin ? n : jmin; }
+        }
+        if (!any) continue;
+      }
+      for (int m = lane; m < nin; m += 32) {
+        S acc[KT];
+        const S hm = hin[m];
+#pragma unroll
+        for (int q = 0; q < KT; ++q) acc[q] = (k0 + q < no) ? ab[k0 + q] * hm : S(T(0));
+        for (int j = jmin; j < d; ++j) {
+          const S tv = Tin[j * nin + m];
+#pragma unroll
+          for (int q = 0; q < KT; ++q)
+            if (k0 + q < no) acc[q] = acc[q] + Ub[j * no + k0 + q] * tv;
+        }
+#pragma unroll
+        for (int q = 0; q < KT; ++q)
+          if (k0 + q < no) gw[(k0 + q) * nin + m] += eps_part<S>(acc[q]);
+      }
+    }
+  }
+
+  // ---- reverse through linear layer li >= 1: (ab[k], Ub[j][k]) -> hb[m], Tb[j][m] of hidden li; lanes over m ----
+  template <typename S>
+  GPF_DEV static void backprop_layer(const GArgs<T>& a, S* sc, int li, const S* ab, const S* Ub, int lane) {
+    const GDims& g = a.g;
+    const GLayout& l = a.lay;
+    const int nin = g.n[li], no = g.n[li + 1], d = g.d;
+    const T* __restrict__ W = a.params + g.woff[li];
+    const bool last = (li == g.L);
+    for (int m = lane; m < nin; m += 32) {
+      S acc = S(T(0));
+      for (int k = 0; k < no; ++k) {
+        if (last && (k % g.nb) > (k / g.nb)) continue;
+        acc = acc + W[k * nin + m] * ab[k];
+      }
+      sc[l.hb[li] + m] = acc;
+      for (int j0 = 0; j0 < d; j0 += JC) {
+        S u[JC];
+#pragma unroll
+        for (int q = 0; q < JC; ++q) u[q] = S(T(0));
+        for (int k = 0; k < no; ++k) {
+          int n_of_k = 0;
+          if (last) {
+            n_of_k = k % g.nb;
+            if (n_of_k > (k / g.nb)) continue;
+          }
+          const T wv = W[k * nin + m];
+#pragma unroll
+          for (int q = 0; q < JC; ++q)
+            if (j0 + q < d && j0 + q >= n_of_k) u[q] = u[q] + wv * Ub[(j0 + q) * no + k];
+        }
+#pragma unroll
+        for (int q = 0; q < JC; ++q)
+          if (j0 + q < d) sc[l.Tb[li] + (j0 + q) * nin + m] = u[q];
+      }
+    }
+  }
+
+  // ---- full reverse sweep of one velocity evaluation (A.3 + A.4).  Needs the activations of eval_forward at
+  //      sc[l.x]; cotangent in sc[l.vbar]; result J_v^T vbar in sc[l.xbar]; parameter gradients into gacc ----
+  template <typename S>
+  __device__ __noinline__ static void eval_reverse(const GArgs<T>& a, S* sc, T* gacc, T t, int lane) {
+    const GDims& g = a.g;
+    const GLayout& l = a.lay;
+    const int d = g.d, nb = g.nb, no = g.nout;
+    const S* x = sc + l.x;
+    for (int j = lane; j < d; j += 32) {
+      sc[l.Qb + j] = sc[l.vbar + j] * sc[l.s + j];
+      sc[l.sb + j] = sc[l.vbar + j] * sc[l.Q + j];
+    }
+    __syncwarp();
+    // suffix sums SX_n = sum_{j>=n} x_j, SQ_n = sum_{i>=n} Qb_i
+    for (int n = lane; n < nb; n += 32) {
+      S sx = S(T(0)), sq = S(T(0));
+      for (int j = n; j < d; ++j) { sx = sx + x[j]; sq = sq + sc[l.Qb + j]; }
+      sc[l.SX + n] = sx;
+      sc[l.SQ + n] = sq;
+    }
+    __syncwarp();
+    // fb[(a,n)] = 2 (Qb_a SX_n - x_a SQ_n);  Jb[(a,n)][j] = s_j Qb_a (j != a, j >= n),  Jb[(a,n)][a] = -s_a (SQ_n - Qb_a)
+    for (int p = lane; p < no; p += 32) {
+      const int ia = p / nb, n = p % nb;
+      if (n > ia) {
+        sc[l.fb + p] = S(T(0));
+        for (int j = 0; j < d; ++j) sc[l.Jb + j * no + p] = S(T(0));
+        continue;
+      }
+      const S qa = sc[l.Qb + ia];
+      sc[l.fb + p] = T(2) * (qa * sc[l.SX + n] - x[ia] * sc[l.SQ + n]);
+      for (int j = 0; j < d; ++j) {
+        S v = S(T(0));
+        if (j >= n) v = (j == ia) ? -(sc[l.s + ia] * (sc[l.SQ + n] - qa)) : sc[l.s + j] * qa;
+        sc[l.Jb + j * no + p] = v;
+      }
+    }
+    // direct terms into xbar / sb (owner j)
+    for (int j = lane; j < d; j += 32) {
+      S xb = S(T(0)), sbj = sc[l.sb + j];
+      const int nmax = j < nb - 1 ? j : nb - 1;
+      for (int n = 0; n <= nmax; ++n) {
+        const S fj = sc[l.f + j * nb + n];
+        const S Jjj = sc[l.J + j * no + j * nb + n];
+        for (int i = n; i < d; ++i) {
+          if (i == j) continue;
+          const S qi = sc[l.Qb + i];
+          xb = xb + (T(2) * (sc[l.f + i * nb + n] - fj)) * qi;
+          sbj = sbj + (sc[l.J + j * no + i * nb + n] - Jjj) * qi;
+        }
+      }
+      sc[l.xbar + j] = xb + (T(2) * x[j]) * sbj;
+    }
+    __syncwarp();
+    // ---- layers, last to first
+    const S* ab = sc + l.fb;
+    const S* Ub = sc + l.Jb;
+    for (int li = g.L; li >= 1; --li) {
+      grad_layer<S>(a, sc, gacc, li, t, ab, Ub, lane);
+      backprop_layer<S>(a, sc, li, ab, Ub, lane);
+      __syncwarp();
+      // through the activation of hidden li (in place: hb -> ab, Tb -> Ub)
+      const int H = g.n[li];
+      for (int k = lane; k < H; k += 32) {
+        const S h = sc[l.h[li] + k], sp = sc[l.sp[li] + k];
+        S rs = S(T(0));
+        for (int j = 0; j < d; ++j) rs = rs + sc[l.Tb[li] + j * H + k] * sc[l.U[li] + j * H + k];
+        const S spp = (T(-2) * h) * sp;
+        sc[l.hb[li] + k] = sc[l.hb[li] + k] * sp + rs * spp;
+        for (int j = 0; j < d; ++j) sc[l.Tb[li] + j * H + k] = sp * sc[l.Tb[li] + j * H + k];
+      }
+      __syncwarp();
+      ab = sc + l.hb[li];
+      Ub = sc + l.Tb[li];
+    }
+    grad_layer<S>(a, sc, gacc, 0, t, ab, Ub, lane);
+    {  // xbar_j += sum_k W0[k][j] ab_1[k]
+      const int H = g.n[1], nin = g.n[0];
+      const T* __restrict__ W0 = a.params + g.woff[0];
+      for (int j = lane; j < d; j += 32) {
+        S acc = sc[l.xbar + j];
+        for (int k = 0; k < H; ++k) acc = acc + W0[k * nin + j] * ab[k];
+        sc[l.xbar + j] = acc;
+      }
+    }
+    __syncwarp();
+  }
+};
+
+template <typename T> template <typename S>
+GPF_DEV T Generic<T>::eps_part(const S& a) { return comp<IsDual<S>::value ? 1 : 0>(a); }
+
+// per-warp real-valued work vectors (elements of T), after the scalar scratch
+struct GVec { int xcur, ys, ksum, xb, ybsum, ybprev, kb, ystage, traj, aw, az, ub, total; };
+inline GVec make_gvec(const GDims& g, int n_steps) {
+  GVec v;
+  int off = 0;
+  auto take = [&](int n) { int o = off; off += (n + 3) / 4 * 4; return o; };
+  v.xcur = take(g.d); v.ys = take(g.d); v.ksum = take(g.d); v.xb = take(g.d); v.ybsum = take(g.d);
+  v.ybprev = take(g.d); v.kb = take(g.d); v.ystage = take(4 * g.d); v.traj = take((n_steps + 1) * g.d);
+  v.aw = take(g.d); v.az = take(g.d); v.ub = take(g.d);
+  v.total = off;
+  return v;
+}
+
+template <typename T>
+struct GKernelArgs {
+  GArgs<T> a;
+  GVec vec;
+  size_t vec_offset_bytes;  // offset of the T work vectors inside one warp's scratch
+};
+
+// epsilon part of a(x) = (v(x + delta v(x,t), t+delta) - v(x,t)) / delta along `dir` (A.7), result in out[d]
+template <typename T>
+__device__ __noinline__ void g_pen_tangent(const GArgs<T>& a, char* wscr, const T* xpt, const T* dir, T t, T bnd, T delta, T* out,
+                           int lane) {
+  typedef Dual<T> DS;
+  DS* sc = reinterpret_cast<DS*>(wscr);
+  const GLayout& l = a.lay;
+  const int d = a.g.d;
+  for (int j = lane; j < d; j += 32) sc[l.x + j] = DS(xpt[j], dir[j]);
+  __syncwarp();
+  Generic<T>::template eval_forward<DS>(a, sc, t, bnd, lane);
+  for (int j = lane; j < d; j += 32) {
+    const DS v1 = sc[l.v + j];
+    out[j] = -v1.e;
+    sc[l.x + j] = sc[l.x + j] + delta * v1;
+  }
+  __syncwarp();
+  Generic<T>::template eval_forward<DS>(a, sc, t + delta, bnd, lane);
+  for (int j = lane; j < d; j += 32) out[j] = (out[j] + sc[l.v + j].e) / delta;
+  __syncwarp();
+}
+
+// reverse of g_pen_tangent for one direction; ubar = cotangent of the epsilon part; accumulates into xb[d]
+template <typename T>
+__device__ __noinline__ void g_pen_reverse(const GArgs<T>& a, char* wscr, T* gacc, const T* xpt, const T* dir, const T* ubar, T t, T bnd,
+                           T delta, T* xb, T* tmp /* d, T */, int lane) {
+  typedef Dual<T> DS;
+  DS* sc = reinterpret_cast<DS*>(wscr);
+  const GLayout& l = a.lay;
+  const int d = a.g.d;
+  // forward 1 to obtain X2 = X + delta v1
+  for (int j = lane; j < d; j += 32) sc[l.x + j] = DS(xpt[j], dir[j]);
+  __syncwarp();
+  Generic<T>::template eval_forward<DS>(a, sc, t, bnd, lane);
+  for (int j = lane; j < d; j += 32) sc[l.x + j] = sc[l.x + j] + delta * sc[l.v + j];
+  __syncwarp();
+  // eval 2 forward (keep) + reverse with V2b = (ubar/delta, 0)
+  Generic<T>::template eval_forward<DS>(a, sc, t + delta, bnd, lane);
+  for (int j = lane; j < d; j += 32) sc[l.vbar + j] = DS(ubar[j] / delta, T(0));
+  __syncwarp();
+  Generic<T>::template eval_reverse<DS>(a, sc, gacc, t + delta, lane);
+  // X2b -> xb (eps part) and V1b = -ubar/delta + delta X2b ; stash V1b in vbar after recomputing eval 1
+  DS* x2b = sc + l.Qb;  // Qb is free after eval_reverse: reuse as a d-vector stash
+  for (int j = lane; j < d; j += 32) {
+    const DS v = sc[l.xbar + j];
+    x2b[j] = v;
+    xb[j] += v.e;
+  }
+  __syncwarp();
+  for (int j = lane; j < d; j += 32) {
+    tmp[j] = x2b[j].v;          // stash both parts in T vectors across the forward recompute
+    tmp[d + j] = x2b[j].e;
+    sc[l.x + j] = DS(xpt[j], dir[j]);
+  }
+  __syncwarp();
+  Generic<T>::template eval_forward<DS>(a, sc, t, bnd, lane);
+  for (int j = lane; j < d; j += 32)
+    sc[l.vbar + j] = DS(-ubar[j] / delta, T(0)) + delta * DS(tmp[j], tmp[d + j]);
+  __syncwarp();
+  Generic<T>::template eval_reverse<DS>(a, sc, gacc, t, lane);
+  for (int j = lane; j < d; j += 32) xb[j] += sc[l.xbar + j].e;
+  __syncwarp();
+}
+
+template <typename T, int MODE, bool EULER>
+__global__ void __launch_bounds__(128) gpflow_generic_kernel(const GKernelArgs<T> ka) {
+  const GArgs<T>& a = ka.a;
+  const GLayout& l = a.lay;
+  const GVec& vv = ka.vec;
+  const int lane = threadIdx.x & 31;
+  const long long gwarp = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const long long nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
+  const int d = a.g.d;
+  char* wscr = a.scratch + (size_t)gwarp * a.scratch_stride;
+  T* sc = reinterpret_cast<T*>(wscr);
+  T* vec = reinterpret_cast<T*>(wscr + ka.vec_offset_bytes);
+  T* part = a.partials + (size_t)gwarp * a.npart;
+  T* gacc = part + 3;
+  if (MODE != MODE_FWD)
+    for (int i = lane; i < a.g.P; i += 32) gacc[i] = T(0);
+  __syncwarp();
+
+  const bool wrap = (a.flags & 0x1u) != 0;
+  const bool want_lagr = (a.flags & 0x2u) != 0;
+  const T bnd = T(1) - Eps<T>::value;
+  const T dt = a.dt, hdt = a.dt / T(2), c6 = a.dt / T(6);
+  const T delta = T(2.0 * sqrt((double)Eps<T>::value));
+  const T sq2s = T(1.4142135623730951) * a.sigma;
+  T reg_cot = T(1);
+  if (MODE == MODE_BWD && a.reg_cotangent != nullptr) reg_cot = *a.reg_cotangent;
+  const T pen_w = a.euler_coef * a.loss_scale;
+  T ot_acc = T(0), pen_acc = T(0), lagr_acc = T(0);  // lane-partial sums
+
+  T* xcur = vec + vv.xcur; T* ys = vec + vv.ys; T* ksum = vec + vv.ksum; T* xb = vec + vv.xb;
+  T* ybsum = vec + vv.ybsum; T* ybprev = vec + vv.ybprev; T* ystage = vec + vv.ystage; T* traj = vec + vv.traj;
+  T* aw = vec + vv.aw; T* az = vec + vv.az; T* ub = vec + vv.ub;
+
+  for (long long b = gwarp; b < a.B; b += nwarps) {
+    for (int j = lane; j < d; j += 32) {
+      const T xi = a.x_in[b * d + j];
+      xcur[j] = wrap ? erf_real(xi / sq2s) : xi;
+    }
+    __syncwarp();
+    // ---------------- forward time loop ----------------
+    T t = a.t0;
+    for (int i = 0; i < a.n_steps; ++i) {
+      for (int j = lane; j < d; j += 32) {
+        traj[i * d + j] = xcur[j];
+        if (a.traj_out != nullptr) a.traj_out[((long long)i * a.B + b) * d + j] = xcur[j];
+        ys[j] = xcur[j];
+      }
+      __syncwarp();
+      for (int sg = 0; sg < 4; ++sg) {
+        const T ts = sg == 0 ? t : (sg == 3 ? t + dt : t + hdt);
+        for (int j = lane; j < d; j += 32) sc[l.x + j] = ys[j];
+        __syncwarp();
+        Generic<T>::template eval_forward<T>(a, sc, ts, bnd, lane);
+        const T wk = (sg == 1 || sg == 2) ? T(2) : T(1);
+        const T ak = sg == 2 ? dt : hdt;
+        for (int j = lane; j < d; j += 32) {
+          const T kv = sc[l.v + j];
+          ksum[j] = sg == 0 ? kv : ksum[j] + wk * kv;
+          ys[j] = xcur[j] + ak * kv;
+        }
+        __syncwarp();
+      }
+      for (int j = lane; j < d; j += 32) xcur[j] = xcur[j] + c6 * ksum[j];
+      __syncwarp();
+      if (want_lagr) {
+        for (int j = lane; j < d; j += 32) sc[l.x + j] = xcur[j];
+        __syncwarp();
+        Generic<T>::template eval_forward<T>(a, sc, t, bnd, lane);
+        for (int j = lane; j < d; j += 32) lagr_acc += T(0.5) * sc[l.v + j] * sc[l.v + j];
+        __syncwarp();
+      }
+      if (EULER && MODE == MODE_FWD) {
+        const T* zv = a.zw + (size_t)(i * 2 + 0) * d;
+        const T* wv = a.zw + (size_t)(i * 2 + 1) * d;
+        g_pen_tangent<T>(a, wscr, xcur, wv, t, bnd, delta, aw, lane);
+        g_pen_tangent<T>(a, wscr, xcur, zv, t, bnd, delta, az, lane);
+        T q = T(0);
+        for (int j = lane; j < d; j += 32) q += zv[j] * aw[j] - wv[j] * az[j];
+        q = warp_sum(q);
+        if (lane == 0) pen_acc += q * q;
+      }
+      t = t + dt;
+    }
+    for (int j = lane; j < d; j += 32) {
+      traj[a.n_steps * d + j] = xcur[j];
+      if (a.traj_out != nullptr) a.traj_out[((long long)a.n_steps * a.B + b) * d + j] = xcur[j];
+    }
+    // ---------------- wrapper epilogue ----------------
+    T ny = T(0), nx = T(0);
+    for (int j = lane; j < d; j += 32) {
+      const T gT = xcur[j];
+      T yv = gT;
+      bool inband = true;
+      if (wrap) {
+        const T lim = T(1) - Eps<T>::value;
+        const T gc = gT < -lim ? -lim : (gT > lim ? lim : gT);
+        inband = (gT >= -lim) && (gT <= lim);
+        yv = sq2s * erfinv_real(gc);
+      }
+      const T xi = a.x_in[b * d + j];
+      ny += yv * yv;
+      nx += xi * xi;
+      if (a.y_out != nullptr) a.y_out[b * d + j] = yv;
+      if (MODE != MODE_FWD) {
+        T yb;
+        if (MODE == MODE_TRAIN) {
+          const T diff = a.x_data[b * d + j] - yv;
+          ot_acc += diff * diff;
+          yb = T(-2) * diff * a.loss_scale;
+        } else {
+          yb = a.grad_y[b * d + j];
+        }
+        if (wrap) {
+          const T dydg = T(1.2533141373155001) * a.sigma * exp_real(yv * yv / (T(2) * a.sigma * a.sigma));
+          xb[j] = inband ? yb * dydg : T(0);
+        } else {
+          xb[j] = yb;
+        }
+      }
+    }
+    if (a.logdet_out != nullptr) {
+      ny = warp_sum(ny);
+      nx = warp_sum(nx);
+      if (lane == 0) a.logdet_out[b] = (ny - nx) / (T(2) * a.sigma * a.sigma);
+    }
+    __syncwarp();
+    if (MODE == MODE_FWD) continue;
+
+    // ---------------- reverse time loop ----------------
+    // times: t_i by repeated addition -> recompute the forward sequence (cheap) for each i
+    for (int i = a.n_steps - 1; i >= 0; --i) {
+      T ti = a.t0;
+      for (int q = 0; q < i; ++q) ti = ti + dt;
+      if (EULER) {
+        const T* xn = traj + (size_t)(i + 1) * d;
+        const T* zv = a.zw + (size_t)(i * 2 + 0) * d;
+        const T* wv = a.zw + (size_t)(i * 2 + 1) * d;
+        g_pen_tangent<T>(a, wscr, xn, wv, ti, bnd, delta, aw, lane);
+        g_pen_tangent<T>(a, wscr, xn, zv, ti, bnd, delta, az, lane);
+        T q = T(0);
+        for (int j = lane; j < d; j += 32) q += zv[j] * aw[j] - wv[j] * az[j];
+        q = warp_sum(q);
+        if (lane == 0) pen_acc += q * q;
+        const T gq = T(2) * q * pen_w * reg_cot;
+        for (int j = lane; j < d; j += 32) ub[j] = gq * zv[j];
+        __syncwarp();
+        g_pen_reverse<T>(a, wscr, gacc, xn, wv, ub, ti, bnd, delta, xb, ystage /* scratch 2d */, lane);
+        for (int j = lane; j < d; j += 32) ub[j] = -gq * wv[j];
+        __syncwarp();
+        g_pen_reverse<T>(a, wscr, gacc, xn, zv, ub, ti, bnd, delta, xb, ystage, lane);
+      }
+      const T* x0 = traj + (size_t)i * d;
+      for (int j = lane; j < d; j += 32) ystage[j] = x0[j];
+      __syncwarp();
+      for (int sg = 0; sg < 3; ++sg) {
+        const T ts = sg == 0 ? ti : ti + hdt;
+        for (int j = lane; j < d; j += 32) sc[l.x + j] = ystage[sg * d + j];
+        __syncwarp();
+        Generic<T>::template eval_forward<T>(a, sc, ts, bnd, lane);
+        const T ak = sg == 2 ? dt : hdt;
+        for (int j = lane; j < d; j += 32) ystage[(sg + 1) * d + j] = x0[j] + ak * sc[l.v + j];
+        __syncwarp();
+      }
+      for (int j = lane; j < d; j += 32) { ybsum[j] = T(0); ybprev[j] = T(0); }
+      __syncwarp();
+      for (int sg = 3; sg >= 0; --sg) {
+        const T ts = sg == 0 ? ti : (sg == 3 ? ti + dt : ti + hdt);
+        const T wk = (sg == 1 || sg == 2) ? T(2) * c6 : c6;
+        const T ak = sg == 3 ? T(0) : (sg == 2 ? dt : hdt);
+        for (int j = lane; j < d; j += 32) sc[l.x + j] = ystage[sg * d + j];
+        __syncwarp();
+        Generic<T>::template eval_forward<T>(a, sc, ts, bnd, lane);
+        for (int j = lane; j < d; j += 32) sc[l.vbar + j] = wk * xb[j] + ak * ybprev[j];
+        __syncwarp();
+        Generic<T>::template eval_reverse<T>(a, sc, gacc, ts, lane);
+        for (int j = lane; j < d; j += 32) {
+          const T yb = sc[l.xbar + j];
+          ybprev[j] = yb;
+          ybsum[j] += yb;
+        }
+        __syncwarp();
+      }
+      for (int j = lane; j < d; j += 32) xb[j] = xb[j] + ybsum[j];
+      __syncwarp();
+    }
+    if (a.grad_x_out != nullptr) {
+      for (int j = lane; j < d; j += 32) {
+        T gx = xb[j];
+        if (wrap) {
+          const T xi = a.x_in[b * d + j];
+          gx *= T(0.7978845608028654) / a.sigma * exp_real(-xi * xi / (T(2) * a.sigma * a.sigma));
+        }
+        a.grad_x_out[b * d + j] = gx;
+      }
+    }
+    __syncwarp();
+  }
+  ot_acc = warp_sum(ot_acc);
+  pen_acc = warp_sum(pen_acc);
+  lagr_acc = warp_sum(lagr_acc);
+  if (lane == 0) {
+    part[0] = ot_acc * a.loss_scale;
+    part[1] = pen_acc * pen_w;
+    part[2] = lagr_acc * a.dt_constraint * a.loss_scale;
+  }
+}
+
+// VelocityField.__call__(x, t)  (velocity_field.py:118-126)
+template <typename T>
+__global__ void __launch_bounds__(128) gpflow_velocity_kernel(const GKernelArgs<T> ka) {
+  const GArgs<T>& a = ka.a;
+  const GLayout& l = a.lay;
+  const int lane = threadIdx.x & 31;
+  const long long gwarp = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const long long nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
+  T* sc = reinterpret_cast<T*>(a.scratch + (size_t)gwarp * a.scratch_stride);
+  const T bnd = T(1) - Eps<T>::value;
+  for (long long b = gwarp; b < a.B; b += nwarps) {
+    for (int j = lane; j < a.g.d; j += 32) sc[l.x + j] = a.x_in[b * a.g.d + j];
+    __syncwarp();
+    Generic<T>::template eval_forward<T>(a, sc, a.t_eval, bnd, lane);
+    for (int j = lane; j < a.g.d; j += 32) a.v_out[b * a.g.d + j] = sc[l.v + j];
+    __syncwarp();
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// host side: workspace carving and launch
+// ---------------------------------------------------------------------------------------------------
+struct GenericPlan {
+  long long nwarps;
+  size_t scratch_stride, vec_offset, partials_bytes, params_t_bytes, scratch_bytes, total;
+};
+inline GenericPlan generic_plan(const GpFlowDesc* d, int64_t B, int op, int sm_count) {
+  const size_t es = d->dtype == GPFLOW_F64 ? 8 : 4;
+  const GDims g = make_gdims(d);
+  const GLayout l = make_glayout(g);
+  const GVec v = make_gvec(g, d->n_steps);
+  const bool dual = (d->flags & GPFLOW_FLAG_EULER_PEN) != 0;
+  GenericPlan p;
+  p.vec_offset = ((size_t)l.total * es * (dual ? 2 : 1) + 255) / 256 * 256;
+  p.scratch_stride = (p.vec_offset + (size_t)v.total * es + 255) / 256 * 256;
+  long long nw = (long long)sm_count * 4 * 4;  // 4 CTAs of 4 warps per SM
+  if (nw > B) nw = B;
+  // bound the per-warp partial vectors (gradient accumulators) to ~2 GiB
+  const size_t per_warp = p.scratch_stride + (size_t)(3 + (op == GPFLOW_OP_FORWARD ? 0 : g.P)) * es;
+  const long long cap = (long long)((size_t)2 << 30) / (long long)per_warp;
+  if (nw > cap) nw = cap;
+  if (nw < 1) nw = 1;
+  nw = (nw + 3) / 4 * 4;  // whole CTAs
+  p.nwarps = nw;
+  p.partials_bytes = ((size_t)nw * (3 + g.P) * es + 255) / 256 * 256;
+  p.params_t_bytes = ((size_t)g.P * es + 255) / 256 * 256;
+  p.scratch_bytes = (size_t)nw * p.scratch_stride;
+  p.total = p.partials_bytes + p.params_t_bytes + p.scratch_bytes;
+  return p;
+}
+inline size_t generic_workspace(const GpFlowDesc* d, int64_t B, int op) {
+  return generic_plan(d, B, op, 160).total;  // device-independent upper bound (B200 has 148 SMs)
+}
+
+template <typename T, bool EULER>
+int launch_generic_impl(const GpFlowDesc* d, int op, const T* params, const T* x_in, const T* x_data, const T* grad_y,
+                   const T* reg_cot, const T* zw, T* y_out, T* logdet_out, T* traj_out, T* grad_x_out, T* grads_out,
+                   T* scalars_out, int64_t B, void* ws, size_t wsb, cudaStream_t st, int sm_count, T* v_out,
+                   double t_eval) {
+  if (ws == nullptr || wsb < generic_workspace(d, B, op)) return GPFLOW_ERR_WORKSPACE;
+  if (reinterpret_cast<uintptr_t>(ws) & 15) return GPFLOW_ERR_MISALIGNED;
+  const GenericPlan pl = generic_plan(d, B, op, sm_count);
+  GKernelArgs<T> ka;
+  memset(&ka, 0, sizeof(ka));
+  GArgs<T>& a = ka.a;
+  a.g = make_gdims(d);
+  a.lay = make_glayout(a.g);
+  ka.vec = make_gvec(a.g, d->n_steps);
+  ka.vec_offset_bytes = pl.vec_offset;
+  char* w = reinterpret_cast<char*>(ws);
+  a.partials = reinterpret_cast<T*>(w); w += pl.partials_bytes;
+  T* pt = reinterpret_cast<T*>(w); w += pl.params_t_bytes;
+  a.scratch = w;
+  a.scratch_stride = pl.scratch_stride;
+  a.params = params; a.params_t = pt; a.x_in = x_in; a.x_data = x_data; a.grad_y = grad_y; a.reg_cotangent = reg_cot;
+  a.zw = zw; a.y_out = y_out; a.logdet_out = logdet_out; a.traj_out = traj_out; a.grad_x_out = grad_x_out;
+  a.v_out = v_out; a.t_eval = (T)t_eval;
+  a.B = B; a.n_steps = d->n_steps; a.npart = 3 + a.g.P; a.flags = d->flags;
+  const bool rev = (d->flags & GPFLOW_FLAG_REVERSE) != 0;
+  a.dt = rev ? -(T)d->dt : (T)d->dt;
+  a.t0 = rev ? (T)(d->dt * (double)d->n_steps_nominal) : (T)0;
+  a.dt_constraint = (T)d->dt_constraint; a.sigma = (T)d->sigma; a.euler_coef = (T)d->euler_coef;
+  a.loss_scale = (T)d->loss_scale;
+  gpflow_transpose_params_kernel<T><<<(a.g.P + 255) / 256, 256, 0, st>>>(a.g, params, pt);
+  if (cudaGetLastError() != cudaSuccess) return GPFLOW_ERR_CUDA;
+  const unsigned grid = (unsigned)(pl.nwarps / 4);
+  if (v_out != nullptr) {
+    if (EULER) return GPFLOW_ERR_BAD_DESC;
+    gpflow_velocity_kernel<T><<<grid, 128, 0, st>>>(ka);
+    return cudaGetLastError() == cudaSuccess ? GPFLOW_OK : GPFLOW_ERR_CUDA;
+  }
+  if (op == GPFLOW_OP_FORWARD) gpflow_generic_kernel<T, MODE_FWD, EULER><<<grid, 128, 0, st>>>(ka);
+  else if (op == GPFLOW_OP_TRAIN_STEP) gpflow_generic_kernel<T, MODE_TRAIN, EULER><<<grid, 128, 0, st>>>(ka);
+  else gpflow_generic_kernel<T, MODE_BWD, EULER><<<grid, 128, 0, st>>>(ka);
+  if (cudaGetLastError() != cudaSuccess) return GPFLOW_ERR_CUDA;
+  const int count = op == GPFLOW_OP_FORWARD ? 3 : a.npart;
+  if (scalars_out != nullptr || grads_out != nullptr) {
+    gpflow_finalize_kernel<T><<<(count + 127) / 128, 128, 0, st>>>(a.partials, (int)pl.nwarps, a.npart, count,
+                                                                   scalars_out, grads_out);
+    if (cudaGetLastError() != cudaSuccess) return GPFLOW_ERR_CUDA;
+  }
+  return GPFLOW_OK;
+}
+
+}  // namespace gpflow

@@ -1,0 +1,127 @@
+"""Host-side mirror of the GP-flow parts of `src/gp_flows/network.py` (class Network) without Lightning.
+
+`gp_flow` (network.py:156-189), `loss_gp_flow` (:70-84), `ot_map` (:191-253) keep their names, arguments and
+semantics; `fused_training_step` is the B200 fast path for the GP branch of `training_step` (:104-114): one fused
+CUDA call produces the OT cost, the Euler regulariser and the parameter gradients (written to `.grad`), followed --
+in data-parallel runs -- by ONE all-reduce of a [P+3] buffer over NCCL.
+The frozen normalising-flow map (`self.map`, BNAF / FFJORD / CPFlow modules of the reference) is whatever module the
+caller passes in: it runs under no_grad upstream of the hot path and is out of scope here.
+"""
+from __future__ import annotations
+
+from contextlib import ExitStack
+from typing import Optional
+
+import torch
+
+from . import _lib, ops
+
+
+class GPFlowNetwork(torch.nn.Module):
+    def __init__(self, flow, map_module=None, sigma=1.0, process_group=None):
+        super().__init__()
+        self.map = map_module
+        self.flow = flow
+        self.sigma = sigma
+        self.target_gaussian = True
+        self.process_group = process_group
+        self._buf = None
+
+    # ---- network.py:156-189 ------------------------------------------------------------------
+    def gp_flow(self, x, reverse=False, save_trajectories=False):
+        if self.flow is None:
+            return (x, torch.zeros_like(x).sum(1)) if not reverse else x
+        y = self.flow(x, reverse=reverse, save_trajectories=save_trajectories, _wrap=True, _sigma=self.sigma)
+        if reverse:
+            return y
+        log_abs_det = ((y ** 2).sum(1) - (x ** 2).sum(1)) / (2.0 * self.sigma ** 2)
+        return y, log_abs_det
+
+    # ---- network.py:70-84 ---------------------------------------------------------------------
+    def loss_gp_flow(self, x, x_map: Optional[torch.Tensor] = None):
+        if x_map is None:
+            with torch.no_grad():
+                x_map = self.map(x)[0]
+        y, _ = self.gp_flow(x_map)
+        return ((x - y) ** 2).sum(-1).mean()
+
+    # ---- fused GP branch of training_step (network.py:104-111) ----------------------------------
+    @torch.no_grad()
+    def fused_training_step(self, x, x_map: Optional[torch.Tensor] = None, global_batch: Optional[int] = None,
+                            with_lagrangian=False):
+        """Computes loss_gp = OT cost, reg, and d(loss_gp + reg)/d(flow parameters) into `.grad`.
+        Returns (loss_gp, reg) as 0-dim tensors (no host sync).  With a process group the [grads | scalars] buffer is
+        all-reduced (SUM) once; `global_batch` defaults to B * world_size."""
+        if x_map is None:
+            x_map = self.map(x)[0]
+        flow = self.flow
+        cfg = flow.config(self.sigma)
+        world = 1
+        pg = self.process_group
+        if pg is not None or (torch.distributed.is_available() and torch.distributed.is_initialized()):
+            world = torch.distributed.get_world_size(pg)
+        B = x.shape[0]
+        gb = global_batch if global_batch is not None else B * world
+        euler = flow.euler_coef_penalization if flow._euler_active(x.dtype) else None
+        zw = flow.draw_probes(cfg.n_eval, x) if euler is not None else None
+        P = cfg.n_params
+        if self._buf is None or self._buf.numel() != P + _lib.NUM_SCALARS or self._buf.dtype != x.dtype or \
+                self._buf.device != x.device:
+            self._buf = torch.empty(P + _lib.NUM_SCALARS, dtype=x.dtype, device=x.device)
+        flat = flow.flat_parameters()
+        res = ops.fused_train_step(cfg, flat, x, x_map, euler_coef=euler, zw=zw, lagrangian=with_lagrangian,
+                                   loss_scale=1.0 / gb, out=self._buf, force_generic=flow.force_generic)
+        if world > 1:
+            torch.distributed.all_reduce(res["buf"], op=torch.distributed.ReduceOp.SUM, group=pg)
+        off = 0
+        for p in flow.parameters():
+            n = p.numel()
+            g = res["grads"][off:off + n].view_as(p)
+            if p.grad is None:
+                p.grad = g.clone()
+            else:
+                p.grad.copy_(g)
+            off += n
+        sc = res["scalars"]
+        flow.regularization_value = sc[_lib.SCALAR_REG]
+        if with_lagrangian:
+            flow.lagrangian = sc[_lib.SCALAR_LAGR]
+        return sc[_lib.SCALAR_OT], sc[_lib.SCALAR_REG]
+
+    # ---- network.py:191-253 -------------------------------------------------------------------
+    def ot_map(self, x, reverse=False, no_grad_map=False, no_grad_gp_flow=False, return_log_det=False):
+        def map_fun(v, reverse):
+            return self.map(v) if not reverse else (self.map.backward(v), None)
+
+        def gp_flow_fun(v, reverse):
+            return self.gp_flow(v) if not reverse else (self.gp_flow(v, reverse=True), None)
+
+        target_gaussian = (not self.target_gaussian) if reverse else self.target_gaussian
+        with ExitStack() as stack:
+            if target_gaussian:
+                if no_grad_map:
+                    stack.enter_context(torch.no_grad())
+                map_x, log_map = map_fun(x, reverse)
+                stack.close()
+                if no_grad_gp_flow:
+                    stack.enter_context(torch.no_grad())
+                out, log_gp = gp_flow_fun(map_x, reverse)
+                stack.close()
+            else:
+                if no_grad_gp_flow:
+                    stack.enter_context(torch.no_grad())
+                out, log_gp = gp_flow_fun(x, reverse)
+                stack.close()
+                if no_grad_map:
+                    stack.enter_context(torch.no_grad())
+                out, log_map = map_fun(out, reverse)
+                stack.close()
+        if return_log_det:
+            return out, log_map + log_gp
+        return out
+
+    def predict_map(self, x, reverse=False):
+        return self.map(x)[0] if not reverse else self.map.backward(x)
+
+    def get_flow_trajectories(self):
+        return self.flow.get_trajectories()

@@ -1,0 +1,27 @@
+"""Auxiliary GPU evaluations used by the module mirrors outside the train step (plots / trajectories)."""
+import ctypes
+
+import torch
+
+from . import _lib, ops
+
+
+def velocity(vf, x: torch.Tensor, t) -> torch.Tensor:
+    """VelocityField.__call__(x, t) (velocity_field.py:118-126) on the GPU."""
+    cfg = ops.FlowConfig(d=vf.dim, nb=vf.nb_div_blocks, hidden=tuple(vf.v.neurons[1:-1]), n_steps=1)
+    x = ops._check_cuda("x", x)
+    flat = vf.flat_parameters().detach()
+    desc = ops.make_desc(cfg, x.dtype, force_generic=True)
+    out = torch.empty_like(x)
+    lib = _lib.load()
+    with torch.cuda.device(x.device):
+        ws, n = ops._workspace(desc, x.shape[0], _lib.OP_FORWARD, x.device)
+        _lib.check(lib.gpflow_velocity(ctypes.byref(desc), x.shape[0], ops._ptr(flat), ops._ptr(x),
+                                       ctypes.c_double(float(t)), ops._ptr(out), ops._ptr(ws), n, ops._stream()))
+    return out
+
+
+def potentials(vfield, x):
+    raise NotImplementedError(
+        "gpflow_b200: VectorField.eval/.jacobian are evaluated inside the fused velocity kernels; a standalone "
+        "potentials op is not exported")

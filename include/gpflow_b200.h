@@ -1,0 +1,164 @@
+/*
+ * gpflow_b200 -- C ABI of the B200-native GP-flow (Gaussian-preserving flow) hot path.
+ *
+ * The reference (morel-g/GPFlow) is pure Python/PyTorch and has no FFI layer; the boundary this
+ * library sits behind is the nn.Module contract of src/gp_flows/res_net.py.  Each
+ * entry point below names the reference call sites whose work it replaces.  The host side
+ * (gpflow_b200/res_net.py, gpflow_b200/network.py) mirrors those modules and reaches this ABI
+ * through ctypes with raw device pointers; see INTEGRATION.md for the binding.
+ *
+ * Contract
+ *   - plain C: pointers, sizes, one POD descriptor.  No torch / C++ types cross the boundary.
+ *   - every pointer is a DEVICE pointer of the current CUDA device unless said otherwise; all
+ *     arrays are dense row-major of the element type selected by GpFlowDesc.dtype.
+ *   - the caller owns every buffer including the workspace; the library never allocates or frees
+ *     device memory and keeps no reference to caller memory after the call returns.
+ *   - all work is enqueued on the given stream; no host<->device synchronisation, no host read of
+ *     device data => calls are CUDA-graph capturable.  Re-entrant (no mutable global state).
+ *   - return value 0 = OK, otherwise a GpFlowStatus; no C++ exception crosses the boundary.
+ *     NaNs are data, not errors (the reference's NaN guard lives in validation_step,
+ *     src/gp_flows/network.py:134-138).
+ */
+#ifndef GPFLOW_B200_H
+#define GPFLOW_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GPFLOW_ABI_VERSION 1
+#define GPFLOW_MAX_HIDDEN 8
+
+typedef enum GpFlowStatus {
+  GPFLOW_OK = 0,
+  GPFLOW_ERR_BAD_DESC = 1,       /* inconsistent / out-of-range descriptor field            */
+  GPFLOW_ERR_UNSUPPORTED = 2,    /* valid but outside what the kernels implement             */
+  GPFLOW_ERR_NULL_POINTER = 3,   /* a required pointer is NULL                               */
+  GPFLOW_ERR_WORKSPACE = 4,      /* workspace smaller than gpflow_query_workspace() reports  */
+  GPFLOW_ERR_MISALIGNED = 5,     /* a buffer is not aligned to its element size              */
+  GPFLOW_ERR_CUDA = 6            /* cudaGetLastError() after a launch was not cudaSuccess    */
+} GpFlowStatus;
+
+typedef enum GpFlowDType { GPFLOW_F32 = 0, GPFLOW_F64 = 1 } GpFlowDType;
+
+typedef enum GpFlowOp { GPFLOW_OP_FORWARD = 0, GPFLOW_OP_TRAIN_STEP = 1, GPFLOW_OP_BACKWARD = 2 } GpFlowOp;
+
+/* GpFlowDesc.flags */
+#define GPFLOW_FLAG_WRAP_GAUSS 0x1u /* input lives in Gaussian space: g0 = erf(x/(sqrt2 sigma)) in front, y = sqrt2 sigma
+                                       erfinv(clip(g_T, +-(1-eps))) behind  (network.py:174-182).  Without it the op is the
+                                       raw cube-space flow, i.e. ResNet.forward (res_net.py:178-197).               */
+#define GPFLOW_FLAG_LAGRANGIAN 0x2u /* accumulate dt * mean_b sum_i 1/2 v_i(x_{k+1}, t_k)^2 (res_net.py:292-294,360-361) */
+#define GPFLOW_FLAG_EULER_PEN 0x4u  /* Euler penalization (res_net.py:295-302,319-358); needs zw probes              */
+#define GPFLOW_FLAG_REVERSE 0x8u    /* integrate from t0 = dt*n_steps_nominal with -dt (res_net.py:217-219)          */
+#define GPFLOW_FLAG_FORCE_GENERIC 0x10u /* testing aid: bypass the specialised small-d kernel                          */
+
+/*
+ * One GP flow = get_gp_flow(dim, velocity_dict, nb_layers_gp, T_final, ...) with nb_blocks == 1
+ * (res_net.py:14-67).  Only what the kernels implement is representable: tanh activation,
+ * continuous-time, incompressible velocity, RK4 / Case.standard; everything else stays on the
+ * reference's Python classes (SURVEY.md 8b "Unsupported by the kernels").
+ */
+typedef struct GpFlowDesc {
+  int32_t abi_version;            /* GPFLOW_ABI_VERSION                                                          */
+  int32_t dtype;                  /* GpFlowDType: precision mode (src/precision.py:7-13); also fixes eps         */
+  int32_t d;                      /* data.dim                                                                    */
+  int32_t nb;                     /* velocity_dict["nb_div_blocks"]  (1 <= nb <= d)                              */
+  int32_t n_hidden;               /* len(velocity_dict["nb_neurons"]) (1..GPFLOW_MAX_HIDDEN)                     */
+  int32_t hidden[GPFLOW_MAX_HIDDEN]; /* velocity_dict["nb_neurons"]                                              */
+  int32_t n_steps;                /* RK4 steps integrated: nb_layers (training) or nb_layers_eval (res_net.py:209-214) */
+  int32_t n_steps_nominal;        /* self.nb_layers; only used for the reverse start time (res_net.py:218)        */
+  uint32_t flags;                 /* GPFLOW_FLAG_*                                                               */
+  int32_t reserved0;
+  double dt;                      /* dt_solve > 0: self.dt or self.dt_eval                                       */
+  double dt_constraint;           /* self.dt -- the Lagrangian's weight is always self.dt (res_net.py:293)       */
+  double sigma;                   /* Network.sigma (network.py:51), used with GPFLOW_FLAG_WRAP_GAUSS             */
+  double euler_coef;              /* flow.euler_coef_penalization for this call (mutated by GPFlowCallback)      */
+  double loss_scale;              /* 1 / B_global.  Every sum over samples this library returns (OT cost, penalty,
+                                     Lagrangian, parameter gradients of the fused train step) is multiplied by it, so
+                                     that a SUM over data-parallel ranks gives the reference's batch MEAN.       */
+} GpFlowDesc;
+
+/* Number of parameters: sum_l (n_l * n_{l+1} + n_{l+1}), n = [d+1, hidden..., d*nb].  The flat parameter /
+ * gradient layout is [W_1, b_1, ..., W_{L+1}, b_{L+1}], each W row-major [out, in] exactly as
+ * nn.Linear.weight (vector_field.py:56-61), i.e. torch.cat([p.reshape(-1) for p in flow.parameters()]). */
+int64_t gpflow_param_count(const GpFlowDesc* desc);
+
+/* scalars_out layout (3 elements of dtype): */
+#define GPFLOW_SCALAR_OT 0   /* loss_scale * sum_b ||x_data_b - y_b||^2        (network.py:82)      */
+#define GPFLOW_SCALAR_REG 1  /* sum_k euler_coef * loss_scale * sum_b q_bk^2   (res_net.py:300-302)  */
+#define GPFLOW_SCALAR_LAGR 2 /* dt_constraint * loss_scale * sum_k sum_b 1/2|v|^2 (res_net.py:292-294) */
+#define GPFLOW_NUM_SCALARS 3
+
+/* Bytes of caller-provided workspace `op` needs for a batch of B samples (16-byte aligned start). */
+int gpflow_query_workspace(const GpFlowDesc* desc, int64_t B, int op, size_t* bytes);
+
+/*
+ * Forward transport.  Replaces ResNet.forward/solve/process_ode_solution (res_net.py:178-272) and, with
+ * GPFLOW_FLAG_WRAP_GAUSS, Network.gp_flow (network.py:156-189).
+ *   params      [P]        flat parameters
+ *   x_in        [B,d]      cube-space points (raw) or Gaussian-space points (WRAP_GAUSS)
+ *   zw          [n_steps,2,d] Euler probes z,w per step (nullable unless EULER_PEN)
+ *   y_out       [B,d]      transported points
+ *   logdet_out  [B]        nullable; (||y||^2 - ||x||^2) / (2 sigma^2), WRAP_GAUSS only (network.py:183-185)
+ *   traj_out    [n_steps+1,B,d] nullable; every RK4 state z_k in cube space (ode_solver.py:70-81)
+ *   scalars_out [3]        nullable; see GPFLOW_SCALAR_* (OT slot is written as 0)
+ */
+int gpflow_forward(const GpFlowDesc* desc, int64_t B, const void* params, const void* x_in, const void* zw, void* y_out,
+                   void* logdet_out, void* traj_out, void* scalars_out, void* workspace, size_t workspace_bytes,
+                   void* cuda_stream);
+
+/*
+ * Fused train step: forward, OT cost, Euler penalty, and the full backward pass in one launch (+ a
+ * deterministic finalize).  Replaces Network.loss_gp_flow + regularization_coef + manual_backward of the GP
+ * branch of training_step (network.py:70-84,104-111) for everything after the frozen map.
+ *   x_data  [B,d]   data points x (OT target)          x_map [B,d]  frozen-map output map(x)[0]
+ *   grads_out [P]   d(loss_scale*sum_b ||x-y||^2 + reg)/d params, flat layout above
+ *   scalars_out [3] GPFLOW_SCALAR_*
+ *   y_out [B,d] nullable.   grad_xmap_out [B,d] nullable: d loss / d x_map (ot_map(no_grad_map=False), network.py:227-236)
+ * Requires GPFLOW_FLAG_WRAP_GAUSS.
+ */
+int gpflow_train_step(const GpFlowDesc* desc, int64_t B, const void* params, const void* x_data, const void* x_map,
+                      const void* zw, void* grads_out, void* scalars_out, void* y_out, void* grad_xmap_out,
+                      void* workspace, size_t workspace_bytes, void* cuda_stream);
+
+/*
+ * Generic backward for the autograd case (any loss on top of the flow): given the cotangent of the
+ * transported points, recompute the trajectory and run the reverse sweep.
+ *   grad_y       [B,d]  cotangent of y_out (already carrying whatever batch normalisation the loss has)
+ *   reg_cotangent       nullable device scalar: cotangent of regularization_value (NULL = 1); the Euler term
+ *                       contributes reg_cotangent * euler_coef * loss_scale * sum_b q^2 per step
+ *   grads_out [P], grad_x_out [B,d] (nullable)
+ */
+int gpflow_backward(const GpFlowDesc* desc, int64_t B, const void* params, const void* x_in, const void* grad_y,
+                    const void* reg_cotangent, const void* zw, void* grads_out, void* grad_x_out,
+                    void* workspace, size_t workspace_bytes, void* cuda_stream);
+
+/*
+ * Velocity field evaluation v(x, t): VelocityField.__call__ (velocity_field.py:118-126), used outside the train step
+ * (trajectory / quiver plots, res_net.py:248-272).  x, v_out [B,d].  Workspace: gpflow_query_workspace(.., OP_FORWARD)
+ * with GPFLOW_FLAG_FORCE_GENERIC set in the descriptor (the evaluation always runs on the generic kernel family).
+ */
+int gpflow_velocity(const GpFlowDesc* desc, int64_t B, const void* params, const void* x, double t, void* v_out,
+                    void* workspace, size_t workspace_bytes, void* cuda_stream);
+
+/* Name of the kernel family an op on this descriptor dispatches to ("small<f32,2,1,15,15>", "generic<f64>", ...). */
+int gpflow_kernel_variant(const GpFlowDesc* desc, int op, char* buf, size_t buf_len);
+
+/* Number of kernel launches one call of `op` enqueues (for launch accounting in benchmarks). */
+int gpflow_launch_count(const GpFlowDesc* desc, int op);
+
+/* FP32 FMA micro-benchmark (roofline denominator): every thread of a grid that fills all SMs runs
+ * `iters` x 128 independent-chain FFMAs.  `sink` is a device float[1] (never written in practice).  The number of
+ * flops enqueued (2 per FFMA) is returned through `host_flops_out` (HOST pointer).  Time it with CUDA events. */
+int gpflow_fp32_fma_burn(int64_t iters, void* sink, double* host_flops_out, void* cuda_stream);
+
+const char* gpflow_error_string(int status);
+int gpflow_abi_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GPFLOW_B200_H */
