@@ -1,0 +1,328 @@
+#!/usr/bin/env python
+"""bench.py -- GP-flow train-step throughput (BASELINE.json metric) on N B200s of one node.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W]            # our CUDA path
+    python bench.py --impl reference [--gpus N] [--steps K] ...    # CPU reference arm (oracle port, host cores)
+
+Workload (BASELINE.json configs[3], SURVEY.md 8d "C4"): synthetic 2-D Gaussian-noise train_gp step, global batch
+2^24 samples sharded over the ranks (strong scaling), d=2, nb_div_blocks=1, velocity MLP [15,15], 15 RK4 steps,
+fp32.  One step = fused forward + OT cost + backward (one CUDA launch + deterministic finalize) -> ONE all-reduce of
+the [grads | scalars] buffer (N > 1) -> Adam update of the 332 parameters.
+Prints ONE JSON line (see the repo's task contract for the keys).
+"""
+import argparse
+import json
+import math
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    # name: (d, nb, hidden, n_steps, log2 global batch, weight std)
+    "c4_2d_2p24": dict(d=2, nb=1, hidden=(15, 15), n_steps=15, log2_batch=24, w_std=0.3,
+                       desc="synthetic train_gp_on_gaussian_noise 2D, 2^24-sample global batch"),
+    "c3_d10_nb9": dict(d=10, nb=9, hidden=(50, 50, 50), n_steps=15, log2_batch=12, w_std=0.05,
+                       desc="dsprites-latent shape d=10 nb=9 H=[50,50,50] (generic kernel)"),
+}
+
+
+def synth_batch(B, d, seed, device):
+    """x_map ~ N(0,I); x_data = deterministic affine image (stand-in for map.backward)."""
+    import torch
+    g = torch.Generator(device=device).manual_seed(seed)
+    x_map = torch.randn(B, d, generator=g, device=device, dtype=torch.float32)
+    th = math.pi / 3
+    A = torch.eye(d, device=device)
+    A[0, 0], A[0, 1], A[1, 0], A[1, 1] = math.cos(th), -math.sin(th), math.sin(th), math.cos(th)
+    scale = torch.ones(d, device=device)
+    scale[0], scale[1] = 1.5, 0.7
+    shift = torch.zeros(d, device=device)
+    shift[0], shift[1] = 0.5, -0.25
+    x_data = (x_map @ A) * scale + shift
+    return x_data.contiguous(), x_map.contiguous()
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md)."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            self.th = threading.Thread(target=self._read, daemon=True)
+            self.th.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm = sorted(float(r[1]) for r in self.rows if len(r) >= 9 and r[1].replace(".", "").isdigit())
+        reasons = set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            if len(r) >= 9:
+                for nm, v in zip(names, r[5:9]):
+                    if v.lower().startswith("active"):
+                        reasons.add(nm)
+        smax = next((float(r[2]) for r in self.rows if len(r) >= 9 and r[2].replace(".", "").isdigit()), None)
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": smax, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+def cpu_oracle_rate(wl, sample, steps, warmup, threads):
+    """The reference's algorithm on the host cores: oracle port (torch CPU, autograd), loss_gp_flow + backward."""
+    import torch
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import gpflow_oracle as O
+    torch.set_num_threads(threads)
+    spec = O.FlowSpec(d=wl["d"], nb=wl["nb"], hidden=list(wl["hidden"]), n_steps=wl["n_steps"])
+    params = O.init_params(spec, wl["w_std"], 0, torch.float32)
+    x_data, x_map = synth_batch(sample, wl["d"], 1234, "cpu")
+    times = []
+    for i in range(warmup + steps):
+        t0 = time.perf_counter()
+        O.train_step(params, x_data, x_map, spec)
+        if i >= warmup:
+            times.append(time.perf_counter() - t0)
+    return sample * len(times) / sum(times), sum(times) / len(times)
+
+
+def run_reference(args, wl, rank, world):
+    if rank != 0:
+        return
+    threads = os.cpu_count() or 1
+    sample = 1 << args.ref_log2_sample
+    rate, sec = cpu_oracle_rate(wl, sample, args.steps, args.warmup, threads)
+    line = {
+        "impl": "reference", "metric": "gp_flow_train_step_samples_per_sec", "value": rate, "unit": "samples/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": sec * 1e3,
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": args.workload + ": " + wl["desc"], "sample_per_step": sample},
+        "cpu_baseline": {"value": rate, "unit": "samples/s", "cores": threads, "kind": "port",
+                         "sample": "%d samples/step of the same synthetic batch; reference is pure Python and cannot "
+                                   "travel to the GPU box, so the oracle port (torch CPU autograd) is timed" % sample},
+        "e2e": {"value": rate, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="c4_2d_2p24", choices=sorted(WORKLOADS))
+    ap.add_argument("--log2-batch", type=int, default=None, help="override the global batch (log2)")
+    ap.add_argument("--ref-log2-sample", type=int, default=15)
+    ap.add_argument("--cpu-baseline-sample", type=int, default=1 << 17)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--euler", type=float, default=None, help="Euler penalization coefficient (extra row)")
+    args = ap.parse_args()
+    wl = dict(WORKLOADS[args.workload])
+    if args.log2_batch is not None:
+        wl["log2_batch"] = args.log2_batch
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.gpus > 1 and world == 1 and "RANK" not in os.environ:
+        # convenience: re-launch under torchrun exactly as the driver does
+        port = 29500 + os.getpid() % 1000
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(args.gpus),
+               "--master-addr", "127.0.0.1", "--master-port", str(port)] + sys.argv
+        sys.exit(subprocess.call(cmd))
+
+    if args.impl == "reference":
+        run_reference(args, wl, rank, world)
+        return
+
+    import torch
+    import torch.distributed as dist
+    import gpflow_b200 as G
+    from gpflow_b200 import ops, _lib
+
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    B_global = 1 << wl["log2_batch"]
+    B = B_global // world
+    d = wl["d"]
+
+    flow = G.get_gp_flow(d, {"nb_neurons": list(wl["hidden"]), "nb_div_blocks": wl["nb"]}, wl["n_steps"],
+                         euler_dict={"use_euler": args.euler is not None, "case": "penalization",
+                                     "coef_penalization": args.euler}).to(dev)
+    torch.manual_seed(0)
+    with torch.no_grad():
+        for p in flow.parameters():
+            p.normal_(0.0, wl["w_std"])           # N(0, 0.3^2) weights AND biases, seed 0
+    net = G.GPFlowNetwork(flow, map_module=None)
+    opt = torch.optim.Adam(flow.parameters(), lr=2e-3, betas=(0.9, 0.999), weight_decay=1e-4)   # network.py:312-317
+    cfg = flow.config()
+
+    # inputs resident in HBM; rotate through enough distinct batches to exceed the 126 MB L2
+    bytes_per_batch = 2 * B * d * 4
+    n_buf = max(1, min(8, math.ceil(300e6 / bytes_per_batch)))
+    bufs = [synth_batch(B, d, 1234 + rank + 1000 * i, dev) for i in range(n_buf)]
+
+    def step(i):
+        x_data, x_map = bufs[i % n_buf]
+        loss, reg = net.fused_training_step(x_data, x_map, global_batch=B_global)
+        opt.step()
+        return loss, reg
+
+    for i in range(args.warmup):
+        step(i)
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    clocks = ClockSampler(local_rank)
+    if rank == 0:
+        clocks.start()
+        time.sleep(0.25)
+    torch.cuda.synchronize()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    kev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    flat = flow.flat_parameters().detach()
+    ev0.record()
+    for i in range(args.steps):
+        x_data, x_map = bufs[i % n_buf]
+        # the fused train-step kernel (+ finalize) bracketed by its own events: roofline numerator
+        kev[i][0].record()
+        loss, reg = net.fused_training_step(x_data, x_map, global_batch=B_global)
+        kev[i][1].record()
+        opt.step()
+    ev1.record()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    ms_total = ev0.elapsed_time(ev1)
+    ms_kernel = sum(a.elapsed_time(b) for a, b in kev) / args.steps
+    t = torch.tensor([ms_total, ms_kernel], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_total, ms_kernel = float(t[0]), float(t[1])
+    clk = clocks.stop() if rank == 0 else None
+    ms_per_step = ms_total / args.steps
+    value = B_global / (ms_per_step * 1e-3)
+
+    # ---- e2e: public API with HOST buffers; H2D of the step's inputs and D2H of the loss inside the timed region
+    e2e = None
+    if not args.no_e2e:
+        hx = [(a.cpu().pin_memory(), b.cpu().pin_memory()) for a, b in bufs[:min(n_buf, 2)]]
+        dx = torch.empty_like(bufs[0][0])
+        dm = torch.empty_like(bufs[0][1])
+
+        def e2e_step(i):
+            a, b = hx[i % len(hx)]
+            dx.copy_(a, non_blocking=True)
+            dm.copy_(b, non_blocking=True)
+            loss, reg = net.fused_training_step(dx, dm, global_batch=B_global)
+            opt.step()
+            return float(loss) + float(reg)        # device->host read of the step's result
+
+        for i in range(2):
+            e2e_step(i)
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(args.steps):
+            e2e_step(i)
+        e1.record()
+        torch.cuda.synchronize()
+        te = torch.tensor([e0.elapsed_time(e1)], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(te, op=dist.ReduceOp.MAX)
+        e2e = {"value": B_global / (float(te[0]) / args.steps * 1e-3), "unit": "samples/s",
+               "h2d_bytes_per_step": 2 * B * d * 4 * world, "d2h_bytes_per_step": 8 * world}
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    # ---- roofline of the dominant kernel: FP32 FMA pipe (compute-bound, K=15 widths -> CUDA cores)
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import gpflow_oracle as O
+    spec = O.FlowSpec(d=d, nb=wl["nb"], hidden=list(wl["hidden"]), n_steps=wl["n_steps"])
+    flops_per_sample = O.algorithmic_flops_per_sample(spec, train=True)
+    peak_tf = ops.fp32_fma_peak_tflops()
+    achieved_tf = flops_per_sample * B / (ms_kernel * 1e-3) / 1e12
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    traffic = None
+    tp = os.path.join(ROOT, "profiles", "traffic_bytes_per_launch.json")
+    if os.path.exists(tp):
+        try:
+            traffic = json.load(open(tp)).get(args.workload)
+        except Exception:
+            traffic = None
+    roofline = {
+        "bound": "fp32_fma", "achieved": achieved_tf, "peak": peak_tf, "unit": "TFLOP/s",
+        "frac": achieved_tf / peak_tf if peak_tf else None, "traffic": traffic,
+        "kernel": G.kernel_variant(cfg, euler_coef=args.euler), "kernel_ms": ms_kernel,
+        "algorithmic_flops_per_sample": flops_per_sample, "samples_per_launch": B,
+        "peak_source": "FFMA burn micro-kernel measured live in this run (gpflow_fp32_fma_burn); MEASURED_PEAKS.json "
+                       "records no FP32 CUDA-core peak. Nominal 148 SM x 128 lanes x 2 x 1.965 GHz = 74.5 TFLOP/s",
+        "hbm_algorithmic_GBps": 12 * d * B / (ms_kernel * 1e-3) / 1e9,
+        "hbm_peak_GBps_measured": peaks.get("hbm_gbs"),
+    }
+    cpu_baseline = None
+    if not args.no_cpu_baseline and world == 1:
+        threads = os.cpu_count() or 1
+        rate, sec = cpu_oracle_rate(wl, args.cpu_baseline_sample, 2, 1, threads)
+        cpu_baseline = {"value": rate, "unit": "samples/s", "cores": threads, "kind": "port",
+                        "sample": "%d samples/step x 2 steps of the same synthetic workload (oracle port, torch CPU "
+                                  "autograd, all host threads)" % args.cpu_baseline_sample}
+    line = {
+        "metric": "gp_flow_train_step_samples_per_sec", "value": value, "unit": "samples/s", "n_gpus": world,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
+        "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": args.workload + ": " + wl["desc"], "global_batch": B_global, "per_gpu_batch": B,
+                   "d": d, "nb_div_blocks": wl["nb"], "hidden": list(wl["hidden"]), "nb_layers_gp": wl["n_steps"],
+                   "euler_coef": args.euler, "parallelism": "dp%d (batch shards, one all-reduce of %d floats)" % (
+                       world, cfg.n_params + 3),
+                   "l2": "inputs larger than L2: rotating through %d distinct resident batches of %.0f MB" % (
+                       n_buf, bytes_per_batch / 1e6),
+                   "step": "fused fwd+OT+bwd kernel, finalize, all-reduce, Adam"},
+        "clocks": clk, "e2e": e2e, "gpu_launches": args.steps * ops.launch_count(cfg),
+        "roofline": roofline, "cpu_baseline": cpu_baseline,
+        "loss": float(loss), "reg": float(reg),
+    }
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -24,7 +24,9 @@ def _cfg(spec):
 
 def _tols(tag, euler):
     if tag == "f64":
-        return dict(y=1e-10, g=1e-10, sc=1e-10, grad=1e-10 if not euler else 5e-9, reg=5e-9)
+        # Euler terms in fp64 mode are a finite difference with delta = 2 sqrt(eps64) = 3e-8: rounding noise of
+        # order eps/delta ~ 7e-9 relative is inherent to the reference's formula (res_net.py:346)
+        return dict(y=1e-10, g=1e-10, sc=1e-10, grad=1e-10 if not euler else 1e-7, reg=1e-7)
     return dict(y=1e-5, g=2e-6, sc=1e-5, grad=1e-5 if not euler else 5e-3, reg=5e-3)
 
 
@@ -75,7 +77,7 @@ def test_train_step_vs_oracle_and_golden(name, tag, force_generic):
     # (1) against the reference's own outputs (same precision mode): both carry their own rounding noise
     gt = dict(y=5e-5, sc=2e-5, grad=3e-5) if tag == "f32" else dict(y=1e-10, sc=1e-10, grad=1e-10)
     if c["euler"] is not None:
-        gt["grad"] = 5e-3 if tag == "f32" else 5e-9
+        gt["grad"] = 5e-3 if tag == "f32" else 1e-7
     assert rel(y, g["y"]) < gt["y"]
     assert abs(float(sc[0]) - float(g["ot"])) < gt["sc"] * abs(float(g["ot"]))
     if "grads" in g:
@@ -105,11 +107,15 @@ def test_forward_reverse_traj_vs_golden(name, tag, force_generic):
     out = G.flow_forward(cfg, flat, xm, wrap=True, lagrangian=True, euler_coef=c["euler"], zw=c["zw"].to(dev),
                          want_logdet=True, force_generic=force_generic)
     assert rel(out["y"].cpu(), g["y"]) < (1e-10 if f64 else 5e-5)
-    assert rel(out["logdet"].cpu(), g["logdet"]) < (1e-9 if f64 else 3e-4)
+    # log_abs_det = (|y|^2 - |x|^2)/2 cancels (it is ~0 for a near-identity flow): bound the error by the size
+    # of the two terms, not by the difference
+    ld_scale = float(np.linalg.norm((g["y"].astype(np.float64) ** 2).sum(1)))
+    ld_err = float(np.linalg.norm(out["logdet"].cpu().double().numpy() - g["logdet"].astype(np.float64)))
+    assert ld_err < (1e-10 if f64 else 5e-5) * ld_scale, (ld_err, ld_scale)
     sc = out["scalars"].cpu().double()
     assert abs(float(sc[2]) - float(g["lagrangian"])) < (1e-10 if f64 else 2e-5) * abs(float(g["lagrangian"])) + 1e-12
     if c["euler"] is not None:
-        assert abs(float(sc[1]) - float(g["reg"])) < (5e-9 if f64 else 5e-3) * abs(float(g["reg"]))
+        assert abs(float(sc[1]) - float(g["reg"])) < (1e-7 if f64 else 5e-3) * abs(float(g["reg"]))
     # raw cube-space flow: ResNet.forward
     g0 = torch.erf(c["x_map"] / np.sqrt(2.0)).to(dev)
     raw = G.flow_forward(cfg, flat, g0, wrap=False, want_traj="traj" in g, force_generic=force_generic)
@@ -146,6 +152,6 @@ def test_generic_backward_with_external_cotangent(name, tag):
     grads, gx = G.flow_backward(cfg, flat, c["x_map"].to(dev), cot.to(c["dtype"]).to(dev), wrap=True,
                                 euler_coef=c["euler"], zw=c["zw"].to(dev),
                                 reg_cotangent=torch.tensor(3.0, dtype=c["dtype"], device=dev))
-    tol = (1e-10 if c["euler"] is None else 5e-9) if tag == "f64" else (1e-5 if c["euler"] is None else 5e-3)
+    tol = (1e-10 if c["euler"] is None else 1e-7) if tag == "f64" else (1e-5 if c["euler"] is None else 5e-3)
     assert rel(grads.cpu(), gref) < tol, rel(grads.cpu(), gref)
     assert rel(gx.cpu(), xm.grad) < tol * 2, rel(gx.cpu(), xm.grad)
