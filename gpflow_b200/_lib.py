@@ -13,7 +13,7 @@ GPFLOW_ABI_VERSION = 1
 GPFLOW_MAX_HIDDEN = 8
 F32, F64 = 0, 1
 OP_FORWARD, OP_TRAIN_STEP, OP_BACKWARD = 0, 1, 2
-FLAG_WRAP_GAUSS, FLAG_LAGRANGIAN, FLAG_EULER_PEN, FLAG_REVERSE, FLAG_FORCE_GENERIC = 0x1, 0x2, 0x4, 0x8, 0x10
+FLAG_WRAP_GAUSS, FLAG_LAGRANGIAN, FLAG_EULER_PEN, FLAG_REVERSE, FLAG_FORCE_GENERIC, FLAG_FORCE_V1 = 0x1, 0x2, 0x4, 0x8, 0x10, 0x20
 SCALAR_OT, SCALAR_REG, SCALAR_LAGR, NUM_SCALARS = 0, 1, 2, 3
 
 EXPORTS = [

@@ -70,6 +70,16 @@ bool small_match(const GpFlowDesc* d, SmallShape* out) {
   return false;
 }
 
+// sf2 (stream-function kernel v2) covers the fp32 train step / backward of the (2,1,15,15) shape without Euler
+// penalization and without the Lagrangian diagnostic; everything else of that shape stays on the v1 kernel.
+bool sf2_match(const GpFlowDesc* d, int op) {
+  SmallShape s;
+  if (!small_match(d, &s) || d->dtype != GPFLOW_F32) return false;
+  if (op == GPFLOW_OP_FORWARD) return false;
+  if (d->flags & (GPFLOW_FLAG_EULER_PEN | GPFLOW_FLAG_LAGRANGIAN | GPFLOW_FLAG_FORCE_V1)) return false;
+  return d->n_steps <= 1024;
+}
+
 template <typename T>
 int dispatch(const GpFlowDesc* d, int op, const Ptrs<T>& p, int64_t B, void* ws, size_t wsb, cudaStream_t st);
 
@@ -78,6 +88,7 @@ int dispatch<float>(const GpFlowDesc* d, int op, const Ptrs<float>& p, int64_t B
   const int sm = device_info().sm_count;
   const bool euler = (d->flags & GPFLOW_FLAG_EULER_PEN) != 0;
   SmallShape s;
+  if (sf2_match(d, op)) return sf2_15_15_f32(d, op, &p, B, ws, wsb, st, sm);
   if (small_match(d, &s)) return euler ? small_2_1_15_15_f32_euler(d, op, &p, B, ws, wsb, st, sm) : small_2_1_15_15_f32(d, op, &p, B, ws, wsb, st, sm);
   return (euler ? generic_f32_euler : generic_f32)(d, op, p.params, p.x_in, p.x_data, p.grad_y, p.reg_cot, p.zw, p.y_out,
                                                  p.logdet_out, p.traj_out, p.grad_x_out, p.grads_out, p.scalars_out, B, ws,
@@ -159,6 +170,10 @@ int gpflow_query_workspace(const GpFlowDesc* d, int64_t B, int op, size_t* bytes
   if (B < 0 || op < GPFLOW_OP_FORWARD || op > GPFLOW_OP_BACKWARD) return GPFLOW_ERR_BAD_DESC;
   const int64_t np = gpflow_param_count(d);
   SmallShape s;
+  if (sf2_match(d, op)) {
+    *bytes = sf2_15_15_workspace(d, B);
+    return GPFLOW_OK;
+  }
   if (small_match(d, &s)) {
     *bytes = small_workspace(d, B, op, (int)np);
     return GPFLOW_OK;
@@ -218,7 +233,9 @@ int gpflow_kernel_variant(const GpFlowDesc* d, int op, char* buf, size_t n) {
   const char* mode = op == GPFLOW_OP_FORWARD ? "fwd" : (op == GPFLOW_OP_TRAIN_STEP ? "train" : "bwd");
   const char* eu = (d->flags & GPFLOW_FLAG_EULER_PEN) ? ",euler" : "";
   SmallShape s;
-  if (small_match(d, &s))
+  if (sf2_match(d, op))
+    snprintf(buf, n, "gpflow_sf2_kernel<f32,d=2,nb=1,H=[15,15],%s>", mode);
+  else if (small_match(d, &s))
     snprintf(buf, n, "gpflow_small_kernel<%s,d=%d,nb=%d,H=[%d,%d],%s%s>", ty, s.d, s.nb, s.h1, s.h2, mode, eu);
   else
     snprintf(buf, n, "gpflow_generic_kernel<%s,%s%s>", ty, mode, eu);

@@ -66,7 +66,8 @@ def _dtype_code(dtype):
 
 
 def make_desc(cfg: FlowConfig, dtype, *, wrap=False, reverse=False, training=False, lagrangian=False,
-              euler_coef: Optional[float] = None, loss_scale: float = 1.0, force_generic=False) -> GpFlowDesc:
+              euler_coef: Optional[float] = None, loss_scale: float = 1.0, force_generic=False,
+              force_v1=False) -> GpFlowDesc:
     d = GpFlowDesc()
     d.abi_version = _lib.GPFLOW_ABI_VERSION
     d.dtype = _dtype_code(dtype)
@@ -95,6 +96,8 @@ def make_desc(cfg: FlowConfig, dtype, *, wrap=False, reverse=False, training=Fal
         flags |= _lib.FLAG_REVERSE
     if force_generic:
         flags |= _lib.FLAG_FORCE_GENERIC
+    if force_v1:
+        flags |= _lib.FLAG_FORCE_V1
     d.flags = flags
     return d
 
@@ -172,7 +175,7 @@ def flow_forward(cfg: FlowConfig, params: torch.Tensor, x: torch.Tensor, *, wrap
 
 def fused_train_step(cfg: FlowConfig, params: torch.Tensor, x_data: torch.Tensor, x_map: torch.Tensor, *,
                      euler_coef=None, zw=None, lagrangian=False, loss_scale: Optional[float] = None, want_y=False,
-                     want_grad_x=False, out: Optional[torch.Tensor] = None, force_generic=False):
+                     want_grad_x=False, out: Optional[torch.Tensor] = None, force_generic=False, force_v1=False):
     """loss_gp_flow + regularization_coef + backward of the GP branch (network.py:70-84,104-111) in one fused call.
 
     Returns dict(buf, grads, scalars, y, grad_x).  `buf` is ONE contiguous tensor [P + 3] = [grads | ot, reg, lagr]
@@ -186,7 +189,8 @@ def fused_train_step(cfg: FlowConfig, params: torch.Tensor, x_data: torch.Tensor
     x_data = _check_cuda("x_data", x_data, dtype, (B, cfg.d))
     params = _check_cuda("params", params, dtype, (cfg.n_params,))
     desc = make_desc(cfg, dtype, wrap=True, training=False, lagrangian=lagrangian, euler_coef=euler_coef,
-                     loss_scale=(1.0 / max(B, 1)) if loss_scale is None else loss_scale, force_generic=force_generic)
+                     loss_scale=(1.0 / max(B, 1)) if loss_scale is None else loss_scale, force_generic=force_generic,
+                     force_v1=force_v1)
     zw = _prep_zw(zw, desc, cfg, dtype, x_map.device)
     P = cfg.n_params
     if out is None:
@@ -209,7 +213,7 @@ def fused_train_step(cfg: FlowConfig, params: torch.Tensor, x_data: torch.Tensor
 
 def flow_backward(cfg: FlowConfig, params: torch.Tensor, x_in: torch.Tensor, grad_y: torch.Tensor, *, wrap=False,
                   reverse=False, training=False, euler_coef=None, zw=None, reg_cotangent: Optional[torch.Tensor] = None,
-                  loss_scale: Optional[float] = None, want_grad_x=True, force_generic=False):
+                  loss_scale: Optional[float] = None, want_grad_x=True, force_generic=False, force_v1=False):
     """Reverse sweep for an arbitrary loss on top of the flow: returns (grads [P], grad_x [B,d] or None)."""
     x_in = _check_cuda("x_in", x_in)
     dtype = x_in.dtype
@@ -218,7 +222,8 @@ def flow_backward(cfg: FlowConfig, params: torch.Tensor, x_in: torch.Tensor, gra
     grad_y = _check_cuda("grad_y", grad_y, dtype, (B, cfg.d))
     params = _check_cuda("params", params, dtype, (cfg.n_params,))
     desc = make_desc(cfg, dtype, wrap=wrap, reverse=reverse, training=training, euler_coef=euler_coef,
-                     loss_scale=(1.0 / max(B, 1)) if loss_scale is None else loss_scale, force_generic=force_generic)
+                     loss_scale=(1.0 / max(B, 1)) if loss_scale is None else loss_scale, force_generic=force_generic,
+                     force_v1=force_v1)
     zw = _prep_zw(zw, desc, cfg, dtype, x_in.device)
     if reg_cotangent is not None:
         reg_cotangent = _check_cuda("reg_cotangent", reg_cotangent.reshape(1).to(dtype), dtype, (1,))

@@ -53,7 +53,8 @@ typedef enum GpFlowOp { GPFLOW_OP_FORWARD = 0, GPFLOW_OP_TRAIN_STEP = 1, GPFLOW_
 #define GPFLOW_FLAG_LAGRANGIAN 0x2u /* accumulate dt * mean_b sum_i 1/2 v_i(x_{k+1}, t_k)^2 (res_net.py:292-294,360-361) */
 #define GPFLOW_FLAG_EULER_PEN 0x4u  /* Euler penalization (res_net.py:295-302,319-358); needs zw probes              */
 #define GPFLOW_FLAG_REVERSE 0x8u    /* integrate from t0 = dt*n_steps_nominal with -dt (res_net.py:217-219)          */
-#define GPFLOW_FLAG_FORCE_GENERIC 0x10u /* testing aid: bypass the specialised small-d kernel                          */
+#define GPFLOW_FLAG_FORCE_GENERIC 0x10u /* testing aid: bypass the specialised small-d kernels                         */
+#define GPFLOW_FLAG_FORCE_V1 0x20u      /* testing aid: use the register-resident v1 small-d kernel instead of sf2     */
 
 /*
  * One GP flow = get_gp_flow(dim, velocity_dict, nb_layers_gp, T_final, ...) with nb_blocks == 1

@@ -55,7 +55,9 @@ def test_param_count_and_validation(lib):
 def test_workspace_query_and_variant_names(lib):
     from gpflow_b200 import ops, FlowConfig, kernel_variant, _lib
     c4 = FlowConfig(2, 1, (15, 15), 15)
-    assert "gpflow_small_kernel<f32,d=2,nb=1,H=[15,15],train>" == kernel_variant(c4)
+    assert "gpflow_sf2_kernel<f32,d=2,nb=1,H=[15,15],train>" == kernel_variant(c4)
+    assert "gpflow_small_kernel<f32,d=2,nb=1,H=[15,15],train>" == kernel_variant(c4, force_v1=True)
+    assert "gpflow_small_kernel<f32,d=2,nb=1,H=[15,15],fwd>" == kernel_variant(c4, op=_lib.OP_FORWARD)
     assert "generic" in kernel_variant(c4, force_generic=True)
     assert "generic" in kernel_variant(FlowConfig(10, 9, (50, 50, 50), 15))
     assert "euler" in kernel_variant(c4, euler_coef=0.01)
@@ -63,7 +65,10 @@ def test_workspace_query_and_variant_names(lib):
     n = ctypes.c_size_t(0)
     d = ops.make_desc(c4, torch.float32, wrap=True)
     assert lib.gpflow_query_workspace(ctypes.byref(d), 1 << 24, _lib.OP_TRAIN_STEP, ctypes.byref(n)) == 0
-    assert 0 < n.value < (1 << 27)          # persistent grid: scratch does not scale with B
+    assert 0 < n.value < (1 << 30)          # persistent grid: the activation stash does not scale with B
+    n_small = ctypes.c_size_t(0)
+    assert lib.gpflow_query_workspace(ctypes.byref(d), 1024, _lib.OP_TRAIN_STEP, ctypes.byref(n_small)) == 0
+    assert 0 < n_small.value < (1 << 25)
     big = ops.make_desc(FlowConfig(64, 63, (256, 256), 15), torch.float32, wrap=True)
     assert lib.gpflow_query_workspace(ctypes.byref(big), 1 << 14, _lib.OP_TRAIN_STEP, ctypes.byref(n)) == 0
     assert n.value < (6 << 30)

@@ -22,6 +22,10 @@ def _cfg(spec):
                       n_steps_eval=spec.n_steps_eval)
 
 
+def _specialised(variant):
+    return "small" in variant or "sf2" in variant
+
+
 def _tols(tag, euler):
     if tag == "f64":
         # Euler terms in fp64 mode are a finite difference with delta = 2 sqrt(eps64) = 3e-8: rounding noise of
@@ -53,7 +57,7 @@ def test_train_step_vs_oracle_and_golden(name, tag, force_generic):
     c, r = _truth(name, tag)
     g, spec = c["g"], c["spec"]
     cfg = _cfg(spec)
-    if not force_generic and "small" not in G.kernel_variant(cfg, c["dtype"]):
+    if not force_generic and not _specialised(G.kernel_variant(cfg, c["dtype"])):
         pytest.skip("no specialised kernel for this shape (generic run covers it)")
     tol = _tols(tag, c["euler"] is not None)
     dev = "cuda"
@@ -97,7 +101,7 @@ def test_forward_reverse_traj_vs_golden(name, tag, force_generic):
     c = load_golden(name, tag)
     g, spec = c["g"], c["spec"]
     cfg = _cfg(spec)
-    if not force_generic and "small" not in G.kernel_variant(cfg, c["dtype"]):
+    if not force_generic and not _specialised(G.kernel_variant(cfg, c["dtype"])):
         pytest.skip("no specialised kernel for this shape (generic run covers it)")
     f64 = tag == "f64"
     dev = "cuda"
@@ -137,7 +141,7 @@ def test_generic_backward_with_external_cotangent(name, tag):
     import gpflow_b200 as G
     c = load_golden(name, tag)
     spec, cfg = c["spec"], _cfg(c["spec"])
-    if "small" not in G.kernel_variant(cfg, c["dtype"]) and not hasattr(G._lib.load(), "gpflow_velocity"):
+    if not _specialised(G.kernel_variant(cfg, c["dtype"])) and not hasattr(G._lib.load(), "gpflow_velocity"):
         pytest.skip("generic kernel not built")
     gen = torch.Generator().manual_seed(3)
     cot = torch.randn(c["x_map"].shape, generator=gen, dtype=torch.float64)
