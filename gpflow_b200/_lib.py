@@ -7,7 +7,8 @@ import ctypes
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libgpflow_b200.so")
+# GPFLOW_B200_LIB: developer override to A/B-test an alternative build of the same library (still in-tree, still CUDA)
+LIB_PATH = os.environ.get("GPFLOW_B200_LIB") or os.path.join(_HERE, "lib", "libgpflow_b200.so")
 
 GPFLOW_ABI_VERSION = 1
 GPFLOW_MAX_HIDDEN = 8

@@ -20,7 +20,7 @@
 //     in the reverse sweep (9 KB per warp and evaluation, ~33 KB per sample and step, far below the HBM roof);
 //   * the only cross-sample coupling, the weight gradients, is handled per layer: W2 (the 15x15 bulk) by a warp-
 //     level rank-96 update per evaluation where each lane owns a 4x4 register tile of the gradient and reads the
-//     other lanes' rows from shared memory; W1/b1 by lane-private shared-memory accumulators; w3/b3 in registers;
+//     other lanes' rows from shared memory; W1/b1 by a second, 16x4 rank update of the same kind; w3/b3 in registers;
 //   * accumulation is two-level (per tile of 32 samples, then across tiles) so that 2^24-sample sums keep fp32
 //     relative accuracy ~1e-6; the per-warp partial vectors are reduced in a fixed order by gpflow_finalize_kernel.
 #pragma once
@@ -56,6 +56,26 @@ GPF_DEV float4 ldsw4(const float* p) {
   asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(smem_u32(p)));
   return v;
 }
+// GPF_SF2_CONST: 0 = packed weights in shared memory (LDS.128, 2 shared-memory wavefronts per warp-uniform load),
+// 1 = packed weights in the constant bank (no shared-memory traffic; with unrolled contractions the FFMA reads its
+// weight operand straight from c[][] and the load instruction disappears).
+#ifndef GPF_SF2_CONST
+#define GPF_SF2_CONST 0
+#endif
+#ifndef GPF_SF2_UNROLL
+#define GPF_SF2_UNROLL 0
+#endif
+#if GPF_SF2_CONST
+__constant__ float sf2_cw[640];
+GPF_DEV float4 ldw4(const float*, int off) { return *reinterpret_cast<const float4*>(&sf2_cw[off]); }
+#else
+GPF_DEV float4 ldw4(const float* W, int off) { return ldsw4(W + off); }
+#endif
+#if GPF_SF2_UNROLL
+#define GPF_SF2_LOOP _Pragma("unroll")
+#else
+#define GPF_SF2_LOOP _Pragma("unroll 1")
+#endif
 GPF_DEV float4 lds4(const float* p) { return *reinterpret_cast<const float4*>(p); }
 GPF_DEV void sts4(float* p, float a, float b, float c, float d) { *reinterpret_cast<float4*>(p) = make_float4(a, b, c, d); }
 
@@ -86,16 +106,16 @@ struct SF2 {
   // per-warp rows
   static constexpr int AS = 20;  // A row: x0 x1 psi g0 | h1[0..14] 1.0          (80 B  = 5 x 16)
   static constexpr int BS = 52;  // B row: h2[0..14] g1 | U2_0[16] | U2_1[16] | pad (208 B = 13 x 16)
-  static constexpr int CS = 68;  // W1 accumulator row: [16][4] + pad           (272 B = 17 x 16)
-  static constexpr int A_FL = 32 * AS, B_FL = 32 * BS, C_FL = 32 * CS;
+  static constexpr int A_FL = 32 * AS, B_FL = 32 * BS;
   static constexpr int A_BYTES = A_FL * 4, B_BYTES = B_FL * 4;
   static constexpr int STASH_BYTES = A_BYTES + B_BYTES;  // per warp and evaluation
-  static constexpr int WARP_FL = 2 * A_FL + 2 * B_FL + C_FL;
-  static constexpr int NACC = 36;  // second level: 16 W2 tile | 16 w3 | b3 | 2 W1 column sums | ot
-  static constexpr int G_W2 = 0, G_W3 = 16, G_B3 = 32, G_W1 = 33, G_OT = 35;
+  static constexpr int WARP_FL = 2 * A_FL + 2 * B_FL;
+  static constexpr int NACC = 50;  // second level: 16 W2 tile | 16 w3 | b3 | 16 W1 tile | ot
+  static constexpr int G_W2 = 0, G_W3 = 16, G_B3 = 32, G_W1 = 33, G_OT = 49;
+  static constexpr int SCT = 16;   // stage-constant table [4][4] {t offset, k weight, y step, k weight * dt/6}
 
   static size_t smem_bytes(int n_steps) {
-    return (size_t)(WEND + round_up(n_steps + 1, 4) + round_up(NPARAM, 4) + NW * WARP_FL) * sizeof(float) + 128;
+    return (size_t)(WEND + SCT + round_up(n_steps + 1, 4) + round_up(NPARAM, 4) + NW * WARP_FL) * sizeof(float) + 128;
   }
 };
 

@@ -1,5 +1,6 @@
 // gpflow_b200 -- sf2 kernel proper + host launch.  See gpflow_sf2.cuh for the design.
 #pragma once
+#include <stdlib.h>
 #include <string.h>
 
 #include "gpflow_dispatch.h"
@@ -7,38 +8,58 @@
 
 namespace gpflow {
 
+// packed weight i (layout in SF2<>) from the flat nn.Linear parameters: transpose / collapse / pad
+template <class K>
+GPF_DEV float sf2_pack_value(const float* __restrict__ raw, int i) {
+  constexpr int H1 = K::H1, H2 = K::H2;
+  float v = 0.0f;
+  if (i < K::W2T) {
+    const int k = i >> 2, c = i & 3;
+    if (k < H1) v = c < 3 ? raw[K::OFF_W1 + 3 * k + c] : raw[K::OFF_B1 + k];
+  } else if (i < K::W2R) {
+    const int m = (i - K::W2T) >> 4, k = (i - K::W2T) & 15;
+    if (k < H2) v = m < H1 ? raw[K::OFF_W2 + k * H1 + m] : (m == 15 ? raw[K::OFF_B2 + k] : 0.0f);
+  } else if (i < K::W3C) {
+    const int k = (i - K::W2R) >> 4, m = (i - K::W2R) & 15;
+    if (k < H2 && m < H1) v = raw[K::OFF_W2 + k * H1 + m];
+  } else if (i < K::B3C) {
+    const int k = i - K::W3C;
+    if (k < H2) v = raw[K::OFF_W3 + k] - raw[K::OFF_W3 + H2 + k];
+  } else if (i == K::B3C) {
+    v = raw[K::OFF_B3] - raw[K::OFF_B3 + 1];
+  }
+  return v;
+}
+
+template <class K>
+__global__ void sf2_pack_kernel(const float* __restrict__ params, float* __restrict__ packed) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < 640) packed[i] = i < K::WEND ? sf2_pack_value<K>(params, i) : 0.0f;
+}
+
 template <int H1, int H2, int NW, bool TRAIN>
 __global__ void __launch_bounds__(NW * 32, 1) gpflow_sf2_kernel(const SF2Args a) {
   typedef SF2<H1, H2, NW> K;
-  extern __shared__ __align__(128) unsigned char smem_raw[];
+  extern __shared__ __align__(16) unsigned char smem_raw[];
   __shared__ uint64_t bar_stage;
   __shared__ uint64_t bars[NW][2];
   float* const W = reinterpret_cast<float*>(smem_raw);
-  float* const times = W + K::WEND;
+  float* const sct = W + K::WEND;  // [4][4] stage constants
+  float* const times = sct + K::SCT;
   float* const raw = times + round_up(a.n_steps + 1, 4);
   float* const warp_area = raw + round_up(K::NPARAM, 4);
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 
   // ---- prologue: TMA bulk copy of the flat parameters, re-pack (transpose / collapse / pad), time table ----
   stage_params_to_smem<float>(raw, a.params, K::NPARAM, &bar_stage);
-  for (int i = tid; i < K::WEND; i += NW * 32) {
-    float v = 0.0f;
-    if (i < K::W2T) {
-      const int k = i >> 2, c = i & 3;
-      if (k < H1) v = c < 3 ? raw[K::OFF_W1 + 3 * k + c] : raw[K::OFF_B1 + k];
-    } else if (i < K::W2R) {
-      const int m = (i - K::W2T) >> 4, k = (i - K::W2T) & 15;
-      if (k < H2) v = m < H1 ? raw[K::OFF_W2 + k * H1 + m] : (m == 15 ? raw[K::OFF_B2 + k] : 0.0f);
-    } else if (i < K::W3C) {
-      const int k = (i - K::W2R) >> 4, m = (i - K::W2R) & 15;
-      if (k < H2 && m < H1) v = raw[K::OFF_W2 + k * H1 + m];
-    } else if (i < K::B3C) {
-      const int k = i - K::W3C;
-      if (k < H2) v = raw[K::OFF_W3 + k] - raw[K::OFF_W3 + H2 + k];
-    } else if (i == K::B3C) {
-      v = raw[K::OFF_B3] - raw[K::OFF_B3 + 1];
-    }
-    W[i] = v;
+  for (int i = tid; i < K::WEND; i += NW * 32) W[i] = sf2_pack_value<K>(raw, i);
+  if (tid < 4) {
+    // RK4 stage sg (ode_order_method.py:66-71): time offset, weight of k_sg in the sum, step to the next stage point
+    // (0 after the last stage; this is also the adjoint's dt-factor of yb_{sg+1}), weight * dt/6
+    const float hdt_ = a.dt / 2.0f, c6_ = a.dt / 6.0f;
+    const float wk_ = (tid == 1 || tid == 2) ? 2.0f : 1.0f;
+    sts4(sct + 4 * tid, tid == 0 ? 0.0f : (tid == 3 ? a.dt : hdt_), wk_, tid == 3 ? 0.0f : (tid == 2 ? a.dt : hdt_),
+         wk_ * c6_);
   }
   if (tid == 0) {
     float t = a.t0;  // repeated addition in the working precision (ode_solver.py:80, res_net.py:262)
@@ -55,28 +76,25 @@ __global__ void __launch_bounds__(NW * 32, 1) gpflow_sf2_kernel(const SF2Args a)
   float* const wa = warp_area + (size_t)warp * K::WARP_FL;
   float* const Abuf0 = wa;                         // A(b) = Abuf0 + b * A_FL
   float* const Bbuf0 = wa + 2 * K::A_FL;           // B(b) = Bbuf0 + b * B_FL
-  float* const Cbuf = wa + 2 * K::A_FL + 2 * K::B_FL;
-  float* const Crow = Cbuf + lane * K::CS;
   const int slot = blockIdx.x * NW + warp, nslots = gridDim.x * NW;
   float* const G = a.g2 + (size_t)slot * K::NACC * 32;
   if (TRAIN) {
-#pragma unroll
-    for (int i = 0; i < K::CS / 4; ++i) sts4(Crow + 4 * i, 0.f, 0.f, 0.f, 0.f);
     for (int i = 0; i < K::NACC; ++i) G[i * 32 + lane] = 0.0f;
   }
   __syncthreads();
 
   const bool wrap = (a.flags & 0x1u) != 0;
   const float bnd = 1.0f - Eps<float>::value;  // velocity_field.py:96
-  const float dt = a.dt, hdt = a.dt / 2.0f, c6 = a.dt / 6.0f;
+  const float c6 = a.dt / 6.0f;
   const float rsq2s = 1.0f / (1.4142135623730951f * a.sigma), sq2s = 1.4142135623730951f * a.sigma;
   const int E = 4 * a.n_steps;
   char* const stash = a.stash + (size_t)slot * E * K::STASH_BYTES;
-  uint32_t ph0 = 0, ph1 = 0;  // mbarrier phase parity of the two stash buffers
+  uint32_t phbits = 0;  // bit b = mbarrier phase parity of stash buffer b
+  uint64_t* const mybars = &bars[warp][0];
 
-  float acc[16], w3b[16], b3b = 0.0f;
+  float acc[16], accw[16], w3b[16], b3b = 0.0f;
 #pragma unroll
-  for (int i = 0; i < 16; ++i) acc[i] = w3b[i] = 0.0f;
+  for (int i = 0; i < 16; ++i) acc[i] = accw[i] = w3b[i] = 0.0f;
 
   const long long ntiles = (a.B + 31) / 32;
   for (long long tile = slot; tile < ntiles; tile += nslots) {
@@ -94,8 +112,8 @@ __global__ void __launch_bounds__(NW * 32, 1) gpflow_sf2_kernel(const SF2Args a)
 #pragma unroll 1
     for (int e = 0; e < E; ++e) {
       const int sg = e & 3, buf = e & 1;
-      const float t = times[e >> 2];
-      const float ts = sg == 0 ? t : (sg == 3 ? t + dt : t + hdt);
+      const float4 sc = ldsw4(sct + 4 * sg);
+      const float ts = times[e >> 2] + sc.x;  // t, t + dt/2, t + dt/2, t + dt
       float* const Ab = Abuf0 + buf * K::A_FL;
       float* const Bb = Bbuf0 + buf * K::B_FL;
       if (TRAIN && e >= 2) {  // the bulk store that read this buffer two evaluations ago must have drained
@@ -114,19 +132,17 @@ __global__ void __launch_bounds__(NW * 32, 1) gpflow_sf2_kernel(const SF2Args a)
           bulk_commit();
         }
       }
-      const float wk = (sg == 1 || sg == 2) ? 2.0f : 1.0f;
-      const float ak = sg == 2 ? dt : hdt;
-      ks0 = sg == 0 ? v0 : fmaf(wk, v0, ks0);
-      ks1 = sg == 0 ? v1 : fmaf(wk, v1, ks1);
-      if (sg == 3) {
-        x0 = fmaf(c6, ks0, x0);
-        x1 = fmaf(c6, ks1, x1);
-        ys0 = x0;
-        ys1 = x1;
-      } else {
-        ys0 = fmaf(ak, v0, x0);
-        ys1 = fmaf(ak, v1, x1);
-      }
+      // ksum = k1 + 2 k2 + 2 k3 + k4 accumulated left to right like the reference expression
+      ks0 = fmaf(sc.y, v0, ks0);
+      ks1 = fmaf(sc.y, v1, ks1);
+      const bool last = sg == 3;
+      const float xn0 = fmaf(c6, ks0, x0), xn1 = fmaf(c6, ks1, x1);
+      ys0 = last ? xn0 : fmaf(sc.z, v0, x0);
+      ys1 = last ? xn1 : fmaf(sc.z, v1, x1);
+      x0 = last ? xn0 : x0;
+      x1 = last ? xn1 : x1;
+      ks0 = last ? 0.0f : ks0;
+      ks1 = last ? 0.0f : ks1;
     }
     // ---------------- wrapper epilogue (network.py:178-185) ----------------
     float y0 = x0, y1 = x1;
@@ -167,43 +183,44 @@ __global__ void __launch_bounds__(NW * 32, 1) gpflow_sf2_kernel(const SF2Args a)
     if (lane == 0) {
       bulk_wait_all<0>();
       fence_proxy_async_all();
-      mbar_expect_tx(&bars[warp][(E - 1) & 1], K::STASH_BYTES);
+      mbar_expect_tx(mybars + ((E - 1) & 1), K::STASH_BYTES);
       const char* src = stash + (size_t)(E - 1) * K::STASH_BYTES;
-      bulk_g2s(Abuf0 + ((E - 1) & 1) * K::A_FL, src, K::A_BYTES, &bars[warp][(E - 1) & 1]);
-      bulk_g2s(Bbuf0 + ((E - 1) & 1) * K::B_FL, src + K::A_BYTES, K::B_BYTES, &bars[warp][(E - 1) & 1]);
+      bulk_g2s(Abuf0 + ((E - 1) & 1) * K::A_FL, src, K::A_BYTES, mybars + ((E - 1) & 1));
+      bulk_g2s(Bbuf0 + ((E - 1) & 1) * K::B_FL, src + K::A_BYTES, K::B_BYTES, mybars + ((E - 1) & 1));
     }
     // ---------------- reverse sweep (A.5) ----------------
     float sum0 = 0.f, sum1 = 0.f, prev0 = 0.f, prev1 = 0.f;
 #pragma unroll 1
     for (int e = E - 1; e >= 0; --e) {
       const int sg = e & 3, buf = e & 1;
-      const float t = times[e >> 2];
-      const float ts = sg == 0 ? t : (sg == 3 ? t + dt : t + hdt);
+      const float4 sc = ldsw4(sct + 4 * sg);
+      const float ts = times[e >> 2] + sc.x;
       // prefetch the rows of evaluation e-1 into the other buffer (its previous user, e+1, is complete)
       fence_proxy_async();
       __syncwarp();
       if (e > 0 && lane == 0) {
         const int nb = buf ^ 1;
-        mbar_expect_tx(&bars[warp][nb], K::STASH_BYTES);
+        mbar_expect_tx(mybars + nb, K::STASH_BYTES);
         const char* src = stash + (size_t)(e - 1) * K::STASH_BYTES;
-        bulk_g2s(Abuf0 + nb * K::A_FL, src, K::A_BYTES, &bars[warp][nb]);
-        bulk_g2s(Bbuf0 + nb * K::B_FL, src + K::A_BYTES, K::B_BYTES, &bars[warp][nb]);
+        bulk_g2s(Abuf0 + nb * K::A_FL, src, K::A_BYTES, mybars + nb);
+        bulk_g2s(Bbuf0 + nb * K::B_FL, src + K::A_BYTES, K::B_BYTES, mybars + nb);
       }
-      if (buf == 0) { mbar_wait(&bars[warp][0], ph0); ph0 ^= 1u; }
-      else { mbar_wait(&bars[warp][1], ph1); ph1 ^= 1u; }
+      mbar_wait(mybars + buf, (phbits >> buf) & 1u);
+      phbits ^= 1u << buf;
       // kb_4 = dt/6 xb; kb_3 = dt/3 xb + dt yb_4; kb_2 = dt/3 xb + dt/2 yb_3; kb_1 = dt/6 xb + dt/2 yb_2
-      const float wk = (sg == 1 || sg == 2) ? 2.0f * c6 : c6;
-      const float ak = sg == 3 ? 0.0f : (sg == 2 ? dt : hdt);
-      const float kb0 = fmaf(ak, prev0, wk * xb0), kb1 = fmaf(ak, prev1, wk * xb1);
+      const float kb0 = fmaf(sc.z, prev0, sc.w * xb0), kb1 = fmaf(sc.z, prev1, sc.w * xb1);
       float r0, r1;
-      sf2_reverse_eval<K>(W, Abuf0 + buf * K::A_FL, Bbuf0 + buf * K::B_FL, Crow, lane, ts, bnd, kb0, kb1, r0, r1, acc,
+      sf2_reverse_eval<K>(W, Abuf0 + buf * K::A_FL, Bbuf0 + buf * K::B_FL, lane, ts, bnd, kb0, kb1, r0, r1, acc, accw,
                           w3b, b3b);
       prev0 = r0; prev1 = r1;
       sum0 += r0; sum1 += r1;
-      if (sg == 0) {
-        xb0 += sum0; xb1 += sum1;
-        sum0 = sum1 = prev0 = prev1 = 0.0f;
-      }
+      const bool first = sg == 0;
+      xb0 = first ? xb0 + sum0 : xb0;
+      xb1 = first ? xb1 + sum1 : xb1;
+      sum0 = first ? 0.0f : sum0;
+      sum1 = first ? 0.0f : sum1;
+      prev0 = first ? 0.0f : prev0;
+      prev1 = first ? 0.0f : prev1;
     }
     if (valid && a.grad_x_out != nullptr) {
       float gx0 = xb0, gx1 = xb1;
@@ -220,23 +237,12 @@ __global__ void __launch_bounds__(NW * 32, 1) gpflow_sf2_kernel(const SF2Args a)
     for (int i = 0; i < 16; ++i) {
       G[(K::G_W2 + i) * 32 + lane] += acc[i];
       G[(K::G_W3 + i) * 32 + lane] += w3b[i];
-      acc[i] = w3b[i] = 0.0f;
+      G[(K::G_W1 + i) * 32 + lane] += accw[i];
+      acc[i] = w3b[i] = accw[i] = 0.0f;
     }
     G[K::G_B3 * 32 + lane] += b3b;
     b3b = 0.0f;
     G[K::G_OT * 32 + lane] += ot;
-    __syncwarp();
-    float c0 = 0.f, c1 = 0.f;
-#pragma unroll 8
-    for (int r = 0; r < 32; ++r) {
-      c0 += Cbuf[r * K::CS + lane];
-      c1 += Cbuf[r * K::CS + 32 + lane];
-    }
-    G[K::G_W1 * 32 + lane] += c0;
-    G[(K::G_W1 + 1) * 32 + lane] += c1;
-    __syncwarp();
-#pragma unroll
-    for (int i = 0; i < K::CS / 4; ++i) sts4(Crow + 4 * i, 0.f, 0.f, 0.f, 0.f);
   }
 
   if (!TRAIN) return;
@@ -251,9 +257,9 @@ __global__ void __launch_bounds__(NW * 32, 1) gpflow_sf2_kernel(const SF2Args a)
   }
   for (int e = lane; e < K::NPARAM; e += 32) {
     float s = 0.0f;
-    if (e < K::OFF_W2) {  // W1 [H1][3] then b1 [H1]  ->  column 4m + c of the C rows
-      const int col = e < K::OFF_B1 ? 4 * (e / 3) + e % 3 : 4 * (e - K::OFF_B1) + 3;
-      s = G[(K::G_W1 + (col >> 5)) * 32 + (col & 31)];
+    if (e < K::OFF_W2) {  // W1 [H1][3] then b1 [H1]  ->  tile entry (m & 3, c) of the lanes (slice, ti = m >> 2)
+      const int m = e < K::OFF_B1 ? e / 3 : e - K::OFF_B1, c = e < K::OFF_B1 ? e % 3 : 3;
+      for (int sl = 0; sl < 8; ++sl) s += G[(K::G_W1 + (m & 3) * 4 + c) * 32 + sl * 4 + (m >> 2)];
     } else if (e < K::OFF_W3) {  // W2 [H2][H1] then b2 [H2]  ->  tile entry (k, m), m = 15 for the bias
       const int k = e < K::OFF_B2 ? (e - K::OFF_W2) / H1 : e - K::OFF_B2;
       const int m = e < K::OFF_B2 ? (e - K::OFF_W2) % H1 : 15;
@@ -270,28 +276,37 @@ __global__ void __launch_bounds__(NW * 32, 1) gpflow_sf2_kernel(const SF2Args a)
 }
 
 // ---- host side --------------------------------------------------------------------------------------------------
-constexpr int kSF2Warps = 8;
+// Warps per CTA (one CTA per SM): 12 = three per scheduler at <= 168 registers, 8 = two per scheduler at <= 255.
+// GPFLOW_SF2_WARPS=8|12 overrides the default for experiments (read once).
+inline int sf2_warps() {
+  static const int w = [] {
+    const char* e = getenv("GPFLOW_SF2_WARPS");
+    const int v = e ? atoi(e) : 0;
+    return (v == 8 || v == 12) ? v : 12;
+  }();
+  return w;
+}
+constexpr int kSF2MaxWarps = 12;
 
 template <int H1, int H2>
 size_t sf2_workspace(const GpFlowDesc* d, int64_t B) {
-  typedef SF2<H1, H2, kSF2Warps> K;
-  const int64_t max_slots = (int64_t)kMaxSMs * kSF2Warps;
+  typedef SF2<H1, H2, kSF2MaxWarps> K;
+  const int64_t max_slots = (int64_t)kMaxSMs * kSF2MaxWarps;
   int64_t slots = (B + 31) / 32;
-  slots = (slots + kSF2Warps - 1) / kSF2Warps * kSF2Warps;
+  slots = (slots + kSF2MaxWarps - 1) / kSF2MaxWarps * kSF2MaxWarps;
   if (slots > max_slots) slots = max_slots;
-  if (slots < kSF2Warps) slots = kSF2Warps;
-  size_t bytes = align_up((size_t)slots * (3 + K::NPARAM) * 4, 256);
+  size_t bytes = 640 * 4;  // packed weights (staging for the constant bank)
+  bytes += align_up((size_t)slots * (3 + K::NPARAM) * 4, 256);
   bytes += align_up((size_t)slots * K::NACC * 32 * 4, 256);
   bytes += (size_t)slots * 4 * d->n_steps * K::STASH_BYTES;
   return bytes;
 }
 
-template <int H1, int H2>
-int launch_sf2(const GpFlowDesc* d, int op, const Ptrs<float>& p, int64_t B, void* ws, size_t ws_bytes, cudaStream_t st,
-               int sm_count) {
-  typedef SF2<H1, H2, kSF2Warps> K;
-  if (op == GPFLOW_OP_FORWARD) return GPFLOW_ERR_UNSUPPORTED;
-  auto kern = gpflow_sf2_kernel<H1, H2, kSF2Warps, true>;
+template <int H1, int H2, int NW>
+int launch_sf2_nw(const GpFlowDesc* d, const Ptrs<float>& p, int64_t B, void* ws, size_t ws_bytes, cudaStream_t st,
+                  int sm_count) {
+  typedef SF2<H1, H2, NW> K;
+  auto kern = gpflow_sf2_kernel<H1, H2, NW, true>;
   const size_t smem = K::smem_bytes(d->n_steps);
   if (smem > 227 * 1024) return GPFLOW_ERR_UNSUPPORTED;
   if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) {
@@ -302,10 +317,10 @@ int launch_sf2(const GpFlowDesc* d, int op, const Ptrs<float>& p, int64_t B, voi
   if (ws == nullptr || ws_bytes < need) return GPFLOW_ERR_WORKSPACE;
   if (reinterpret_cast<uintptr_t>(ws) & 255) return GPFLOW_ERR_MISALIGNED;
   const int64_t tiles = (B + 31) / 32;
-  int64_t grid = (tiles + kSF2Warps - 1) / kSF2Warps;
+  int64_t grid = (tiles + NW - 1) / NW;
   if (grid > sm_count) grid = sm_count;
   if (grid < 1) grid = 1;
-  const int64_t slots = grid * kSF2Warps;
+  const int64_t slots = grid * NW;
   const int npart = 3 + K::NPARAM;
 
   SF2Args a;
@@ -313,6 +328,8 @@ int launch_sf2(const GpFlowDesc* d, int op, const Ptrs<float>& p, int64_t B, voi
   a.params = p.params; a.x_in = p.x_in; a.x_data = p.x_data; a.grad_y = p.grad_y;
   a.y_out = p.y_out; a.grad_x_out = p.grad_x_out;
   char* wsp = reinterpret_cast<char*>(ws);
+  float* packed = reinterpret_cast<float*>(wsp);
+  wsp += 640 * 4;
   a.partials = reinterpret_cast<float*>(wsp);
   wsp += align_up((size_t)slots * npart * 4, 256);
   a.g2 = reinterpret_cast<float*>(wsp);
@@ -324,12 +341,30 @@ int launch_sf2(const GpFlowDesc* d, int op, const Ptrs<float>& p, int64_t B, voi
   a.t0 = rev ? (float)(d->dt * (double)d->n_steps_nominal) : 0.0f;  // res_net.py:217-219
   a.sigma = (float)d->sigma;
   a.loss_scale = (float)d->loss_scale;
-  kern<<<(unsigned)grid, kSF2Warps * 32, smem, st>>>(a);
+#if GPF_SF2_CONST
+  sf2_pack_kernel<K><<<5, 128, 0, st>>>(p.params, packed);
+  if (cudaGetLastError() != cudaSuccess) return GPFLOW_ERR_CUDA;
+  if (cudaMemcpyToSymbolAsync(sf2_cw, packed, 640 * 4, 0, cudaMemcpyDeviceToDevice, st) != cudaSuccess) {
+    cudaGetLastError();
+    return GPFLOW_ERR_CUDA;
+  }
+#else
+  (void)packed;
+#endif
+  kern<<<(unsigned)grid, NW * 32, smem, st>>>(a);
   if (cudaGetLastError() != cudaSuccess) return GPFLOW_ERR_CUDA;
   gpflow_finalize_kernel<float><<<(npart + 127) / 128, 128, 0, st>>>(a.partials, (int)slots, npart, npart, p.scalars_out,
                                                                      p.grads_out);
   if (cudaGetLastError() != cudaSuccess) return GPFLOW_ERR_CUDA;
   return GPFLOW_OK;
+}
+
+template <int H1, int H2>
+int launch_sf2(const GpFlowDesc* d, int op, const Ptrs<float>& p, int64_t B, void* ws, size_t ws_bytes, cudaStream_t st,
+               int sm_count) {
+  if (op == GPFLOW_OP_FORWARD) return GPFLOW_ERR_UNSUPPORTED;
+  if (sf2_warps() == 8) return launch_sf2_nw<H1, H2, 8>(d, p, B, ws, ws_bytes, st, sm_count);
+  return launch_sf2_nw<H1, H2, 12>(d, p, B, ws, ws_bytes, st, sm_count);
 }
 
 }  // namespace gpflow
