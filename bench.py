@@ -282,9 +282,9 @@ def main():
         pass
     traffic = None
     tp = os.path.join(ROOT, "profiles", "traffic_bytes_per_launch.json")
-    if os.path.exists(tp):
+    if os.path.exists(tp) and args.euler is None:
         try:
-            traffic = json.load(open(tp)).get(args.workload)
+            traffic = json.load(open(tp))[args.workload]["dram_bytes_per_sample"] * B   # per launch, like `achieved`
         except Exception:
             traffic = None
     roofline = {
@@ -294,8 +294,12 @@ def main():
         "algorithmic_flops_per_sample": flops_per_sample, "samples_per_launch": B,
         "peak_source": "FFMA burn micro-kernel measured live in this run (gpflow_fp32_fma_burn); MEASURED_PEAKS.json "
                        "records no FP32 CUDA-core peak. Nominal 148 SM x 128 lanes x 2 x 1.965 GHz = 74.5 TFLOP/s",
-        "hbm_algorithmic_GBps": 12 * d * B / (ms_kernel * 1e-3) / 1e9,
-        "hbm_peak_GBps_measured": peaks.get("hbm_gbs"),
+        "hbm": {"algorithmic_GBps": 12 * d * B / (ms_kernel * 1e-3) / 1e9,
+                "traffic_GBps": (traffic / (ms_kernel * 1e-3) / 1e9) if traffic else None,
+                "peak_GBps": peaks.get("hbm_gbs"), "peak_kind": "of measured (MEASURED_PEAKS.json copy bandwidth)",
+                "note": "algorithmic bytes = x_data + x_map + y (12 d B/sample); the measured DRAM traffic is the "
+                        "activation stash the kernel streams out in the forward sweep and back in the reverse sweep "
+                        "by TMA instead of recomputing 60 velocity evaluations (DESIGN.md section 4)"},
     }
     cpu_baseline = None
     if not args.no_cpu_baseline and world == 1:

@@ -14,7 +14,7 @@ from typing import Optional
 
 import torch
 
-from . import _lib, ops
+from . import _lib, data_parallel, ops
 
 
 class GPFlowNetwork(torch.nn.Module):
@@ -64,6 +64,8 @@ class GPFlowNetwork(torch.nn.Module):
         gb = global_batch if global_batch is not None else B * world
         euler = flow.euler_coef_penalization if flow._euler_active(x.dtype) else None
         zw = flow.draw_probes(cfg.n_eval, x) if euler is not None else None
+        if world > 1:
+            zw = data_parallel.broadcast_probes(zw, 0, pg)   # z, w are shared by all samples (res_net.py:330-343)
         P = cfg.n_params
         if self._buf is None or self._buf.numel() != P + _lib.NUM_SCALARS or self._buf.dtype != x.dtype or \
                 self._buf.device != x.device:
@@ -72,7 +74,7 @@ class GPFlowNetwork(torch.nn.Module):
         res = ops.fused_train_step(cfg, flat, x, x_map, euler_coef=euler, zw=zw, lagrangian=with_lagrangian,
                                    loss_scale=1.0 / gb, out=self._buf, force_generic=flow.force_generic)
         if world > 1:
-            torch.distributed.all_reduce(res["buf"], op=torch.distributed.ReduceOp.SUM, group=pg)
+            data_parallel.allreduce_train_buffer(res["buf"], pg)
         off = 0
         for p in flow.parameters():
             n = p.numel()
