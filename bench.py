@@ -48,48 +48,49 @@ def synth_batch(B, d, seed, device):
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md)."""
+    """Clocks / throttle reasons DURING the timed region (B200_PROFILING.md).
+    * throttle reasons + clocks.sm through NVML (the counters `nvidia-smi --query-gpu=clocks.sm,clocks_event_reasons.*`
+      prints) from a thread of this process, every 100 ms;
+    * the SM clock under load from an on-device probe (gpflow_clock_probe: clock64 ticks over globaltimer ns) enqueued
+      after every timed step -- no driver round trip, one sample per step."""
 
-    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
-         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
-         "clocks_event_reasons.sw_power_cap")
+    REASONS = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap"}
 
     def __init__(self, index):
-        self.index, self.rows, self.proc = index, [], None
+        self.index, self.sm, self.bits, self.th, self.stop_flag, self.smax, self.err = index, [], 0, None, False, None, None
 
     def start(self):
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
-                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE,
-                                         stderr=subprocess.DEVNULL, text=True)
-            self.th = threading.Thread(target=self._read, daemon=True)
-            self.th.start()
-        except Exception:
-            self.proc = None
+            import pynvml
+            pynvml.nvmlInit()
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            phys = int(vis.split(",")[self.index]) if vis and all(v.strip().isdigit() for v in vis.split(",")) else self.index
+            h = pynvml.nvmlDeviceGetHandleByIndex(phys)
+            self.smax = float(pynvml.nvmlDeviceGetMaxClockInfo(h, pynvml.NVML_CLOCK_SM))
 
-    def _read(self):
-        for line in self.proc.stdout:
-            self.rows.append([c.strip() for c in line.split(",")])
+            def loop():
+                while not self.stop_flag:
+                    try:
+                        self.sm.append(float(pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM)))
+                        self.bits |= int(pynvml.nvmlDeviceGetCurrentClocksEventReasons(h))
+                    except Exception as e:  # noqa: BLE001
+                        self.err = repr(e)
+                    time.sleep(0.1)
+
+            self.th = threading.Thread(target=loop, daemon=True)
+            self.th.start()
+        except Exception as e:  # noqa: BLE001
+            self.err = repr(e)
 
     def stop(self):
-        if self.proc is None:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        self.proc.terminate()
-        try:
-            self.proc.wait(timeout=2)
-        except Exception:
-            self.proc.kill()
-        sm = sorted(float(r[1]) for r in self.rows if len(r) >= 9 and r[1].replace(".", "").isdigit())
-        reasons = set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for r in self.rows:
-            if len(r) >= 9:
-                for nm, v in zip(names, r[5:9]):
-                    if v.lower().startswith("active"):
-                        reasons.add(nm)
-        smax = next((float(r[2]) for r in self.rows if len(r) >= 9 and r[2].replace(".", "").isdigit()), None)
-        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": smax, "reasons": sorted(reasons),
-                "samples": len(sm)}
+        self.stop_flag = True
+        if self.th is not None:
+            self.th.join(timeout=1.0)
+        if not self.sm:
+            return {"sm_mhz": None, "sm_max_mhz": self.smax, "reasons": ["nvml unavailable: %s" % self.err]}
+        sm = sorted(self.sm)
+        return {"sm_mhz": sm[len(sm) // 2], "sm_min_mhz": sm[0], "sm_max_mhz": self.smax,
+                "reasons": sorted(v for k, v in self.REASONS.items() if self.bits & k), "nvml_samples": len(sm)}
 
 
 def cpu_oracle_rate(wl, sample, steps, warmup, threads):
@@ -141,6 +142,7 @@ def main():
     ap.add_argument("--cpu-baseline-sample", type=int, default=1 << 17)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--dbg", default="", help=argparse.SUPPRESS)   # developer toggles: nbuf1,noopt,noclk
     ap.add_argument("--euler", type=float, default=None, help="Euler penalization coefficient (extra row)")
     args = ap.parse_args()
     wl = dict(WORKLOADS[args.workload])
@@ -160,6 +162,10 @@ def main():
     if args.impl == "reference":
         run_reference(args, wl, rank, world)
         return
+
+    # NCCL / torchrun may print banners on stdout: route fd 1 to stderr for the run, keep the real one for the JSON line
+    json_fd = os.dup(1)
+    os.dup2(2, 1)
 
     import torch
     import torch.distributed as dist
@@ -188,6 +194,8 @@ def main():
     # inputs resident in HBM; rotate through enough distinct batches to exceed the 126 MB L2
     bytes_per_batch = 2 * B * d * 4
     n_buf = max(1, min(8, math.ceil(300e6 / bytes_per_batch)))
+    if "nbuf1" in args.dbg:
+        n_buf = 1
     bufs = [synth_batch(B, d, 1234 + rank + 1000 * i, dev) for i in range(n_buf)]
 
     def step(i):
@@ -202,13 +210,16 @@ def main():
     if world > 1:
         dist.barrier()
     clocks = ClockSampler(local_rank)
-    if rank == 0:
-        clocks.start()
-        time.sleep(0.25)
+    if rank == 0 and "noclk" not in args.dbg:
+        clocks.start()   # no sleep here: a delay on one rank after the barrier would be charged to every rank
     torch.cuda.synchronize()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     kev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
     flat = flow.flat_parameters().detach()
+    probe = torch.zeros(args.steps, 2, dtype=torch.int64, device=dev)
+    import ctypes
+    lib = _lib.load()
+    stream_ptr = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
     ev0.record()
     for i in range(args.steps):
         x_data, x_map = bufs[i % n_buf]
@@ -216,7 +227,9 @@ def main():
         kev[i][0].record()
         loss, reg = net.fused_training_step(x_data, x_map, global_batch=B_global)
         kev[i][1].record()
-        opt.step()
+        if "noopt" not in args.dbg:
+            opt.step()
+        lib.gpflow_clock_probe(ctypes.c_void_p(probe[i].data_ptr()), stream_ptr)   # ~20 us, SM clock right after the step
     ev1.record()
     torch.cuda.synchronize()
     if world > 1:
@@ -228,6 +241,13 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms_total, ms_kernel = float(t[0]), float(t[1])
     clk = clocks.stop() if rank == 0 else None
+    if rank == 0:
+        pr = probe.cpu().double()
+        mhz = sorted((1e3 * pr[:, 0] / pr[:, 1].clamp(min=1)).tolist())
+        clk["nvml_sm_mhz"] = clk.get("sm_mhz")
+        clk["sm_mhz"] = round(mhz[len(mhz) // 2], 1)          # median of the on-device probes, one per timed step
+        clk["sm_min_mhz"] = round(mhz[0], 1)
+        clk["samples"] = len(mhz)
     ms_per_step = ms_total / args.steps
     value = B_global / (ms_per_step * 1e-3)
 
@@ -323,7 +343,8 @@ def main():
         "roofline": roofline, "cpu_baseline": cpu_baseline,
         "loss": float(loss), "reg": float(reg),
     }
-    print(json.dumps(line), flush=True)
+    sys.stdout.flush()
+    os.write(json_fd, (json.dumps(line) + "\n").encode())
     if world > 1:
         dist.destroy_process_group()
 

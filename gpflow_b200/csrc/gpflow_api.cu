@@ -148,6 +148,18 @@ __global__ void __launch_bounds__(256) fma_burn_kernel(long long iters, float* s
   if (s == 123.456f) sink[0] = s;
 }
 
+// ---- SM clock probe: (clock64 ticks, globaltimer ns) over a short spin; MHz = 1e3 * ticks / ns ----
+__global__ void clock_probe_kernel(unsigned long long* out) {
+  unsigned long long c0 = clock64(), t0, t1;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+  while (clock64() - c0 < 40000ull) {
+  }
+  const unsigned long long c1 = clock64();
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+  out[0] = c1 - c0;
+  out[1] = t1 - t0;
+}
+
 }  // namespace
 
 extern "C" {
@@ -257,6 +269,12 @@ int gpflow_fp32_fma_burn(int64_t iters, void* sink, double* host_flops_out, void
   if (cudaGetLastError() != cudaSuccess) return GPFLOW_ERR_CUDA;
   if (host_flops_out) *host_flops_out = 2.0 * 128.0 * (double)iters * (double)grid * (double)block;
   return GPFLOW_OK;
+}
+
+int gpflow_clock_probe(void* out2, void* stream) {
+  if (out2 == nullptr) return GPFLOW_ERR_NULL_POINTER;
+  clock_probe_kernel<<<1, 1, 0, reinterpret_cast<cudaStream_t>(stream)>>>(reinterpret_cast<unsigned long long*>(out2));
+  return cudaGetLastError() == cudaSuccess ? GPFLOW_OK : GPFLOW_ERR_CUDA;
 }
 
 const char* gpflow_error_string(int status) {

@@ -156,6 +156,11 @@ int gpflow_launch_count(const GpFlowDesc* desc, int op);
  * flops enqueued (2 per FFMA) is returned through `host_flops_out` (HOST pointer).  Time it with CUDA events. */
 int gpflow_fp32_fma_burn(int64_t iters, void* sink, double* host_flops_out, void* cuda_stream);
 
+/* SM clock probe for benchmarks: one thread spins ~40k SM cycles and writes {clock64 ticks, globaltimer ns} to the
+ * device uint64[2] `out2`; SM MHz = 1e3 * ticks / ns.  Enqueued between timed steps it samples the clock the GPU is
+ * actually running at under load without the driver round trip of an NVML / nvidia-smi query. */
+int gpflow_clock_probe(void* out2, void* cuda_stream);
+
 const char* gpflow_error_string(int status);
 int gpflow_abi_version(void);
 
