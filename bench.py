@@ -28,6 +28,8 @@ WORKLOADS = {
                        desc="synthetic train_gp_on_gaussian_noise 2D, 2^24-sample global batch"),
     "c3_d10_nb9": dict(d=10, nb=9, hidden=(50, 50, 50), n_steps=15, log2_batch=12, w_std=0.05,
                        desc="dsprites-latent shape d=10 nb=9 H=[50,50,50] (generic kernel)"),
+    "c5_d64_nb63": dict(d=64, nb=63, hidden=(256, 256), n_steps=15, log2_batch=10, w_std=0.02,
+                        desc="synthetic d=64 nb=63 H=[256,256] (generic kernel; SURVEY 8d quotes 2^14 per GPU)"),
 }
 
 

@@ -70,13 +70,14 @@ bool small_match(const GpFlowDesc* d, SmallShape* out) {
   return false;
 }
 
-// sf2 (stream-function kernel v2) covers the fp32 train step / backward of the (2,1,15,15) shape without Euler
-// penalization and without the Lagrangian diagnostic; everything else of that shape stays on the v1 kernel.
+// sf2 (stream-function kernels v2) covers fp32 ops of the (2,1,15,15) shape without Euler penalization: forward
+// (with or without the Lagrangian diagnostic / trajectory), train step and backward (without the Lagrangian);
+// everything else of that shape stays on the v1 kernel.
 bool sf2_match(const GpFlowDesc* d, int op) {
   SmallShape s;
   if (!small_match(d, &s) || d->dtype != GPFLOW_F32) return false;
-  if (op == GPFLOW_OP_FORWARD) return false;
-  if (d->flags & (GPFLOW_FLAG_EULER_PEN | GPFLOW_FLAG_LAGRANGIAN | GPFLOW_FLAG_FORCE_V1)) return false;
+  if (d->flags & (GPFLOW_FLAG_EULER_PEN | GPFLOW_FLAG_FORCE_V1)) return false;
+  if (op != GPFLOW_OP_FORWARD && (d->flags & GPFLOW_FLAG_LAGRANGIAN)) return false;  // diagnostic: forward kernel only
   return d->n_steps <= 1024;
 }
 
@@ -183,7 +184,7 @@ int gpflow_query_workspace(const GpFlowDesc* d, int64_t B, int op, size_t* bytes
   const int64_t np = gpflow_param_count(d);
   SmallShape s;
   if (sf2_match(d, op)) {
-    *bytes = sf2_15_15_workspace(d, B);
+    *bytes = sf2_15_15_workspace(d, B, op);
     return GPFLOW_OK;
   }
   if (small_match(d, &s)) {

@@ -150,7 +150,7 @@ def _prep_zw(zw, desc, cfg, dtype, device):
 
 def flow_forward(cfg: FlowConfig, params: torch.Tensor, x: torch.Tensor, *, wrap=False, reverse=False,
                  training=False, lagrangian=False, euler_coef=None, zw=None, want_logdet=False, want_traj=False,
-                 want_scalars=True, loss_scale: Optional[float] = None, force_generic=False):
+                 want_scalars=True, loss_scale: Optional[float] = None, force_generic=False, force_v1=False):
     """ResNet.forward (raw, cube space) or Network.gp_flow (wrap=True).  Returns dict(y, logdet, traj, scalars)."""
     x = _check_cuda("x", x)
     dtype = x.dtype
@@ -159,7 +159,7 @@ def flow_forward(cfg: FlowConfig, params: torch.Tensor, x: torch.Tensor, *, wrap
     params = _check_cuda("params", params, dtype, (cfg.n_params,))
     desc = make_desc(cfg, dtype, wrap=wrap, reverse=reverse, training=training, lagrangian=lagrangian,
                      euler_coef=euler_coef, loss_scale=(1.0 / max(B, 1)) if loss_scale is None else loss_scale,
-                     force_generic=force_generic)
+                     force_generic=force_generic, force_v1=force_v1)
     zw = _prep_zw(zw, desc, cfg, dtype, x.device)
     y = torch.empty_like(x)
     logdet = torch.empty(B, dtype=dtype, device=x.device) if (want_logdet and wrap) else None

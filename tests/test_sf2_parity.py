@@ -186,3 +186,33 @@ def test_sf2_out_of_band_samples_have_zero_gradient():
     assert torch.isfinite(res["buf"]).all() and torch.isfinite(res["y"]).all()
     assert rel(res["grads"].cpu(), ref["grads"].cpu()) < 5e-6
     assert torch.equal(res["grad_x"][:8].cpu(), torch.zeros(8, 2))
+
+
+@pytest.mark.parametrize("reverse", [False, True])
+@pytest.mark.parametrize("wrap", [True, False])
+def test_sf2_forward_kernel_matches_v1_and_oracle(wrap, reverse):
+    """Forward-only sf2 kernel (ot_map / compute_ot_costs path): y, log|det|, Lagrangian, trajectory, both time
+    directions, against the v1 kernel on a ragged 70 001-sample batch and against the fp64 oracle on its head."""
+    import gpflow_b200 as G
+    B = 70001
+    params, x_data, x_map = _inputs(B, seed=21)
+    flat = O.flatten_params(params).cuda()
+    xin = (x_map if wrap else torch.erf(x_map / np.sqrt(2.0))).cuda()
+    assert "sf2" in G.kernel_variant(_cfg(), op=0, lagrangian=True, wrap=wrap, reverse=reverse)
+    a = G.flow_forward(_cfg(), flat, xin, wrap=wrap, reverse=reverse, lagrangian=True, want_logdet=True, want_traj=True)
+    b = G.flow_forward(_cfg(), flat, xin, wrap=wrap, reverse=reverse, lagrangian=True, want_logdet=True, want_traj=True,
+                       force_v1=True)
+    assert rel(a["y"].cpu(), b["y"].cpu()) < 2e-6
+    assert rel(a["traj"].cpu(), b["traj"].cpu()) < 1e-6
+    assert abs(float(a["scalars"][2]) - float(b["scalars"][2])) < 2e-6 * abs(float(b["scalars"][2]))
+    assert float(a["scalars"][0]) == 0.0 and float(a["scalars"][1]) == 0.0
+    if wrap:
+        scale = float((b["y"].cpu().double() ** 2).sum(1).norm())
+        assert float((a["logdet"].cpu().double() - b["logdet"].cpu().double()).norm()) < 5e-6 * scale
+    n = 2048
+    p64 = [p.double() for p in params]
+    if wrap:
+        y64, _, res = O.gp_flow(p64, x_map[:n].double(), SPEC, reverse=reverse, with_lagrangian=False)
+    else:
+        y64 = O.flow_forward(p64, xin[:n].cpu().double(), SPEC, reverse=reverse, with_lagrangian=False).out
+    assert rel(a["y"][:n].cpu(), y64) < 1e-5
