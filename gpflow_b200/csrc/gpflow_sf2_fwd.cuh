@@ -58,7 +58,9 @@ __global__ void __launch_bounds__(NW * 32, 1) gpflow_sf2_fwd_kernel(const SF2Fwd
   const float c6 = a.dt / 6.0f;
   const float rsq2s = 1.0f / (1.4142135623730951f * a.sigma), sq2s = 1.4142135623730951f * a.sigma;
   const int nsg = want_lagr ? 5 : 4;  // stage 4 = the Lagrangian's extra velocity evaluation at (x_{i+1}, t_i)
-  const int slot = blockIdx.x * NW + warp, nslots = gridDim.x * NW;
+  // warp-major slot numbering: a small batch (tiles < resident warps) spreads over the SMs first, then over the
+  // warps of an SM
+  const int slot = warp * gridDim.x + blockIdx.x, nslots = gridDim.x * NW;
   float lagr = 0.0f;
 
   const long long ntiles = (a.B + 31) / 32;
@@ -150,7 +152,7 @@ int launch_sf2_fwd(const GpFlowDesc* d, const Ptrs<float>& p, int64_t B, void* w
   if (ws == nullptr || ws_bytes < sf2_fwd_workspace<H1, H2>(B)) return GPFLOW_ERR_WORKSPACE;
   if (reinterpret_cast<uintptr_t>(ws) & 15) return GPFLOW_ERR_MISALIGNED;
   const int64_t tiles = (B + 31) / 32;
-  int64_t grid = (tiles + NW - 1) / NW;
+  int64_t grid = tiles;
   if (grid > sm_count) grid = sm_count;
   if (grid < 1) grid = 1;
   SF2FwdArgs a;

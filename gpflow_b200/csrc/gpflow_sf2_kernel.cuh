@@ -76,7 +76,9 @@ __global__ void __launch_bounds__(NW * 32, 1) gpflow_sf2_kernel(const SF2Args a)
   float* const wa = warp_area + (size_t)warp * K::WARP_FL;
   float* const Abuf0 = wa;                         // A(b) = Abuf0 + b * A_FL
   float* const Bbuf0 = wa + 2 * K::A_FL;           // B(b) = Bbuf0 + b * B_FL
-  const int slot = blockIdx.x * NW + warp, nslots = gridDim.x * NW;
+  // warp-major slot numbering: a small batch (tiles < resident warps) spreads over the SMs first, then over the
+  // warps of an SM
+  const int slot = warp * gridDim.x + blockIdx.x, nslots = gridDim.x * NW;
   float* const G = a.g2 + (size_t)slot * K::NACC * 32;
   if (TRAIN) {
     for (int i = 0; i < K::NACC; ++i) G[i * 32 + lane] = 0.0f;
@@ -291,14 +293,16 @@ constexpr int kSF2MaxWarps = 12;
 template <int H1, int H2>
 size_t sf2_workspace(const GpFlowDesc* d, int64_t B) {
   typedef SF2<H1, H2, kSF2MaxWarps> K;
-  const int64_t max_slots = (int64_t)kMaxSMs * kSF2MaxWarps;
-  int64_t slots = (B + 31) / 32;
-  slots = (slots + kSF2MaxWarps - 1) / kSF2MaxWarps * kSF2MaxWarps;
-  if (slots > max_slots) slots = max_slots;
+  // slots = resident warps of the launch (partials / second-level accumulators exist for all of them); only the
+  // first min(slots, tiles) slots ever own a tile (warp-major numbering), so only they need a stash region
+  const int64_t tiles = (B + 31) / 32;
+  const int64_t ctas = tiles < kMaxSMs ? (tiles < 1 ? 1 : tiles) : kMaxSMs;
+  const int64_t slots = ctas * kSF2MaxWarps;
+  const int64_t stash_slots = tiles < slots ? tiles : slots;
   size_t bytes = 640 * 4;  // packed weights (staging for the constant bank)
   bytes += align_up((size_t)slots * (3 + K::NPARAM) * 4, 256);
   bytes += align_up((size_t)slots * K::NACC * 32 * 4, 256);
-  bytes += (size_t)slots * 4 * d->n_steps * K::STASH_BYTES;
+  bytes += (size_t)stash_slots * 4 * d->n_steps * K::STASH_BYTES;
   return bytes;
 }
 
@@ -317,7 +321,7 @@ int launch_sf2_nw(const GpFlowDesc* d, const Ptrs<float>& p, int64_t B, void* ws
   if (ws == nullptr || ws_bytes < need) return GPFLOW_ERR_WORKSPACE;
   if (reinterpret_cast<uintptr_t>(ws) & 255) return GPFLOW_ERR_MISALIGNED;
   const int64_t tiles = (B + 31) / 32;
-  int64_t grid = (tiles + NW - 1) / NW;
+  int64_t grid = tiles;
   if (grid > sm_count) grid = sm_count;
   if (grid < 1) grid = 1;
   const int64_t slots = grid * NW;
