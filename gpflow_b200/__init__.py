@@ -11,6 +11,7 @@ from .res_net import get_gp_flow, ResNet  # noqa: F401
 from .velocity_field import VelocityField  # noqa: F401
 from .vector_field import VectorField  # noqa: F401
 from .network import GPFlowNetwork  # noqa: F401
+from .host_stream import HostBatchStream  # noqa: F401
 
 __all__ = ["FlowConfig", "flow_forward", "flow_backward", "fused_train_step", "kernel_variant", "get_gp_flow",
-           "ResNet", "VelocityField", "VectorField", "GPFlowNetwork"]
+           "ResNet", "VelocityField", "VectorField", "GPFlowNetwork", "HostBatchStream"]
