@@ -216,3 +216,29 @@ def test_sf2_forward_kernel_matches_v1_and_oracle(wrap, reverse):
     else:
         y64 = O.flow_forward(p64, xin[:n].cpu().double(), SPEC, reverse=reverse, with_lagrangian=False).out
     assert rel(a["y"][:n].cpu(), y64) < 1e-5
+
+
+def test_sf2_full_size_2p24_properties():
+    """BASELINE.json C4 at its full size (2^24 samples, one launch) through size-independent properties:
+    (i) the fused [grads | ot] buffer of the full batch equals the SUM of the buffers of its 8 contiguous shards
+        computed with loss_scale = 1/2^24 -- exactly what the 8-GPU all-reduce computes;
+    (ii) y of a strided 2^13-sample subsample equals the fp64 oracle on those samples (samples are independent);
+    (iii) the OT scalar equals the mean over the transported points the kernel wrote."""
+    import gpflow_b200 as G
+    B = 1 << 24
+    params = O.init_params(SPEC, 0.3, 0, torch.float32)
+    flat = O.flatten_params(params).cuda()
+    g = torch.Generator(device="cuda").manual_seed(1234)
+    x_map = torch.randn(B, 2, generator=g, device="cuda").clamp_(-3.0, 3.0)
+    x_data = (1.3 * x_map.flip(-1) * torch.tensor([1.0, 0.6], device="cuda") + torch.tensor([0.4, -0.2], device="cuda"))
+    full = G.fused_train_step(_cfg(), flat, x_data, x_map, want_y=True)
+    acc = torch.zeros_like(full["buf"], dtype=torch.float64)
+    for r in range(8):
+        lo, hi = r * (B // 8), (r + 1) * (B // 8)
+        acc += G.fused_train_step(_cfg(), flat, x_data[lo:hi], x_map[lo:hi], loss_scale=1.0 / B)["buf"].double()
+    assert rel(acc.cpu(), full["buf"].double().cpu()) < 2e-6, rel(acc.cpu(), full["buf"].double().cpu())
+    idx = torch.arange(0, B, B >> 13, device="cuda")
+    r64 = O.train_step([p.double() for p in params], x_data[idx].cpu().double(), x_map[idx].cpu().double(), SPEC)
+    assert rel(full["y"][idx].cpu(), r64["y"]) < 1e-5
+    ot = ((x_data.double() - full["y"].double()) ** 2).sum(1).mean()
+    assert abs(float(full["scalars"][0]) - float(ot)) < 2e-6 * float(ot)
