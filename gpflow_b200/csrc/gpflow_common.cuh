@@ -103,6 +103,7 @@ template <typename T> GPF_DEV T warp_sum(T v) {
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
   return v;
 }
+template <typename T> GPF_DEV Dual<T> warp_sum(Dual<T> a) { return Dual<T>(warp_sum(a.v), warp_sum(a.e)); }
 
 __host__ __device__ constexpr int round_up(int a, int b) { return (a + b - 1) / b * b; }
 __host__ __device__ constexpr int cdiv(int a, int b) { return (a + b - 1) / b; }

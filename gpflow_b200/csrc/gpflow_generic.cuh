@@ -9,12 +9,16 @@
 // original nn.Linear layout (lanes over input units).
 //
 // Same math, same reference call sites as gpflow_small.cuh; scalar type S is T or
-// Dual<T> (Euler penalization by reverse-over-forward, see gpflow_common.cuh).
+// Dual<T> (Euler penalization by reverse-over-forward, see gpflow_common.cuh).  For S = float the hidden-layer
+// contractions run on the tensor cores (3xTF32 mma.sync, gpflow_generic_mma.cuh); the last layer and the closed
+// form A.2 are evaluated in contracted form (3 dot products per kept output row, no Jacobian), see Generic<T>.
 #pragma once
 #include "../../include/gpflow_b200.h"
 #include "gpflow_common.cuh"
 #include <string.h>
 #include "gpflow_small.cuh"  // MODE_*, gpflow_finalize_kernel
+#include "gpflow_generic_mma.cuh"
+#include <type_traits>
 
 namespace gpflow {
 
@@ -28,7 +32,8 @@ struct GDims {
 };
 struct GLayout {         // offsets (elements of the scalar type) inside one warp's scratch
   int h[GMAXL + 1], sp[GMAXL + 1], U[GMAXL + 1], T[GMAXL + 1], hb[GMAXL + 1], Tb[GMAXL + 1];  // hidden li = 1..L
-  int f, J, fb, Jb, x, s, Q, Qb, sb, v, vbar, xbar, SX, SQ;
+  int f, G, D, fb, R;    // last layer in contracted form: f_p, g_p, D_p, cotangent of f, R_n[m]
+  int x, s, Q, Qb, sb, v, vbar, xbar, SX, SQ, CN, SXb;
   int total;
 };
 
@@ -56,9 +61,9 @@ inline GLayout make_glayout(const GDims& g) {
     l.h[li] = take(g.n[li]); l.sp[li] = take(g.n[li]); l.U[li] = take(g.n[li] * g.d); l.T[li] = take(g.n[li] * g.d);
     l.hb[li] = take(g.n[li]); l.Tb[li] = take(g.n[li] * g.d);
   }
-  l.f = take(g.nout); l.J = take(g.nout * g.d); l.fb = take(g.nout); l.Jb = take(g.nout * g.d);
+  l.f = take(g.nout); l.G = take(g.nout); l.D = take(g.nout); l.fb = take(g.nout); l.R = take(g.nb * g.n[g.L]);
   l.x = take(g.d); l.s = take(g.d); l.Q = take(g.d); l.Qb = take(g.d); l.sb = take(g.d); l.v = take(g.d);
-  l.vbar = take(g.d); l.xbar = take(g.d); l.SX = take(g.nb); l.SQ = take(g.nb);
+  l.vbar = take(g.d); l.xbar = take(g.d); l.SX = take(g.nb); l.SQ = take(g.nb); l.CN = take(g.nb); l.SXb = take(g.nb);
   l.total = off;
   return l;
 }
@@ -94,6 +99,24 @@ __global__ void gpflow_transpose_params_kernel(GDims g, const T* __restrict__ p,
   pt[i] = p[i];  // biases
 }
 
+// ---------------------------------------------------------------------------------------------------
+// The last linear layer and the closed form A.2 in CONTRACTED form.  A.2 needs the Jacobian J = W_{L+1} T_L only
+// through two contractions, so J (d x d nb per sample) is never formed:
+//     R_n[m]  = sum_{j>=n} s_j T_L[j][m]                       (suffix sums over the tangent directions)
+//     g_p     = W_{L+1}[p] . R_n      = sum_{j>=n} s_j J_{i,n,j}        p = (i, n), n <= min(i, nb-1)
+//     D_p     = W_{L+1}[p] . T_L[i]   = J_{i,n,i}
+//     Q_i     = sum_{n<=min(i,nb-1)} [ 2 f_p SX_n - 2 FX_n + g_p - SD_n ],      v_i = s_i Q_i
+//     SX_n = sum_{j>=n} x_j,  FX_n = sum_{j>=n} f_{(j,n)} x_j,  SD_n = sum_{j>=n} s_j D_{(j,n)}
+// which is the same sum as velocity_field.py:53-79 (the j = i terms cancel) at 3 dot products per kept output row
+// instead of d + 1: the last layer costs O(3 R H) instead of O(H sum_n (d-n)^2) (13x fewer flops per evaluation at
+// d=64, nb=63, H=256).  Reverse (A.3 + the last layer of A.4), with Qb_i = vbar_i s_i, SQ_n = sum_{i>=n} Qb_i:
+//     fb_p = 2 (Qb_i SX_n - x_i SQ_n)     gb_p = Qb_i     Db_p = -s_i SQ_n
+//     xbar_j = sum_{n<=min(j,nb-1)} [ SXb_n - 2 SQ_n f_{(j,n)} ],   SXb_n = sum_{i>=n} 2 f_{(i,n)} Qb_i
+//     Rb_n = sum_{i>=n} Qb_i W[(i,n)]     CR_n = sum_{n'<=n} Rb_n'
+//     hb_L = sum_p fb_p W[p]              Tb_L[j] = s_j CR_{min(j,nb-1)} + sum_n Db_{(j,n)} W[(j,n)]
+//     sb_j = vbar_j Q_j - sum_n SQ_n D_{(j,n)} + CR_{min(j,nb-1)} . T_L[j];   xbar_j += 2 x_j sb_j
+//     dW[p] += fb_p h_L + Qb_i R_n + Db_p T_L[i];   db[p] += fb_p
+// ---------------------------------------------------------------------------------------------------
 template <typename T>
 struct Generic {
   static constexpr int JC = 8;  // tangent directions per register chunk
@@ -101,7 +124,7 @@ struct Generic {
 
   template <typename S> GPF_DEV static T eps_part(const S& a);
 
-  // ---- forward of one linear layer li (0..L) + activation, lanes over output units ----
+  // ---- forward of one hidden linear layer li (0..L-1) + activation, lanes over output units ----
   // in: li == 0 -> the point x (S[d]) and time t; else hidden li (h, T)
   template <typename S>
   GPF_DEV static void forward_layer(const GArgs<T>& a, S* sc, int li, T t, int lane) {
@@ -110,49 +133,46 @@ struct Generic {
     const int nin = g.n[li], no = g.n[li + 1], d = g.d;
     const T* __restrict__ Wt = a.params_t + g.woff[li];
     const T* __restrict__ bias = a.params + g.boff[li];
-    const bool last = (li == g.L);
     if (li == 0) {
       const S* x = sc + l.x;
       for (int k = lane; k < no; k += 32) {
         S acc = S(bias[k] + Wt[d * no + k] * t);
         for (int j = 0; j < d; ++j) acc = acc + Wt[j * no + k] * x[j];
-        if (last) {
-          sc[l.f + k] = acc;
-          for (int j = 0; j < d; ++j) sc[l.J + j * no + k] = S(Wt[j * no + k]);
-        } else {
-          const S h = act_tanh(acc);
-          sc[l.h[1] + k] = h;
-          const S sp = T(1) - h * h;
-          sc[l.sp[1] + k] = sp;
-          for (int j = 0; j < d; ++j) {
-            sc[l.U[1] + j * no + k] = S(Wt[j * no + k]);
-            sc[l.T[1] + j * no + k] = sp * Wt[j * no + k];
-          }
+        const S h = act_tanh(acc);
+        sc[l.h[1] + k] = h;
+        const S sp = T(1) - h * h;
+        sc[l.sp[1] + k] = sp;
+        for (int j = 0; j < d; ++j) {
+          sc[l.U[1] + j * no + k] = S(Wt[j * no + k]);
+          sc[l.T[1] + j * no + k] = sp * Wt[j * no + k];
         }
       }
       return;
     }
     const S* __restrict__ hin = sc + l.h[li];
     const S* __restrict__ Tin = sc + l.T[li];
-    for (int k = lane; k < no; k += 32) {
-      int n_of_k = 0;
-      if (last) {  // pruning: row (i, n) is only used when n <= i; column j only when j >= n
-        const int i = k / g.nb;
-        n_of_k = k % g.nb;
-        if (n_of_k > i) continue;
+    if constexpr (std::is_same<S, float>::value && GPF_GENERIC_MMA) {
+      // tensor-core form (3xTF32): raw pre-activations / tangents first, activation pass after
+      S* y0 = sc + l.h[li + 1];
+      S* Y = sc + l.U[li + 1];
+      gm_rows_times_w<true>(hin, Tin, nin, d, nin, no, Wt, no, bias, y0, Y, no, lane);
+      for (int k = lane; k < no; k += 32) {
+        const S h = act_tanh(y0[k]);
+        y0[k] = h;
+        const S sp = T(1) - h * h;
+        sc[l.sp[li + 1] + k] = sp;
+        for (int j = 0; j < d; ++j) sc[l.T[li + 1] + j * no + k] = sp * Y[j * no + k];
       }
+      return;
+    }
+    for (int k = lane; k < no; k += 32) {
       S acc = S(bias[k]);
       for (int m = 0; m < nin; ++m) acc = acc + Wt[m * no + k] * hin[m];
-      S sp = S(T(0));
-      if (last) {
-        sc[l.f + k] = acc;
-      } else {
-        const S h = act_tanh(acc);
-        sc[l.h[li + 1] + k] = h;
-        sp = T(1) - h * h;
-        sc[l.sp[li + 1] + k] = sp;
-      }
-      for (int j0 = last ? (n_of_k / JC) * JC : 0; j0 < d; j0 += JC) {
+      const S h = act_tanh(acc);
+      sc[l.h[li + 1] + k] = h;
+      const S sp = T(1) - h * h;
+      sc[l.sp[li + 1] + k] = sp;
+      for (int j0 = 0; j0 < d; j0 += JC) {
         S u[JC];
 #pragma unroll
         for (int q = 0; q < JC; ++q) u[q] = S(T(0));
@@ -165,36 +185,72 @@ struct Generic {
 #pragma unroll
         for (int q = 0; q < JC; ++q)
           if (j0 + q < d) {
-            if (last) sc[l.J + (j0 + q) * no + k] = u[q];
-            else {
-              sc[l.U[li + 1] + (j0 + q) * no + k] = u[q];
-              sc[l.T[li + 1] + (j0 + q) * no + k] = sp * u[q];
-            }
+            sc[l.U[li + 1] + (j0 + q) * no + k] = u[q];
+            sc[l.T[li + 1] + (j0 + q) * no + k] = sp * u[q];
           }
       }
     }
   }
 
-  // ---- A.2 assembly: Q_i, v_i from f, J, x ----
+  // ---- last linear layer + A.2 (contracted form, see above): f, g, D, SX, Q, v from h_L, T_L, x ----
   template <typename S>
-  GPF_DEV static void assemble(const GArgs<T>& a, S* sc, T bnd, int lane) {
+  GPF_DEV static void last_layer_forward(const GArgs<T>& a, S* sc, T bnd, int lane) {
     const GDims& g = a.g;
     const GLayout& l = a.lay;
-    const int d = g.d, nb = g.nb, no = g.nout;
+    const int d = g.d, nb = g.nb, H = g.n[g.L];
+    const T* __restrict__ W = a.params + g.woff[g.L];  // [d nb][H]
+    const T* __restrict__ bias = a.params + g.boff[g.L];
     const S* x = sc + l.x;
+    const S* __restrict__ hL = sc + l.h[g.L];
+    const S* __restrict__ TL = sc + l.T[g.L];
     for (int j = lane; j < d; j += 32) sc[l.s + j] = x[j] * x[j] - bnd;
+    __syncwarp();
+    for (int m = lane; m < H; m += 32) {
+      S acc = S(T(0));
+      for (int j = d - 1; j >= 0; --j) {
+        acc = acc + sc[l.s + j] * TL[j * H + m];
+        if (j < nb) sc[l.R + j * H + m] = acc;
+      }
+    }
+    __syncwarp();
+    for (int i = 0; i < d; ++i) {
+      const int nmax = i < nb - 1 ? i : nb - 1;
+      for (int n = 0; n <= nmax; ++n) {
+        const int p = i * nb + n;
+        S af = S(T(0)), ag = S(T(0)), ad = S(T(0));
+        for (int m = lane; m < H; m += 32) {
+          const T w = W[p * H + m];
+          af = af + w * hL[m];
+          ag = ag + w * sc[l.R + n * H + m];
+          ad = ad + w * TL[i * H + m];
+        }
+        af = warp_sum(af);
+        ag = warp_sum(ag);
+        ad = warp_sum(ad);
+        if (lane == 0) {
+          sc[l.f + p] = af + bias[p];
+          sc[l.G + p] = ag;
+          sc[l.D + p] = ad;
+        }
+      }
+    }
+    __syncwarp();
+    for (int n = lane; n < nb; n += 32) {
+      S sx = S(T(0)), fx = S(T(0)), sd = S(T(0));
+      for (int j = n; j < d; ++j) {
+        sx = sx + x[j];
+        fx = fx + sc[l.f + j * nb + n] * x[j];
+        sd = sd + sc[l.s + j] * sc[l.D + j * nb + n];
+      }
+      sc[l.SX + n] = sx;
+      sc[l.CN + n] = T(-2) * fx - sd;
+    }
     __syncwarp();
     for (int i = lane; i < d; i += 32) {
       S Q = S(T(0));
       const int nmax = i < nb - 1 ? i : nb - 1;
-      for (int n = 0; n <= nmax; ++n) {
-        const S fi = sc[l.f + i * nb + n];
-        for (int j = n; j < d; ++j) {
-          if (j == i) continue;
-          Q = Q + (T(2) * (fi - sc[l.f + j * nb + n])) * x[j] +
-              sc[l.s + j] * (sc[l.J + j * no + i * nb + n] - sc[l.J + j * no + j * nb + n]);
-        }
-      }
+      for (int n = 0; n <= nmax; ++n)
+        Q = Q + (T(2) * sc[l.f + i * nb + n]) * sc[l.SX + n] + sc[l.G + i * nb + n] + sc[l.CN + n];
       sc[l.Q + i] = Q;
       sc[l.v + i] = sc[l.s + i] * Q;
     }
@@ -204,14 +260,14 @@ struct Generic {
   // velocity at the point stored in sc[l.x], result in sc[l.v]; keeps the activations for a following reverse
   template <typename S>
   __device__ __noinline__ static void eval_forward(const GArgs<T>& a, S* sc, T t, T bnd, int lane) {
-    for (int li = 0; li <= a.g.L; ++li) {
+    for (int li = 0; li < a.g.L; ++li) {
       forward_layer<S>(a, sc, li, t, lane);
       __syncwarp();
     }
-    assemble<S>(a, sc, bnd, lane);
+    last_layer_forward<S>(a, sc, bnd, lane);
   }
 
-  // ---- weight-gradient accumulation of linear layer li: gacc[k][m] += eps/real part of
+  // ---- weight-gradient accumulation of hidden linear layer li < L: gacc[k][m] += eps/real part of
   //      ab[k] * in[m] + sum_j Ub[j][k] * Tin[j][m];  lanes over m, KT rows per tile ----
   template <typename S>
   GPF_DEV static void grad_layer(const GArgs<T>& a, const S* sc, T* gacc, int li, T t, const S* ab, const S* Ub, int lane) {
@@ -220,7 +276,6 @@ struct Generic {
     const int nin = g.n[li], no = g.n[li + 1], d = g.d;
     T* __restrict__ gw = gacc + g.woff[li];
     T* __restrict__ gb = gacc + g.boff[li];
-    const bool last = (li == g.L);
     for (int k = lane; k < no; k += 32) gb[k] += eps_part<S>(ab[k]);
     if (li == 0) {
       // W0[k][j] += ab[k] x_j + Ub[j][k];  W0[k][d] += ab[k] t      (lanes over k; rows are short)
@@ -234,23 +289,17 @@ struct Generic {
     }
     const S* __restrict__ hin = sc + l.h[li];
     const S* __restrict__ Tin = sc + l.T[li];
+    if constexpr (std::is_same<S, float>::value && GPF_GENERIC_MMA) {
+      gm_weight_grad(ab, Ub, no, hin, Tin, nin, d, no, nin, gw, lane);
+      return;
+    }
     for (int k0 = 0; k0 < no; k0 += KT) {
-      int jmin = 0;
-      if (last) {  // rows (i, n) with n > i carry zero adjoints; columns j < n are pruned
-        bool any = false;
-        jmin = d;
-        for (int q = 0; q < KT && k0 + q < no; ++q) {
-          const int i = (k0 + q) / g.nb, n = (k0 + q) % g.nb;
-          if (n <= i) { any = true; jmin = n < jmin ? n : jmin; }
-        }
-        if (!any) continue;
-      }
       for (int m = lane; m < nin; m += 32) {
         S acc[KT];
         const S hm = hin[m];
 #pragma unroll
         for (int q = 0; q < KT; ++q) acc[q] = (k0 + q < no) ? ab[k0 + q] * hm : S(T(0));
-        for (int j = jmin; j < d; ++j) {
+        for (int j = 0; j < d; ++j) {
           const S tv = Tin[j * nin + m];
 #pragma unroll
           for (int q = 0; q < KT; ++q)
@@ -263,35 +312,30 @@ struct Generic {
     }
   }
 
-  // ---- reverse through linear layer li >= 1: (ab[k], Ub[j][k]) -> hb[m], Tb[j][m] of hidden li; lanes over m ----
+  // ---- reverse through hidden linear layer 1 <= li < L: (ab[k], Ub[j][k]) -> hb[m], Tb[j][m] of hidden li ----
   template <typename S>
   GPF_DEV static void backprop_layer(const GArgs<T>& a, S* sc, int li, const S* ab, const S* Ub, int lane) {
     const GDims& g = a.g;
     const GLayout& l = a.lay;
     const int nin = g.n[li], no = g.n[li + 1], d = g.d;
     const T* __restrict__ W = a.params + g.woff[li];
-    const bool last = (li == g.L);
+    if constexpr (std::is_same<S, float>::value && GPF_GENERIC_MMA) {
+      gm_rows_times_w<true>(ab, Ub, no, d, no, nin, W, nin, nullptr, sc + l.hb[li], sc + l.Tb[li], nin, lane);
+      return;
+    }
     for (int m = lane; m < nin; m += 32) {
       S acc = S(T(0));
-      for (int k = 0; k < no; ++k) {
-        if (last && (k % g.nb) > (k / g.nb)) continue;
-        acc = acc + W[k * nin + m] * ab[k];
-      }
+      for (int k = 0; k < no; ++k) acc = acc + W[k * nin + m] * ab[k];
       sc[l.hb[li] + m] = acc;
       for (int j0 = 0; j0 < d; j0 += JC) {
         S u[JC];
 #pragma unroll
         for (int q = 0; q < JC; ++q) u[q] = S(T(0));
         for (int k = 0; k < no; ++k) {
-          int n_of_k = 0;
-          if (last) {
-            n_of_k = k % g.nb;
-            if (n_of_k > (k / g.nb)) continue;
-          }
           const T wv = W[k * nin + m];
 #pragma unroll
           for (int q = 0; q < JC; ++q)
-            if (j0 + q < d && j0 + q >= n_of_k) u[q] = u[q] + wv * Ub[(j0 + q) * no + k];
+            if (j0 + q < d) u[q] = u[q] + wv * Ub[(j0 + q) * no + k];
         }
 #pragma unroll
         for (int q = 0; q < JC; ++q)
@@ -300,67 +344,120 @@ struct Generic {
     }
   }
 
+  // ---- reverse of last_layer_forward: cotangent sc[l.vbar] -> hb_L, Tb_L, first part of xbar, dW_{L+1}, db_{L+1} ----
+  template <typename S>
+  GPF_DEV static void last_layer_reverse(const GArgs<T>& a, S* sc, T* gacc, int lane) {
+    const GDims& g = a.g;
+    const GLayout& l = a.lay;
+    const int d = g.d, nb = g.nb, no = g.nout, L = g.L, H = g.n[L];
+    const T* __restrict__ W = a.params + g.woff[L];
+    T* __restrict__ gw = gacc + g.woff[L];
+    T* __restrict__ gb = gacc + g.boff[L];
+    const S* x = sc + l.x;
+    const S* __restrict__ hL = sc + l.h[L];
+    const S* __restrict__ TL = sc + l.T[L];
+    for (int j = lane; j < d; j += 32) {
+      sc[l.Qb + j] = sc[l.vbar + j] * sc[l.s + j];
+      sc[l.sb + j] = sc[l.vbar + j] * sc[l.Q + j];
+    }
+    __syncwarp();
+    for (int n = lane; n < nb; n += 32) {
+      S sq = S(T(0)), sxb = S(T(0));
+      for (int i = n; i < d; ++i) {
+        const S qi = sc[l.Qb + i];
+        sq = sq + qi;
+        sxb = sxb + (T(2) * sc[l.f + i * nb + n]) * qi;
+      }
+      sc[l.SQ + n] = sq;
+      sc[l.SXb + n] = sxb;
+    }
+    __syncwarp();
+    for (int p = lane; p < no; p += 32) {
+      const int i = p / nb, n = p % nb;
+      S fbp = S(T(0));
+      if (n <= i) {
+        fbp = T(2) * (sc[l.Qb + i] * sc[l.SX + n] - x[i] * sc[l.SQ + n]);
+        gb[p] += eps_part<S>(fbp);
+      }
+      sc[l.fb + p] = fbp;
+    }
+    for (int j = lane; j < d; j += 32) {
+      S xb = S(T(0)), sbj = sc[l.sb + j];
+      const int nmax = j < nb - 1 ? j : nb - 1;
+      for (int n = 0; n <= nmax; ++n) {
+        const S sq = sc[l.SQ + n];
+        xb = xb + sc[l.SXb + n] - (T(2) * sq) * sc[l.f + j * nb + n];
+        sbj = sbj - sq * sc[l.D + j * nb + n];
+      }
+      sc[l.xbar + j] = xb;
+      sc[l.sb + j] = sbj;
+    }
+    __syncwarp();
+    for (int m0 = 0; m0 < H; m0 += 32) {
+      const int m = m0 + lane;
+      const bool act = m < H;
+      S hbm = S(T(0));
+      const S hm = act ? hL[m] : S(T(0));
+      // pass A: rows in storage order; hb_L, the D part of Tb_L, dW
+      for (int i = 0; i < d; ++i) {
+        const int nmax = i < nb - 1 ? i : nb - 1;
+        const S Ti = act ? TL[i * H + m] : S(T(0));
+        const S qbi = sc[l.Qb + i];
+        const S nsi = -sc[l.s + i];
+        S Ei = S(T(0));
+        if (act)
+          for (int n = 0; n <= nmax; ++n) {
+            const int p = i * nb + n;
+            const T w = W[p * H + m];
+            const S fbp = sc[l.fb + p];
+            const S dbp = nsi * sc[l.SQ + n];
+            hbm = hbm + fbp * w;
+            Ei = Ei + dbp * w;
+            gw[p * H + m] += eps_part<S>(fbp * hm + qbi * sc[l.R + n * H + m] + dbp * Ti);
+          }
+        if (act) sc[l.Tb[L] + i * H + m] = Ei;
+      }
+      if (act) sc[l.hb[L] + m] = hbm;
+      // pass B: blocks n in order; Rb_n, its running sum CR_n, the R part of Tb_L and of sb
+      S CR = S(T(0));
+      for (int n = 0; n < nb; ++n) {
+        S rb = S(T(0));
+        if (act)
+          for (int i = n; i < d; ++i) rb = rb + sc[l.Qb + i] * W[(i * nb + n) * H + m];
+        CR = CR + rb;
+        const int jhi = (n == nb - 1) ? d - 1 : n;
+        for (int j = n; j <= jhi; ++j) {
+          S part = S(T(0));
+          if (act) {
+            part = CR * TL[j * H + m];
+            sc[l.Tb[L] + j * H + m] = sc[l.Tb[L] + j * H + m] + sc[l.s + j] * CR;
+          }
+          part = warp_sum(part);
+          if (lane == 0) sc[l.sb + j] = sc[l.sb + j] + part;
+        }
+      }
+    }
+    __syncwarp();
+    for (int j = lane; j < d; j += 32) sc[l.xbar + j] = sc[l.xbar + j] + (T(2) * x[j]) * sc[l.sb + j];
+    __syncwarp();
+  }
+
   // ---- full reverse sweep of one velocity evaluation (A.3 + A.4).  Needs the activations of eval_forward at
   //      sc[l.x]; cotangent in sc[l.vbar]; result J_v^T vbar in sc[l.xbar]; parameter gradients into gacc ----
   template <typename S>
   __device__ __noinline__ static void eval_reverse(const GArgs<T>& a, S* sc, T* gacc, T t, int lane) {
     const GDims& g = a.g;
     const GLayout& l = a.lay;
-    const int d = g.d, nb = g.nb, no = g.nout;
-    const S* x = sc + l.x;
-    for (int j = lane; j < d; j += 32) {
-      sc[l.Qb + j] = sc[l.vbar + j] * sc[l.s + j];
-      sc[l.sb + j] = sc[l.vbar + j] * sc[l.Q + j];
-    }
-    __syncwarp();
-    // suffix sums SX_n = sum_{j>=n} x_j, SQ_n = sum_{i>=n} Qb_i
-    for (int n = lane; n < nb; n += 32) {
-      S sx = S(T(0)), sq = S(T(0));
-      for (int j = n; j < d; ++j) { sx = sx + x[j]; sq = sq + sc[l.Qb + j]; }
-      sc[l.SX + n] = sx;
-      sc[l.SQ + n] = sq;
-    }
-    __syncwarp();
-    // fb[(a,n)] = 2 (Qb_a SX_n - x_a SQ_n);  Jb[(a,n)][j] = s_j Qb_a (j != a, j >= n),  Jb[(a,n)][a] = -s_a (SQ_n - Qb_a)
-    for (int p = lane; p < no; p += 32) {
-      const int ia = p / nb, n = p % nb;
-      if (n > ia) {
-        sc[l.fb + p] = S(T(0));
-        for (int j = 0; j < d; ++j) sc[l.Jb + j * no + p] = S(T(0));
-        continue;
-      }
-      const S qa = sc[l.Qb + ia];
-      sc[l.fb + p] = T(2) * (qa * sc[l.SX + n] - x[ia] * sc[l.SQ + n]);
-      for (int j = 0; j < d; ++j) {
-        S v = S(T(0));
-        if (j >= n) v = (j == ia) ? -(sc[l.s + ia] * (sc[l.SQ + n] - qa)) : sc[l.s + j] * qa;
-        sc[l.Jb + j * no + p] = v;
-      }
-    }
-    // direct terms into xbar / sb (owner j)
-    for (int j = lane; j < d; j += 32) {
-      S xb = S(T(0)), sbj = sc[l.sb + j];
-      const int nmax = j < nb - 1 ? j : nb - 1;
-      for (int n = 0; n <= nmax; ++n) {
-        const S fj = sc[l.f + j * nb + n];
-        const S Jjj = sc[l.J + j * no + j * nb + n];
-        for (int i = n; i < d; ++i) {
-          if (i == j) continue;
-          const S qi = sc[l.Qb + i];
-          xb = xb + (T(2) * (sc[l.f + i * nb + n] - fj)) * qi;
-          sbj = sbj + (sc[l.J + j * no + i * nb + n] - Jjj) * qi;
-        }
-      }
-      sc[l.xbar + j] = xb + (T(2) * x[j]) * sbj;
-    }
-    __syncwarp();
-    // ---- layers, last to first
-    const S* ab = sc + l.fb;
-    const S* Ub = sc + l.Jb;
+    const int d = g.d;
+    last_layer_reverse<S>(a, sc, gacc, lane);
+    const S* ab = sc + l.hb[g.L];
+    const S* Ub = sc + l.Tb[g.L];
     for (int li = g.L; li >= 1; --li) {
-      grad_layer<S>(a, sc, gacc, li, t, ab, Ub, lane);
-      backprop_layer<S>(a, sc, li, ab, Ub, lane);
-      __syncwarp();
+      if (li < g.L) {
+        grad_layer<S>(a, sc, gacc, li, t, ab, Ub, lane);
+        backprop_layer<S>(a, sc, li, ab, Ub, lane);
+        __syncwarp();
+      }
       // through the activation of hidden li (in place: hb -> ab, Tb -> Ub)
       const int H = g.n[li];
       for (int k = lane; k < H; k += 32) {

@@ -1,0 +1,134 @@
+// gpflow_b200 -- tensor-core contractions of the generic (any d, nb, depth, width) fp32 kernels.
+//
+// The three contractions of one linear layer, per sample (one warp = one sample, rows = value row + d tangent rows):
+//   forward   Y[r][k]  = sum_m X[r][m]  W[k][m]        vector_field.py:75-128   (A.1)
+//   backprop  Xb[r][m] = sum_k Yb[r][k] W[k][m]                                  (A.4)
+//   gradient  dW[k][m] += sum_r Yb[r][k] X[r][m]                                 (A.4)
+// are issued as mma.sync.m16n8k8 TF32 tiles with the 3xTF32 error-compensated split (x = hi + lo, hi = tf32(x),
+// lo = tf32(x - hi); x*y ~= lo*hi' + hi*lo' + hi*hi', fp32 accumulation): single-pass TF32 (2^-11) would break the
+// 1e-5 parity bar, the dropped lo*lo' term is 2^-22 relative.  Measured on B200 (tools/mma_tf32_bench.cu): 279 TFLOP/s
+// for mma.sync tf32 = 3.9x the FP32 FFMA roof, i.e. 1.3x FFMA-equivalent after the 3x split, with ~25x fewer issued
+// instructions than the scalar loops these routines replace.  Operands are read straight from the warp's scratch
+// rows / the nn.Linear weights with bounds predicates (zero padding of ragged tiles), so no layout change is needed.
+// Fragment layouts (PTX ISA, m16n8k8 .tf32): g = lane >> 2, t = lane & 3;
+//   A (16x8, row): a0 (g, t) a1 (g+8, t) a2 (g, t+4) a3 (g+8, t+4);  B (8x8, col): b0 (t, g) b1 (t+4, g);
+//   C (16x8): c0 (g, 2t) c1 (g, 2t+1) c2 (g+8, 2t) c3 (g+8, 2t+1).
+#pragma once
+#include "gpflow_common.cuh"
+
+#ifndef GPF_GENERIC_MMA
+#define GPF_GENERIC_MMA 1  // 0: scalar FFMA contractions everywhere (the fp64 / Dual path)
+#endif
+
+namespace gpflow {
+
+GPF_DEV void tf32_split(float x, uint32_t& hi, uint32_t& lo) {
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(hi) : "f"(x));
+  const float r = x - __uint_as_float(hi);
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(lo) : "f"(r));
+}
+GPF_DEV void mma_tf32(float (&c)[4], const uint32_t (&a)[4], const uint32_t (&b)[2]) {
+  asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+               : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+               : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b[0]), "r"(b[1]));
+}
+// c += a * b with the 3xTF32 split, small terms first
+GPF_DEV void mma_3xtf32(float (&c)[4], const uint32_t (&ah)[4], const uint32_t (&al)[4], const uint32_t (&bh)[2],
+                        const uint32_t (&bl)[2]) {
+  mma_tf32(c, al, bh);
+  mma_tf32(c, ah, bl);
+  mma_tf32(c, ah, bh);
+}
+
+// row r of the (1 + d)-row operand: r == 0 -> value vector v0, 1 <= r <= d -> tangent rows V[(r-1) * ld ..], else zero
+GPF_DEV float row_elem(const float* __restrict__ v0, const float* __restrict__ V, int ld, int d, int r, int col, int ncol) {
+  if (col >= ncol || r > d) return 0.0f;
+  return r == 0 ? v0[col] : V[(r - 1) * ld + col];
+}
+
+constexpr int GM_NT = 8;  // n-tiles per accumulator block (64 output columns)
+
+// Y[r][n] = sum_k X[r][k] * Bm(k, n), r < 1 + d, n < N, k < K.  TRANS_B = false: Bm(k, n) = W[n * ldw + k] (forward:
+// W is [out][in], n = out, k = in); TRANS_B = true: Bm(k, n) = W[k * ldw + n] (backprop: n = in, k = out).
+// Results: row 0 -> y0[n] (+ bias0[n] if bias0), rows 1..d -> Y[(r-1) * ldy + n].  One warp; ends with __syncwarp().
+template <bool TRANS_B>
+GPF_DEV void gm_rows_times_w(const float* __restrict__ x0, const float* __restrict__ X, int ldx, int d, int K, int N,
+                             const float* __restrict__ W, int ldw, const float* __restrict__ bias0,
+                             float* __restrict__ y0, float* __restrict__ Y, int ldy, int lane) {
+  const int g = lane >> 2, t = lane & 3;
+  const int R = d + 1;
+  for (int r0 = 0; r0 < R; r0 += 16) {
+    const int rl = r0 + g, rh = r0 + g + 8;
+    for (int nb0 = 0; nb0 < N; nb0 += 8 * GM_NT) {
+      float c[GM_NT][4];
+#pragma unroll
+      for (int i = 0; i < GM_NT; ++i) c[i][0] = c[i][1] = c[i][2] = c[i][3] = 0.0f;
+      for (int k0 = 0; k0 < K; k0 += 8) {
+        uint32_t ah[4], al[4];
+        tf32_split(row_elem(x0, X, ldx, d, rl, k0 + t, K), ah[0], al[0]);
+        tf32_split(row_elem(x0, X, ldx, d, rh, k0 + t, K), ah[1], al[1]);
+        tf32_split(row_elem(x0, X, ldx, d, rl, k0 + t + 4, K), ah[2], al[2]);
+        tf32_split(row_elem(x0, X, ldx, d, rh, k0 + t + 4, K), ah[3], al[3]);
+#pragma unroll
+        for (int i = 0; i < GM_NT; ++i) {
+          const int n = nb0 + 8 * i + g;
+          if (nb0 + 8 * i < N) {  // warp-uniform
+            float w0 = 0.0f, w1 = 0.0f;
+            if (n < N) {
+              if (k0 + t < K) w0 = TRANS_B ? W[(k0 + t) * ldw + n] : W[n * ldw + k0 + t];
+              if (k0 + t + 4 < K) w1 = TRANS_B ? W[(k0 + t + 4) * ldw + n] : W[n * ldw + k0 + t + 4];
+            }
+            uint32_t bh[2], bl[2];
+            tf32_split(w0, bh[0], bl[0]);
+            tf32_split(w1, bh[1], bl[1]);
+            mma_3xtf32(c[i], ah, al, bh, bl);
+          }
+        }
+      }
+#pragma unroll
+      for (int i = 0; i < GM_NT; ++i) {
+        const int n = nb0 + 8 * i + 2 * t;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const int r = (q & 2) ? rh : rl, nn = n + (q & 1);
+          if (nn < N && r <= d) {
+            if (r == 0) y0[nn] = c[i][q] + (bias0 != nullptr ? bias0[nn] : 0.0f);
+            else Y[(r - 1) * ldy + nn] = c[i][q];
+          }
+        }
+      }
+    }
+  }
+  __syncwarp();
+}
+
+// gw[k * N + m] += sum_{r <= d} Yb[r][k] * X[r][m], k < M (outputs), m < N (inputs); rows as in row_elem.
+GPF_DEV void gm_weight_grad(const float* __restrict__ yb0, const float* __restrict__ Yb, int ldyb, const float* __restrict__ x0,
+                            const float* __restrict__ X, int ldx, int d, int M, int N, float* __restrict__ gw, int lane) {
+  const int g = lane >> 2, t = lane & 3;
+  const int R = d + 1;
+  for (int k0 = 0; k0 < M; k0 += 16) {
+    for (int m0 = 0; m0 < N; m0 += 8) {
+      float c[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+      for (int r0 = 0; r0 < R; r0 += 8) {
+        uint32_t ah[4], al[4], bh[2], bl[2];
+        // A[k][r] = Yb[r][k]
+        tf32_split(row_elem(yb0, Yb, ldyb, d, r0 + t, k0 + g, M), ah[0], al[0]);
+        tf32_split(row_elem(yb0, Yb, ldyb, d, r0 + t, k0 + g + 8, M), ah[1], al[1]);
+        tf32_split(row_elem(yb0, Yb, ldyb, d, r0 + t + 4, k0 + g, M), ah[2], al[2]);
+        tf32_split(row_elem(yb0, Yb, ldyb, d, r0 + t + 4, k0 + g + 8, M), ah[3], al[3]);
+        // B[r][m] = X[r][m]
+        tf32_split(row_elem(x0, X, ldx, d, r0 + t, m0 + g, N), bh[0], bl[0]);
+        tf32_split(row_elem(x0, X, ldx, d, r0 + t + 4, m0 + g, N), bh[1], bl[1]);
+        mma_3xtf32(c, ah, al, bh, bl);
+      }
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const int k = k0 + g + ((q & 2) ? 8 : 0), m = m0 + 2 * t + (q & 1);
+        if (k < M && m < N) gw[k * N + m] += c[q];
+      }
+    }
+  }
+}
+
+}  // namespace gpflow
