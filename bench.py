@@ -26,9 +26,9 @@ WORKLOADS = {
     # name: (d, nb, hidden, n_steps, log2 global batch, weight std)
     "c4_2d_2p24": dict(d=2, nb=1, hidden=(15, 15), n_steps=15, log2_batch=24, w_std=0.3,
                        desc="synthetic train_gp_on_gaussian_noise 2D, 2^24-sample global batch"),
-    "c3_d10_nb9": dict(d=10, nb=9, hidden=(50, 50, 50), n_steps=15, log2_batch=12, w_std=0.05,
+    "c3_d10_nb9": dict(d=10, nb=9, hidden=(50, 50, 50), n_steps=15, log2_batch=14, w_std=0.05,
                        desc="dsprites-latent shape d=10 nb=9 H=[50,50,50] (generic kernel)"),
-    "c5_d64_nb63": dict(d=64, nb=63, hidden=(256, 256), n_steps=15, log2_batch=10, w_std=0.02,
+    "c5_d64_nb63": dict(d=64, nb=63, hidden=(256, 256), n_steps=15, log2_batch=12, w_std=0.02,
                         desc="synthetic d=64 nb=63 H=[256,256] (generic kernel; SURVEY 8d quotes 2^14 per GPU)"),
 }
 

@@ -104,6 +104,26 @@ template <typename T> GPF_DEV T warp_sum(T v) {
   return v;
 }
 template <typename T> GPF_DEV Dual<T> warp_sum(Dual<T> a) { return Dual<T>(warp_sum(a.v), warp_sum(a.e)); }
+template <typename T> GPF_DEV T shfl_xor_s(T v, int o) { return __shfl_xor_sync(0xffffffffu, v, o); }
+template <typename T> GPF_DEV Dual<T> shfl_xor_s(Dual<T> a, int o) {
+  return Dual<T>(__shfl_xor_sync(0xffffffffu, a.v, o), __shfl_xor_sync(0xffffffffu, a.e, o));
+}
+// Four warp sums in 6 shuffles instead of 20: the first two butterfly stages exchange half of the values, so that
+// lane L ends with the warp total of v[2 * ((L >> 4) & 1) + ((L >> 3) & 1)].
+template <typename S> GPF_DEV S warp_sum4(const S (&v)[4], int lane) {
+  const bool h16 = (lane & 16) != 0, h8 = (lane & 8) != 0;
+  S k0 = h16 ? v[2] : v[0], k1 = h16 ? v[3] : v[1];
+  const S s0 = h16 ? v[0] : v[2], s1 = h16 ? v[1] : v[3];
+  k0 = k0 + shfl_xor_s(s0, 16);
+  k1 = k1 + shfl_xor_s(s1, 16);
+  S k = h8 ? k1 : k0;
+  const S s = h8 ? k0 : k1;
+  k = k + shfl_xor_s(s, 8);
+  k = k + shfl_xor_s(k, 4);
+  k = k + shfl_xor_s(k, 2);
+  k = k + shfl_xor_s(k, 1);
+  return k;
+}
 
 __host__ __device__ constexpr int round_up(int a, int b) { return (a + b - 1) / b * b; }
 __host__ __device__ constexpr int cdiv(int a, int b) { return (a + b - 1) / b; }

@@ -16,6 +16,7 @@
 #include "../../include/gpflow_b200.h"
 #include "gpflow_common.cuh"
 #include <string.h>
+#include <stdlib.h>
 #include "gpflow_small.cuh"  // MODE_*, gpflow_finalize_kernel
 #include "gpflow_generic_mma.cuh"
 #include <type_traits>
@@ -23,6 +24,8 @@
 namespace gpflow {
 
 constexpr int GMAXL = GPFLOW_MAX_HIDDEN + 1;  // linear layers
+constexpr int kGenericMaxThreads = 512;   // register allocation bounded for 16 warps per SM (128 registers per thread)
+constexpr int kGenericSmemBudget = 226 * 1024;
 
 struct GDims {
   int d, nb, L, nout, P;
@@ -77,8 +80,10 @@ struct GArgs {
   const T* x_in; const T* x_data; const T* grad_y; const T* reg_cotangent; const T* zw;
   T* y_out; T* logdet_out; T* traj_out; T* grad_x_out; T* v_out;
   T* partials;           // [nwarps][3 + P]
-  char* scratch;         // per-warp scratch, stride scratch_stride bytes
+  char* scratch;         // per-warp scratch, stride scratch_stride bytes (global mode)
   size_t scratch_stride;
+  int on_chip;           // 1: the parameters and every warp's scratch live in the CTA's shared memory
+  unsigned smem_scratch_off;  // byte offset of warp 0's scratch inside dynamic shared memory (on-chip mode)
   long long B;
   int n_steps; int npart; unsigned flags;
   T dt, t0, dt_constraint, sigma, euler_coef, loss_scale, t_eval;
@@ -97,6 +102,13 @@ __global__ void gpflow_transpose_params_kernel(GDims g, const T* __restrict__ p,
     }
   }
   pt[i] = p[i];  // biases
+}
+
+// flat parameters as the kernels read them: the CTA's shared-memory copy in on-chip mode, else the caller's buffer
+template <typename T>
+GPF_DEV const T* gparams(const GArgs<T>& a) {
+  extern __shared__ __align__(16) unsigned char g_dyn_smem[];
+  return a.on_chip ? reinterpret_cast<const T*>(g_dyn_smem) : a.params;
 }
 
 // ---------------------------------------------------------------------------------------------------
@@ -121,6 +133,7 @@ template <typename T>
 struct Generic {
   static constexpr int JC = 8;  // tangent directions per register chunk
   static constexpr int KT = 4;  // output rows per weight-gradient tile
+  static constexpr int NU = 4;  // last-layer rows per pass (independent loads in flight)
 
   template <typename S> GPF_DEV static T eps_part(const S& a);
 
@@ -132,7 +145,7 @@ struct Generic {
     const GLayout& l = a.lay;
     const int nin = g.n[li], no = g.n[li + 1], d = g.d;
     const T* __restrict__ Wt = a.params_t + g.woff[li];
-    const T* __restrict__ bias = a.params + g.boff[li];
+    const T* __restrict__ bias = gparams(a) + g.boff[li];
     if (li == 0) {
       const S* x = sc + l.x;
       for (int k = lane; k < no; k += 32) {
@@ -155,7 +168,8 @@ struct Generic {
       // tensor-core form (3xTF32): raw pre-activations / tangents first, activation pass after
       S* y0 = sc + l.h[li + 1];
       S* Y = sc + l.U[li + 1];
-      gm_rows_times_w<true>(hin, Tin, nin, d, nin, no, Wt, no, bias, y0, Y, no, lane);
+      if (a.on_chip) gm_rows_times_w<false>(hin, Tin, nin, d, nin, no, gparams(a) + g.woff[li], nin, bias, y0, Y, no, lane);
+      else gm_rows_times_w<true>(hin, Tin, nin, d, nin, no, Wt, no, bias, y0, Y, no, lane);
       for (int k = lane; k < no; k += 32) {
         const S h = act_tanh(y0[k]);
         y0[k] = h;
@@ -198,8 +212,8 @@ struct Generic {
     const GDims& g = a.g;
     const GLayout& l = a.lay;
     const int d = g.d, nb = g.nb, H = g.n[g.L];
-    const T* __restrict__ W = a.params + g.woff[g.L];  // [d nb][H]
-    const T* __restrict__ bias = a.params + g.boff[g.L];
+    const T* __restrict__ W = gparams(a) + g.woff[g.L];  // [d nb][H]
+    const T* __restrict__ bias = gparams(a) + g.boff[g.L];
     const S* x = sc + l.x;
     const S* __restrict__ hL = sc + l.h[g.L];
     const S* __restrict__ TL = sc + l.T[g.L];
@@ -213,24 +227,38 @@ struct Generic {
       }
     }
     __syncwarp();
+    // three dot products per kept row, NU rows per pass so that 2 NU + 2 independent loads are in flight per lane
     for (int i = 0; i < d; ++i) {
       const int nmax = i < nb - 1 ? i : nb - 1;
-      for (int n = 0; n <= nmax; ++n) {
-        const int p = i * nb + n;
-        S af = S(T(0)), ag = S(T(0)), ad = S(T(0));
+      for (int n0 = 0; n0 <= nmax; n0 += NU) {
+        S af[NU], ag[NU], ad[NU];
+#pragma unroll
+        for (int q = 0; q < NU; ++q) af[q] = ag[q] = ad[q] = S(T(0));
         for (int m = lane; m < H; m += 32) {
-          const T w = W[p * H + m];
-          af = af + w * hL[m];
-          ag = ag + w * sc[l.R + n * H + m];
-          ad = ad + w * TL[i * H + m];
+          T w[NU];
+          S r[NU];
+#pragma unroll
+          for (int q = 0; q < NU; ++q) {
+            const int nq = n0 + q <= nmax ? n0 + q : nmax;  // clamped rows are discarded below
+            w[q] = W[(i * nb + nq) * H + m];
+            r[q] = sc[l.R + nq * H + m];
+          }
+          const S hm = hL[m], ti = TL[i * H + m];
+#pragma unroll
+          for (int q = 0; q < NU; ++q) {
+            af[q] = af[q] + w[q] * hm;
+            ag[q] = ag[q] + w[q] * r[q];
+            ad[q] = ad[q] + w[q] * ti;
+          }
         }
-        af = warp_sum(af);
-        ag = warp_sum(ag);
-        ad = warp_sum(ad);
-        if (lane == 0) {
-          sc[l.f + p] = af + bias[p];
-          sc[l.G + p] = ag;
-          sc[l.D + p] = ad;
+        static_assert(NU == 4, "warp_sum4");
+        const S rf = warp_sum4(af, lane), rg = warp_sum4(ag, lane), rd = warp_sum4(ad, lane);
+        const int q = 2 * ((lane >> 4) & 1) + ((lane >> 3) & 1);  // the row whose totals this lane holds
+        if ((lane & 7) == 0 && n0 + q <= nmax) {
+          const int p = i * nb + n0 + q;
+          sc[l.f + p] = rf + bias[p];
+          sc[l.G + p] = rg;
+          sc[l.D + p] = rd;
         }
       }
     }
@@ -318,7 +346,7 @@ struct Generic {
     const GDims& g = a.g;
     const GLayout& l = a.lay;
     const int nin = g.n[li], no = g.n[li + 1], d = g.d;
-    const T* __restrict__ W = a.params + g.woff[li];
+    const T* __restrict__ W = gparams(a) + g.woff[li];
     if constexpr (std::is_same<S, float>::value && GPF_GENERIC_MMA) {
       gm_rows_times_w<true>(ab, Ub, no, d, no, nin, W, nin, nullptr, sc + l.hb[li], sc + l.Tb[li], nin, lane);
       return;
@@ -350,7 +378,7 @@ struct Generic {
     const GDims& g = a.g;
     const GLayout& l = a.lay;
     const int d = g.d, nb = g.nb, no = g.nout, L = g.L, H = g.n[L];
-    const T* __restrict__ W = a.params + g.woff[L];
+    const T* __restrict__ W = gparams(a) + g.woff[L];
     T* __restrict__ gw = gacc + g.woff[L];
     T* __restrict__ gb = gacc + g.boff[L];
     const S* x = sc + l.x;
@@ -406,14 +434,26 @@ struct Generic {
         const S nsi = -sc[l.s + i];
         S Ei = S(T(0));
         if (act)
-          for (int n = 0; n <= nmax; ++n) {
-            const int p = i * nb + n;
-            const T w = W[p * H + m];
-            const S fbp = sc[l.fb + p];
-            const S dbp = nsi * sc[l.SQ + n];
-            hbm = hbm + fbp * w;
-            Ei = Ei + dbp * w;
-            gw[p * H + m] += eps_part<S>(fbp * hm + qbi * sc[l.R + n * H + m] + dbp * Ti);
+          for (int n0 = 0; n0 <= nmax; n0 += NU) {
+            T w[NU], go[NU];
+            S r[NU], fbp[NU], dbp[NU];
+#pragma unroll
+            for (int q = 0; q < NU; ++q) {  // all loads of the pass first (the dW stores below may alias for the compiler)
+              const int nq = n0 + q <= nmax ? n0 + q : nmax;
+              const int p = i * nb + nq;
+              w[q] = W[p * H + m];
+              go[q] = gw[p * H + m];
+              r[q] = sc[l.R + nq * H + m];
+              fbp[q] = sc[l.fb + p];
+              dbp[q] = nsi * sc[l.SQ + nq];
+            }
+#pragma unroll
+            for (int q = 0; q < NU; ++q)
+              if (n0 + q <= nmax) {
+                hbm = hbm + fbp[q] * w[q];
+                Ei = Ei + dbp[q] * w[q];
+                gw[(i * nb + n0 + q) * H + m] = go[q] + eps_part<S>(fbp[q] * hm + qbi * r[q] + dbp[q] * Ti);
+              }
           }
         if (act) sc[l.Tb[L] + i * H + m] = Ei;
       }
@@ -422,8 +462,17 @@ struct Generic {
       S CR = S(T(0));
       for (int n = 0; n < nb; ++n) {
         S rb = S(T(0));
-        if (act)
-          for (int i = n; i < d; ++i) rb = rb + sc[l.Qb + i] * W[(i * nb + n) * H + m];
+        if (act) {
+          int i = n;
+          for (; i + NU <= d; i += NU) {
+            T w[NU];
+#pragma unroll
+            for (int q = 0; q < NU; ++q) w[q] = W[((i + q) * nb + n) * H + m];
+#pragma unroll
+            for (int q = 0; q < NU; ++q) rb = rb + sc[l.Qb + i + q] * w[q];
+          }
+          for (; i < d; ++i) rb = rb + sc[l.Qb + i] * W[(i * nb + n) * H + m];
+        }
         CR = CR + rb;
         const int jhi = (n == nb - 1) ? d - 1 : n;
         for (int j = n; j <= jhi; ++j) {
@@ -475,7 +524,7 @@ struct Generic {
     grad_layer<S>(a, sc, gacc, 0, t, ab, Ub, lane);
     {  // xbar_j += sum_k W0[k][j] ab_1[k]
       const int H = g.n[1], nin = g.n[0];
-      const T* __restrict__ W0 = a.params + g.woff[0];
+      const T* __restrict__ W0 = gparams(a) + g.woff[0];
       for (int j = lane; j < d; j += 32) {
         S acc = sc[l.xbar + j];
         for (int k = 0; k < H; ++k) acc = acc + W0[k * nin + j] * ab[k];
@@ -573,8 +622,20 @@ __device__ __noinline__ void g_pen_reverse(const GArgs<T>& a, char* wscr, T* gac
   __syncwarp();
 }
 
+// this warp's scratch; in on-chip mode also stages the flat parameters into the CTA's shared memory (all threads of
+// the CTA must call it)
+template <typename T>
+GPF_DEV char* generic_warp_scratch(const GArgs<T>& a, long long gwarp) {
+  extern __shared__ __align__(16) unsigned char g_dyn_smem[];
+  if (!a.on_chip) return a.scratch + (size_t)gwarp * a.scratch_stride;
+  T* ps = reinterpret_cast<T*>(g_dyn_smem);
+  for (int i = threadIdx.x; i < a.g.P; i += blockDim.x) ps[i] = a.params[i];
+  __syncthreads();
+  return reinterpret_cast<char*>(g_dyn_smem) + a.smem_scratch_off + (size_t)(threadIdx.x >> 5) * a.scratch_stride;
+}
+
 template <typename T, int MODE, bool EULER>
-__global__ void __launch_bounds__(128) gpflow_generic_kernel(const GKernelArgs<T> ka) {
+__global__ void __launch_bounds__(kGenericMaxThreads, 1) gpflow_generic_kernel(const GKernelArgs<T> ka) {
   const GArgs<T>& a = ka.a;
   const GLayout& l = a.lay;
   const GVec& vv = ka.vec;
@@ -582,7 +643,7 @@ __global__ void __launch_bounds__(128) gpflow_generic_kernel(const GKernelArgs<T
   const long long gwarp = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const long long nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
   const int d = a.g.d;
-  char* wscr = a.scratch + (size_t)gwarp * a.scratch_stride;
+  char* wscr = generic_warp_scratch<T>(a, gwarp);
   T* sc = reinterpret_cast<T*>(wscr);
   T* vec = reinterpret_cast<T*>(wscr + ka.vec_offset_bytes);
   T* part = a.partials + (size_t)gwarp * a.npart;
@@ -782,13 +843,13 @@ __global__ void __launch_bounds__(128) gpflow_generic_kernel(const GKernelArgs<T
 
 // VelocityField.__call__(x, t)  (velocity_field.py:118-126)
 template <typename T>
-__global__ void __launch_bounds__(128) gpflow_velocity_kernel(const GKernelArgs<T> ka) {
+__global__ void __launch_bounds__(kGenericMaxThreads, 1) gpflow_velocity_kernel(const GKernelArgs<T> ka) {
   const GArgs<T>& a = ka.a;
   const GLayout& l = a.lay;
   const int lane = threadIdx.x & 31;
   const long long gwarp = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const long long nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
-  T* sc = reinterpret_cast<T*>(a.scratch + (size_t)gwarp * a.scratch_stride);
+  T* sc = reinterpret_cast<T*>(generic_warp_scratch<T>(a, gwarp));
   const T bnd = T(1) - Eps<T>::value;
   for (long long b = gwarp; b < a.B; b += nwarps) {
     for (int j = lane; j < a.g.d; j += 32) sc[l.x + j] = a.x_in[b * a.g.d + j];
@@ -804,8 +865,16 @@ __global__ void __launch_bounds__(128) gpflow_velocity_kernel(const GKernelArgs<
 // ---------------------------------------------------------------------------------------------------
 struct GenericPlan {
   long long nwarps;
+  int warps_per_cta, on_chip;
+  size_t smem_bytes, smem_scratch_off;
   size_t scratch_stride, vec_offset, partials_bytes, params_t_bytes, scratch_bytes, total;
 };
+// Two placements of the per-warp scratch (activations, tangents, adjoints of ONE velocity evaluation):
+//   on-chip  when the flat parameters + at least 12 warps' scratch fit the CTA's shared memory: one CTA per SM of up
+//            to 16 warps, every operand of the contractions at shared-memory latency (small latent shapes);
+//   global   otherwise: 4 CTAs of 4 warps per SM, scratch in the workspace (L2 / HBM).  Measured at d=10, nb=9,
+//            H=[50,50,50] (24 KB per warp, 7 warps fit): 45k samples/s on-chip vs 55k global -- 7 warps do not hide
+//            the remaining latencies, so the threshold is 12 warps.  d=64, nb=63, H=256 needs 400 KB per warp.
 inline GenericPlan generic_plan(const GpFlowDesc* d, int64_t B, int op, int sm_count) {
   const size_t es = d->dtype == GPFLOW_F64 ? 8 : 4;
   const GDims g = make_gdims(d);
@@ -813,20 +882,32 @@ inline GenericPlan generic_plan(const GpFlowDesc* d, int64_t B, int op, int sm_c
   const GVec v = make_gvec(g, d->n_steps);
   const bool dual = (d->flags & GPFLOW_FLAG_EULER_PEN) != 0;
   GenericPlan p;
+  memset(&p, 0, sizeof(p));
   p.vec_offset = ((size_t)l.total * es * (dual ? 2 : 1) + 255) / 256 * 256;
   p.scratch_stride = (p.vec_offset + (size_t)v.total * es + 255) / 256 * 256;
+  p.smem_scratch_off = ((size_t)g.P * es + 255) / 256 * 256;
+  p.warps_per_cta = 4;
   long long nw = (long long)sm_count * 4 * 4;  // 4 CTAs of 4 warps per SM
+  static const int on_chip_allowed = [] { const char* e = getenv("GPFLOW_GENERIC_ONCHIP"); return e == nullptr || e[0] != '0'; }();
+  if (on_chip_allowed && (size_t)kGenericSmemBudget > p.smem_scratch_off + 12 * p.scratch_stride) {
+    int w = (int)(((size_t)kGenericSmemBudget - p.smem_scratch_off) / p.scratch_stride);
+    if (w > kGenericMaxThreads / 32) w = kGenericMaxThreads / 32;
+    p.on_chip = 1;
+    p.warps_per_cta = w;
+    p.smem_bytes = p.smem_scratch_off + (size_t)w * p.scratch_stride;
+    nw = (long long)sm_count * w;
+  }
   if (nw > B) nw = B;
-  // bound the per-warp partial vectors (gradient accumulators) to ~2 GiB
-  const size_t per_warp = p.scratch_stride + (size_t)(3 + (op == GPFLOW_OP_FORWARD ? 0 : g.P)) * es;
-  const long long cap = (long long)((size_t)2 << 30) / (long long)per_warp;
+  // bound the per-warp scratch + partial vectors (gradient accumulators) to 16 GiB of the 180 GB
+  const size_t per_warp = (p.on_chip ? 0 : p.scratch_stride) + (size_t)(3 + (op == GPFLOW_OP_FORWARD ? 0 : g.P)) * es;
+  const long long cap = (long long)((size_t)16 << 30) / (long long)per_warp;
   if (nw > cap) nw = cap;
   if (nw < 1) nw = 1;
-  nw = (nw + 3) / 4 * 4;  // whole CTAs
+  nw = (nw + p.warps_per_cta - 1) / p.warps_per_cta * p.warps_per_cta;  // whole CTAs
   p.nwarps = nw;
   p.partials_bytes = ((size_t)nw * (3 + g.P) * es + 255) / 256 * 256;
   p.params_t_bytes = ((size_t)g.P * es + 255) / 256 * 256;
-  p.scratch_bytes = (size_t)nw * p.scratch_stride;
+  p.scratch_bytes = p.on_chip ? 0 : (size_t)nw * p.scratch_stride;
   p.total = p.partials_bytes + p.params_t_bytes + p.scratch_bytes;
   return p;
 }
@@ -865,16 +946,27 @@ int launch_generic_impl(const GpFlowDesc* d, int op, const T* params, const T* x
   a.loss_scale = (T)d->loss_scale;
   gpflow_transpose_params_kernel<T><<<(a.g.P + 255) / 256, 256, 0, st>>>(a.g, params, pt);
   if (cudaGetLastError() != cudaSuccess) return GPFLOW_ERR_CUDA;
-  const unsigned grid = (unsigned)(pl.nwarps / 4);
+  a.on_chip = pl.on_chip;
+  a.smem_scratch_off = (unsigned)pl.smem_scratch_off;
+  const unsigned grid = (unsigned)(pl.nwarps / pl.warps_per_cta), threads = 32u * (unsigned)pl.warps_per_cta;
+  auto launch = [&](void (*kern)(const GKernelArgs<T>)) -> int {
+    if (pl.smem_bytes > 48 * 1024 &&
+        cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem_bytes) != cudaSuccess) {
+      cudaGetLastError();
+      return GPFLOW_ERR_CUDA;
+    }
+    kern<<<grid, threads, pl.smem_bytes, st>>>(ka);
+    return cudaGetLastError() == cudaSuccess ? GPFLOW_OK : GPFLOW_ERR_CUDA;
+  };
   if (v_out != nullptr) {
     if (EULER) return GPFLOW_ERR_BAD_DESC;
-    gpflow_velocity_kernel<T><<<grid, 128, 0, st>>>(ka);
-    return cudaGetLastError() == cudaSuccess ? GPFLOW_OK : GPFLOW_ERR_CUDA;
+    return launch(gpflow_velocity_kernel<T>);
   }
-  if (op == GPFLOW_OP_FORWARD) gpflow_generic_kernel<T, MODE_FWD, EULER><<<grid, 128, 0, st>>>(ka);
-  else if (op == GPFLOW_OP_TRAIN_STEP) gpflow_generic_kernel<T, MODE_TRAIN, EULER><<<grid, 128, 0, st>>>(ka);
-  else gpflow_generic_kernel<T, MODE_BWD, EULER><<<grid, 128, 0, st>>>(ka);
-  if (cudaGetLastError() != cudaSuccess) return GPFLOW_ERR_CUDA;
+  int rc;
+  if (op == GPFLOW_OP_FORWARD) rc = launch(gpflow_generic_kernel<T, MODE_FWD, EULER>);
+  else if (op == GPFLOW_OP_TRAIN_STEP) rc = launch(gpflow_generic_kernel<T, MODE_TRAIN, EULER>);
+  else rc = launch(gpflow_generic_kernel<T, MODE_BWD, EULER>);
+  if (rc != GPFLOW_OK) return rc;
   const int count = op == GPFLOW_OP_FORWARD ? 3 : a.npart;
   if (scalars_out != nullptr || grads_out != nullptr) {
     gpflow_finalize_kernel<T><<<(count + 127) / 128, 128, 0, st>>>(a.partials, (int)pl.nwarps, a.npart, count,

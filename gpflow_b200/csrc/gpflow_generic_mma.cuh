@@ -63,27 +63,38 @@ GPF_DEV void gm_rows_times_w(const float* __restrict__ x0, const float* __restri
       float c[GM_NT][4];
 #pragma unroll
       for (int i = 0; i < GM_NT; ++i) c[i][0] = c[i][1] = c[i][2] = c[i][3] = 0.0f;
-      for (int k0 = 0; k0 < K; k0 += 8) {
-        uint32_t ah[4], al[4];
-        tf32_split(row_elem(x0, X, ldx, d, rl, k0 + t, K), ah[0], al[0]);
-        tf32_split(row_elem(x0, X, ldx, d, rh, k0 + t, K), ah[1], al[1]);
-        tf32_split(row_elem(x0, X, ldx, d, rl, k0 + t + 4, K), ah[2], al[2]);
-        tf32_split(row_elem(x0, X, ldx, d, rh, k0 + t + 4, K), ah[3], al[3]);
+      // operands of k-step k0 are fetched one step ahead (register double buffer): the loads of step k0 + 8 are in
+      // flight while the 3 x GM_NT mma of step k0 issue
+      float an[4], wn[GM_NT][2];
+      auto fetch = [&](int k0) {
+        an[0] = row_elem(x0, X, ldx, d, rl, k0 + t, K);
+        an[1] = row_elem(x0, X, ldx, d, rh, k0 + t, K);
+        an[2] = row_elem(x0, X, ldx, d, rl, k0 + t + 4, K);
+        an[3] = row_elem(x0, X, ldx, d, rh, k0 + t + 4, K);
 #pragma unroll
         for (int i = 0; i < GM_NT; ++i) {
           const int n = nb0 + 8 * i + g;
-          if (nb0 + 8 * i < N) {  // warp-uniform
-            float w0 = 0.0f, w1 = 0.0f;
-            if (n < N) {
-              if (k0 + t < K) w0 = TRANS_B ? W[(k0 + t) * ldw + n] : W[n * ldw + k0 + t];
-              if (k0 + t + 4 < K) w1 = TRANS_B ? W[(k0 + t + 4) * ldw + n] : W[n * ldw + k0 + t + 4];
-            }
-            uint32_t bh[2], bl[2];
-            tf32_split(w0, bh[0], bl[0]);
-            tf32_split(w1, bh[1], bl[1]);
-            mma_3xtf32(c[i], ah, al, bh, bl);
+          wn[i][0] = wn[i][1] = 0.0f;
+          if (n < N) {
+            if (k0 + t < K) wn[i][0] = TRANS_B ? W[(k0 + t) * ldw + n] : W[n * ldw + k0 + t];
+            if (k0 + t + 4 < K) wn[i][1] = TRANS_B ? W[(k0 + t + 4) * ldw + n] : W[n * ldw + k0 + t + 4];
           }
         }
+      };
+      fetch(0);
+      for (int k0 = 0; k0 < K; k0 += 8) {
+        uint32_t ah[4], al[4], bh[GM_NT][2], bl[GM_NT][2];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) tf32_split(an[q], ah[q], al[q]);
+#pragma unroll
+        for (int i = 0; i < GM_NT; ++i) {
+          tf32_split(wn[i][0], bh[i][0], bl[i][0]);
+          tf32_split(wn[i][1], bh[i][1], bl[i][1]);
+        }
+        if (k0 + 8 < K) fetch(k0 + 8);
+#pragma unroll
+        for (int i = 0; i < GM_NT; ++i)
+          if (nb0 + 8 * i < N) mma_3xtf32(c[i], ah, al, bh[i], bl[i]);  // warp-uniform
       }
 #pragma unroll
       for (int i = 0; i < GM_NT; ++i) {
@@ -109,7 +120,12 @@ GPF_DEV void gm_weight_grad(const float* __restrict__ yb0, const float* __restri
   const int R = d + 1;
   for (int k0 = 0; k0 < M; k0 += 16) {
     for (int m0 = 0; m0 < N; m0 += 8) {
-      float c[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+      float c[4] = {0.0f, 0.0f, 0.0f, 0.0f}, go[4];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {  // the accumulator's old values travel while the tile is computed
+        const int k = k0 + g + ((q & 2) ? 8 : 0), m = m0 + 2 * t + (q & 1);
+        go[q] = (k < M && m < N) ? gw[k * N + m] : 0.0f;
+      }
       for (int r0 = 0; r0 < R; r0 += 8) {
         uint32_t ah[4], al[4], bh[2], bl[2];
         // A[k][r] = Yb[r][k]
@@ -125,7 +141,7 @@ GPF_DEV void gm_weight_grad(const float* __restrict__ yb0, const float* __restri
 #pragma unroll
       for (int q = 0; q < 4; ++q) {
         const int k = k0 + g + ((q & 2) ? 8 : 0), m = m0 + 2 * t + (q & 1);
-        if (k < M && m < N) gw[k * N + m] += c[q];
+        if (k < M && m < N) gw[k * N + m] = go[q] + c[q];
       }
     }
   }

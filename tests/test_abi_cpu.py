@@ -73,7 +73,7 @@ def test_workspace_query_and_variant_names(lib):
     assert 0 < n_small.value < (1 << 25)
     big = ops.make_desc(FlowConfig(64, 63, (256, 256), 15), torch.float32, wrap=True)
     assert lib.gpflow_query_workspace(ctypes.byref(big), 1 << 14, _lib.OP_TRAIN_STEP, ctypes.byref(n)) == 0
-    assert n.value < (6 << 30)
+    assert n.value < (17 << 30)    # <= 16 GiB of per-warp scratch + gradient partials (1.1 M parameters per warp) + finalize buffers
 
 
 def test_module_mirror_keeps_reference_interface():
