@@ -7,7 +7,7 @@
 Workload (BASELINE.json configs[3], SURVEY.md 8d "C4"): synthetic 2-D Gaussian-noise train_gp step, global batch
 2^24 samples sharded over the ranks (strong scaling), d=2, nb_div_blocks=1, velocity MLP [15,15], 15 RK4 steps,
 fp32.  One step = fused forward + OT cost + backward (one CUDA launch + deterministic finalize) -> ONE all-reduce of
-the [grads | scalars] buffer (N > 1) -> Adam update of the 332 parameters.
+the [grads | scalars] buffer (N > 1) -> fused Adam update (gpflow_adam_step) of the flat parameter buffer.
 Prints ONE JSON line (see the repo's task contract for the keys).
 """
 import argparse
@@ -190,7 +190,8 @@ def main():
         for p in flow.parameters():
             p.normal_(0.0, wl["w_std"])           # N(0, 0.3^2) weights AND biases, seed 0
     net = G.GPFlowNetwork(flow, map_module=None)
-    opt = torch.optim.Adam(flow.parameters(), lr=2e-3, betas=(0.9, 0.999), weight_decay=1e-4)   # network.py:312-317
+    # network.py:307-320: Adam(lr, betas=(0.9, 0.999), weight_decay=1e-4) on the flat parameter buffer, one launch per step
+    opt = net.configure_fused_optimizer(lr=2e-3, weight_decay=1e-4)
     cfg = flow.config()
 
     # inputs resident in HBM; rotate through enough distinct batches to exceed the 126 MB L2
@@ -283,7 +284,7 @@ def main():
             dist.all_reduce(te, op=dist.ReduceOp.MAX)
         e2e = {"value": B_global / (float(te[0]) / args.steps * 1e-3), "unit": "samples/s",
                "h2d_bytes_per_step": h2d // args.steps * world, "d2h_bytes_per_step": 8 * world,
-               "api": "HostBatchStream -> GPFlowNetwork.fused_training_step -> Adam -> float(loss)"}
+               "api": "HostBatchStream -> GPFlowNetwork.fused_training_step -> FlatAdam.step -> float(loss)"}
 
     if rank != 0:
         if world > 1:
@@ -291,10 +292,9 @@ def main():
         return
 
     # ---- roofline of the dominant kernel: FP32 FMA pipe (compute-bound, K=15 widths -> CUDA cores)
-    sys.path.insert(0, os.path.join(ROOT, "oracle"))
-    import gpflow_oracle as O
-    spec = O.FlowSpec(d=d, nb=wl["nb"], hidden=list(wl["hidden"]), n_steps=wl["n_steps"])
-    flops_per_sample = O.algorithmic_flops_per_sample(spec, train=True)
+    from gpflow_b200.roofline import algorithmic_flops_per_sample
+    flops_per_sample = algorithmic_flops_per_sample(d, wl["nb"], wl["hidden"], wl["n_steps"], train=True,
+                                                    euler=args.euler is not None)
     peak_tf = ops.fp32_fma_peak_tflops()
     achieved_tf = flops_per_sample * B / (ms_kernel * 1e-3) / 1e12
     peaks = {}
@@ -340,8 +340,8 @@ def main():
                        world, cfg.n_params + 3),
                    "l2": "inputs larger than L2: rotating through %d distinct resident batches of %.0f MB" % (
                        n_buf, bytes_per_batch / 1e6),
-                   "step": "fused fwd+OT+bwd kernel, finalize, all-reduce, Adam"},
-        "clocks": clk, "e2e": e2e, "gpu_launches": args.steps * ops.launch_count(cfg),
+                   "step": "fused fwd+OT+bwd kernel, finalize, all-reduce, fused Adam (gpflow_adam_step)"},
+        "clocks": clk, "e2e": e2e, "gpu_launches": args.steps * (ops.launch_count(cfg) + 1),   # + gpflow_adam_step
         "roofline": roofline, "cpu_baseline": cpu_baseline,
         "loss": float(loss), "reg": float(reg),
     }

@@ -5,6 +5,7 @@
 #include <cuda_runtime.h>
 #include <stdio.h>
 #include <string.h>
+#include <math.h>
 
 #include <mutex>
 
@@ -163,6 +164,21 @@ __global__ void clock_probe_kernel(unsigned long long* out) {
 
 }  // namespace
 
+// torch.optim.Adam (L2-coupled weight decay) on a flat buffer, element-wise; grid-stride
+template <typename T>
+__global__ void adam_step_kernel(int64_t n, T* __restrict__ p, const T* __restrict__ g, T* __restrict__ m, T* __restrict__ v,
+                                 T step_size, T beta1, T beta2, T eps, T wd, T bc2_sqrt) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const T pi = p[i];
+    const T gi = g[i] + wd * pi;
+    const T mi = m[i] + (T(1) - beta1) * (gi - m[i]);
+    const T vi = beta2 * v[i] + (T(1) - beta2) * gi * gi;
+    m[i] = mi;
+    v[i] = vi;
+    p[i] = pi - step_size * (mi / (sqrt(vi) / bc2_sqrt + eps));
+  }
+}
+
 extern "C" {
 
 int64_t gpflow_param_count(const GpFlowDesc* d) {
@@ -275,6 +291,25 @@ int gpflow_fp32_fma_burn(int64_t iters, void* sink, double* host_flops_out, void
 int gpflow_clock_probe(void* out2, void* stream) {
   if (out2 == nullptr) return GPFLOW_ERR_NULL_POINTER;
   clock_probe_kernel<<<1, 1, 0, reinterpret_cast<cudaStream_t>(stream)>>>(reinterpret_cast<unsigned long long*>(out2));
+  return cudaGetLastError() == cudaSuccess ? GPFLOW_OK : GPFLOW_ERR_CUDA;
+}
+
+int gpflow_adam_step(int dtype, int64_t n, void* params, const void* grads, void* exp_avg, void* exp_avg_sq, double lr,
+                     double beta1, double beta2, double eps, double weight_decay, int64_t step, void* stream) {
+  if (params == nullptr || grads == nullptr || exp_avg == nullptr || exp_avg_sq == nullptr) return GPFLOW_ERR_NULL_POINTER;
+  if (n < 0 || step < 1 || (dtype != GPFLOW_F32 && dtype != GPFLOW_F64)) return GPFLOW_ERR_BAD_DESC;
+  if (n == 0) return GPFLOW_OK;
+  const double bc1 = 1.0 - pow(beta1, (double)step), bc2 = 1.0 - pow(beta2, (double)step);
+  const double step_size = lr / bc1, bc2_sqrt = sqrt(bc2);
+  const unsigned grid = (unsigned)((n + 255) / 256 < 148 * 8 ? (n + 255) / 256 : 148 * 8);
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  if (dtype == GPFLOW_F32)
+    adam_step_kernel<float><<<grid, 256, 0, st>>>(n, (float*)params, (const float*)grads, (float*)exp_avg, (float*)exp_avg_sq,
+                                                  (float)step_size, (float)beta1, (float)beta2, (float)eps,
+                                                  (float)weight_decay, (float)bc2_sqrt);
+  else
+    adam_step_kernel<double><<<grid, 256, 0, st>>>(n, (double*)params, (const double*)grads, (double*)exp_avg,
+                                                   (double*)exp_avg_sq, step_size, beta1, beta2, eps, weight_decay, bc2_sqrt);
   return cudaGetLastError() == cudaSuccess ? GPFLOW_OK : GPFLOW_ERR_CUDA;
 }
 

@@ -26,6 +26,17 @@ class GPFlowNetwork(torch.nn.Module):
         self.target_gaussian = True
         self.process_group = process_group
         self._buf = None
+        self._flat_opt = None
+
+    # ---- network.py:307-320 (GP branch of configure_optimizers) --------------------------------
+    def configure_fused_optimizer(self, lr=2e-3, weight_decay=1e-4, betas=(0.9, 0.999), eps=1e-8, step_size=None,
+                                  gamma=0.5):
+        """Adam(+L2) + StepLR of the reference on ONE flat parameter buffer (`gpflow_b200.optim.FlatAdam`):
+        `fused_training_step` then reads the parameters and writes `.grad` in place, and `opt.step()` is one launch."""
+        from .optim import FlatAdam
+        self._flat_opt = FlatAdam(self.flow.parameters(), lr=lr, betas=betas, eps=eps, weight_decay=weight_decay,
+                                  step_size=step_size, gamma=gamma)
+        return self._flat_opt
 
     # ---- network.py:156-189 ------------------------------------------------------------------
     def gp_flow(self, x, reverse=False, save_trajectories=False):
@@ -67,16 +78,21 @@ class GPFlowNetwork(torch.nn.Module):
         if world > 1:
             zw = data_parallel.broadcast_probes(zw, 0, pg)   # z, w are shared by all samples (res_net.py:330-343)
         P = cfg.n_params
-        if self._buf is None or self._buf.numel() != P + _lib.NUM_SCALARS or self._buf.dtype != x.dtype or \
-                self._buf.device != x.device:
-            self._buf = torch.empty(P + _lib.NUM_SCALARS, dtype=x.dtype, device=x.device)
-        flat = flow.flat_parameters()
+        opt = self._flat_opt
+        in_place = opt is not None and opt.n == P and opt.dtype == x.dtype and opt.intact()
+        if in_place:            # parameters and .grad are views of the optimiser's flat buffers: no cat, no copies
+            flat, buf = opt.flat, opt.gradbuf
+        else:
+            if self._buf is None or self._buf.numel() != P + _lib.NUM_SCALARS or self._buf.dtype != x.dtype or \
+                    self._buf.device != x.device:
+                self._buf = torch.empty(P + _lib.NUM_SCALARS, dtype=x.dtype, device=x.device)
+            flat, buf = flow.flat_parameters(), self._buf
         res = ops.fused_train_step(cfg, flat, x, x_map, euler_coef=euler, zw=zw, lagrangian=with_lagrangian,
-                                   loss_scale=1.0 / gb, out=self._buf, force_generic=flow.force_generic)
+                                   loss_scale=1.0 / gb, out=buf, force_generic=flow.force_generic)
         if world > 1:
             data_parallel.allreduce_train_buffer(res["buf"], pg)
         off = 0
-        for p in flow.parameters():
+        for p in (() if in_place else flow.parameters()):
             n = p.numel()
             g = res["grads"][off:off + n].view_as(p)
             if p.grad is None:

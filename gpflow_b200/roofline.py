@@ -1,0 +1,30 @@
+"""Algorithmic flop count of the GP-flow path -- the numerator of `bench.py`'s roofline object.
+
+Pruned count per velocity evaluation (FMA = 2 flops; only the `(i >= n, j >= n)` entries that enter the velocity,
+`velocity_field.py:20-79`; tanh / erf counted separately):
+
+    F_val = sum_l 2 n_l n_{l+1} + 2 H_L R                R  = sum_{n<nb} (d - n)
+    F_jac = H_1 d + sum_{l>=2} (2 H_{l-1} H_l d + H_l d) + 2 H_L R2      R2 = sum_{n<nb} (d - n)^2
+    F_asm = 6 R2
+
+forward = 4 N F_eval, train step = 3 x forward.  The Euler penalization (`res_net.py:319-358`) adds the NOMINAL
+increment of 10 N F_eval forward flops (2 evaluation points per step, each = base evaluation + 2 directional
+derivatives at about 2 F_eval apiece), x 3 for the train step.  The kernels may do fewer flops than this count (the
+generic kernel evaluates the last layer in contracted form); the count is the survey's definition, not the kernels'.
+"""
+
+
+def flops_per_eval(d, nb, hidden):
+    H = list(hidden)
+    n = [d + 1] + H
+    R = sum(d - k for k in range(nb))
+    R2 = sum((d - k) ** 2 for k in range(nb))
+    f_val = sum(2 * n[l] * n[l + 1] for l in range(len(n) - 1)) + 2 * H[-1] * R
+    f_jac = H[0] * d + sum(2 * H[l - 1] * H[l] * d + H[l] * d for l in range(1, len(H))) + 2 * H[-1] * R2
+    f_asm = 6 * R2
+    return float(f_val + f_jac + f_asm)
+
+
+def algorithmic_flops_per_sample(d, nb, hidden, n_steps, train=True, euler=False):
+    fwd = (4 + (10 if euler else 0)) * n_steps * flops_per_eval(d, nb, hidden)
+    return 3.0 * fwd if train else fwd

@@ -161,6 +161,18 @@ int gpflow_fp32_fma_burn(int64_t iters, void* sink, double* host_flops_out, void
  * actually running at under load without the driver round trip of an NVML / nvidia-smi query. */
 int gpflow_clock_probe(void* out2, void* cuda_stream);
 
+/* Fused Adam step on the flat parameter buffer -- the `gp_flow_opt.step()` of the GP branch of
+ * `Network.training_step` (src/gp_flows/network.py:104-111) for the optimiser built in `configure_optimizers`
+ * (network.py:307-317: `torch.optim.Adam(flow_params, lr, betas=(0.9, 0.999), weight_decay)`, L2-coupled decay, no
+ * amsgrad).  Same update as torch.optim.Adam:
+ *     g = grad + weight_decay * p;  m = m + (1 - beta1) (g - m);  v = beta2 v + (1 - beta2) g^2
+ *     p = p - lr / (1 - beta1^step) * m / (sqrt(v) / sqrt(1 - beta2^step) + eps)
+ * `step` is the 1-based count of this update.  The StepLR schedule (network.py:318-320) is a host-side scalar: pass
+ * the current `lr`.  dtype: GPFLOW_F32 / GPFLOW_F64; all buffers have `n` elements; `params`, `exp_avg`, `exp_avg_sq`
+ * are updated in place.  One launch. */
+int gpflow_adam_step(int dtype, int64_t n, void* params, const void* grads, void* exp_avg, void* exp_avg_sq, double lr,
+                     double beta1, double beta2, double eps, double weight_decay, int64_t step, void* cuda_stream);
+
 const char* gpflow_error_string(int status);
 int gpflow_abi_version(void);
 
