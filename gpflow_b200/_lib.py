@@ -11,6 +11,8 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("GPFLOW_B200_LIB") or os.path.join(_HERE, "lib", "libgpflow_b200.so")
 
 GPFLOW_ABI_VERSION = 1
+ABI_VERSION = GPFLOW_ABI_VERSION
+ERR_UNSUPPORTED = 2    # include/gpflow_b200.h: GPFLOW_ERR_UNSUPPORTED
 GPFLOW_MAX_HIDDEN = 8
 F32, F64 = 0, 1
 OP_FORWARD, OP_TRAIN_STEP, OP_BACKWARD = 0, 1, 2
@@ -20,9 +22,15 @@ SCALAR_OT, SCALAR_REG, SCALAR_LAGR, NUM_SCALARS = 0, 1, 2, 3
 EXPORTS = [
     "gpflow_param_count", "gpflow_query_workspace", "gpflow_forward", "gpflow_train_step", "gpflow_backward",
     "gpflow_velocity", "gpflow_kernel_variant", "gpflow_launch_count", "gpflow_fp32_fma_burn", "gpflow_clock_probe",
-    "gpflow_adam_step", "gpflow_error_string",
+    "gpflow_adam_step", "gpflow_bnaf_param_count", "gpflow_bnaf_forward", "gpflow_error_string",
     "gpflow_abi_version",
 ]
+
+
+class GpFlowBnafDesc(ctypes.Structure):
+    """include/gpflow_b200.h: GpFlowBnafDesc."""
+    _fields_ = [("abi_version", ctypes.c_int32), ("dtype", ctypes.c_int32), ("dim", ctypes.c_int32),
+                ("hidden_per_dim", ctypes.c_int32), ("n_layers", ctypes.c_int32), ("reserved0", ctypes.c_int32)]
 
 
 class GpFlowDesc(ctypes.Structure):
@@ -81,6 +89,11 @@ def load():
     lib.gpflow_launch_count.argtypes = [D, ctypes.c_int]
     lib.gpflow_clock_probe.restype = ctypes.c_int
     lib.gpflow_clock_probe.argtypes = [P, P]
+    BD = ctypes.POINTER(GpFlowBnafDesc)
+    lib.gpflow_bnaf_param_count.restype = ctypes.c_int
+    lib.gpflow_bnaf_param_count.argtypes = [BD, ctypes.POINTER(ctypes.c_int64)]
+    lib.gpflow_bnaf_forward.restype = ctypes.c_int
+    lib.gpflow_bnaf_forward.argtypes = [BD, ctypes.c_int64, P, P, P, P, P]
     lib.gpflow_adam_step.restype = ctypes.c_int
     lib.gpflow_adam_step.argtypes = [ctypes.c_int, ctypes.c_int64, P, P, P, P] + [ctypes.c_double] * 5 + [ctypes.c_int64, P]
     lib.gpflow_fp32_fma_burn.restype = ctypes.c_int

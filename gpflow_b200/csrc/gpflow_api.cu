@@ -10,6 +10,7 @@
 #include <mutex>
 
 #include "gpflow_dispatch.h"
+#include "gpflow_bnaf.cuh"
 
 using namespace gpflow;
 
@@ -311,6 +312,34 @@ int gpflow_adam_step(int dtype, int64_t n, void* params, const void* grads, void
     adam_step_kernel<double><<<grid, 256, 0, st>>>(n, (double*)params, (const double*)grads, (double*)exp_avg,
                                                    (double*)exp_avg_sq, step_size, beta1, beta2, eps, weight_decay, bc2_sqrt);
   return cudaGetLastError() == cudaSuccess ? GPFLOW_OK : GPFLOW_ERR_CUDA;
+}
+
+static int bnaf_check(const GpFlowBnafDesc* d) {
+  if (d == nullptr) return GPFLOW_ERR_NULL_POINTER;
+  if (d->abi_version != GPFLOW_ABI_VERSION || d->dim < 1 || d->hidden_per_dim < 1 || d->n_layers < 2) return GPFLOW_ERR_BAD_DESC;
+  if (d->dtype != GPFLOW_F32 || d->dim != 2 || d->hidden_per_dim != 16 || d->n_layers > kBnafMaxLayers)
+    return GPFLOW_ERR_UNSUPPORTED;
+  return GPFLOW_OK;
+}
+
+int gpflow_bnaf_param_count(const GpFlowBnafDesc* d, int64_t* count) {
+  if (count == nullptr) return GPFLOW_ERR_NULL_POINTER;
+  const int rc = bnaf_check(d);
+  if (rc != GPFLOW_OK) return rc;
+  *count = Bnaf<2, 16>::param_count(d->n_layers);
+  return GPFLOW_OK;
+}
+
+int gpflow_bnaf_forward(const GpFlowBnafDesc* d, int64_t B, const void* params, const void* x, void* y_out,
+                        void* logdet_out, void* stream) {
+  const int rc = bnaf_check(d);
+  if (rc != GPFLOW_OK) return rc;
+  if (B < 0) return GPFLOW_ERR_BAD_DESC;
+  if (B == 0) return GPFLOW_OK;
+  if (params == nullptr || x == nullptr || y_out == nullptr) return GPFLOW_ERR_NULL_POINTER;
+  if (reinterpret_cast<uintptr_t>(params) & 3) return GPFLOW_ERR_MISALIGNED;
+  return launch_bnaf_forward<2, 16>(d->n_layers, (const float*)params, (const float*)x, (float*)y_out, (float*)logdet_out,
+                                    B, reinterpret_cast<cudaStream_t>(stream), device_info().sm_count);
 }
 
 const char* gpflow_error_string(int status) {

@@ -173,6 +173,26 @@ int gpflow_clock_probe(void* out2, void* cuda_stream);
 int gpflow_adam_step(int dtype, int64_t n, void* params, const void* grads, void* exp_avg, void* exp_avg_sq, double lr,
                      double beta1, double beta2, double eps, double weight_decay, int64_t step, void* cuda_stream);
 
+/* Forward of the frozen BNAF map in front of the GP flow: `x_map, log_det = self.map(x)` of `Network.loss_gp_flow`
+ * (src/gp_flows/network.py:76-78) for `flow_models/bnaf/bnaf.py:11-39` with ONE block (`nblocks = 1`, res = None, the
+ * shape of pretrained_models/{eight_gaussians,moons}/bnaf): MaskedWeight(dim -> H) Tanh [MaskedWeight(H -> H) Tanh]^(n-2)
+ * MaskedWeight(H -> dim), H = dim * hidden_per_dim, n = n_layers masked linear layers (bnaf_module.py:151-325).
+ * `params` = concatenation over the masked layers, in state_dict order, of `_weight [out][in]`, `_diag_weight [out]`,
+ * `bias [out]` (the `mask_d` / `mask_o` buffers are implied by the shape).  fp32 only; supported shapes: dim = 2,
+ * hidden_per_dim = 16; anything else returns GPFLOW_ERR_UNSUPPORTED (the caller keeps the reference module).
+ * Writes y_out [B, dim] and, if not NULL, logdet_out [B].  One launch, no workspace. */
+typedef struct GpFlowBnafDesc {
+  int32_t abi_version;     /* GPFLOW_ABI_VERSION */
+  int32_t dtype;           /* GPFLOW_F32 */
+  int32_t dim;
+  int32_t hidden_per_dim;  /* n_neurons / dim */
+  int32_t n_layers;        /* masked linear layers, >= 2 */
+  int32_t reserved0;
+} GpFlowBnafDesc;
+int gpflow_bnaf_param_count(const GpFlowBnafDesc* desc, int64_t* count);
+int gpflow_bnaf_forward(const GpFlowBnafDesc* desc, int64_t B, const void* params, const void* x, void* y_out,
+                        void* logdet_out, void* cuda_stream);
+
 const char* gpflow_error_string(int status);
 int gpflow_abi_version(void);
 
