@@ -83,6 +83,8 @@ struct GArgs {
   char* scratch;         // per-warp scratch, stride scratch_stride bytes (global mode)
   size_t scratch_stride;
   int on_chip;           // 1: the parameters and every warp's scratch live in the CTA's shared memory
+  int vec4;              // 1: fp32, last hidden width and the last layer's parameter offset multiples of 4, 16-byte
+                         //    aligned parameters: the last-layer passes use 128-bit loads (4 input units per lane)
   unsigned smem_scratch_off;  // byte offset of warp 0's scratch inside dynamic shared memory (on-chip mode)
   long long B;
   int n_steps; int npart; unsigned flags;
@@ -227,8 +229,15 @@ struct Generic {
       }
     }
     __syncwarp();
+    bool dots_done = false;
+    if constexpr (std::is_same<S, float>::value) {
+      if (a.vec4) {
+        gl_dots_v4(W, bias, hL, TL, sc + l.R, sc + l.f, sc + l.G, sc + l.D, d, nb, H, lane);
+        dots_done = true;
+      }
+    }
     // three dot products per kept row, NU rows per pass so that 2 NU + 2 independent loads are in flight per lane
-    for (int i = 0; i < d; ++i) {
+    for (int i = 0; i < d && !dots_done; ++i) {
       const int nmax = i < nb - 1 ? i : nb - 1;
       for (int n0 = 0; n0 <= nmax; n0 += NU) {
         S af[NU], ag[NU], ad[NU];
@@ -421,7 +430,15 @@ struct Generic {
       sc[l.sb + j] = sbj;
     }
     __syncwarp();
-    for (int m0 = 0; m0 < H; m0 += 32) {
+    bool passes_done = false;
+    if constexpr (std::is_same<S, float>::value) {
+      if (a.vec4) {
+        gl_reverse_v4(W, gw, hL, TL, sc + l.R, sc + l.fb, sc + l.Qb, sc + l.s, sc + l.SQ, sc + l.hb[L], sc + l.Tb[L],
+                      sc + l.sb, d, nb, H, lane);
+        passes_done = true;
+      }
+    }
+    for (int m0 = 0; m0 < H && !passes_done; m0 += 32) {
       const int m = m0 + lane;
       const bool act = m < H;
       S hbm = S(T(0));
@@ -863,6 +880,9 @@ __global__ void __launch_bounds__(kGenericMaxThreads, 1) gpflow_velocity_kernel(
 // ---------------------------------------------------------------------------------------------------
 // host side: workspace carving and launch
 // ---------------------------------------------------------------------------------------------------
+// per-warp partial vector [1 pad | ot, reg, lagr | P gradients | pad]: the gradients start 16-byte aligned
+inline size_t generic_part_stride(int P) { return (size_t)(3 + P + 1 + 3) / 4 * 4; }
+
 struct GenericPlan {
   long long nwarps;
   int warps_per_cta, on_chip;
@@ -905,7 +925,7 @@ inline GenericPlan generic_plan(const GpFlowDesc* d, int64_t B, int op, int sm_c
   if (nw < 1) nw = 1;
   nw = (nw + p.warps_per_cta - 1) / p.warps_per_cta * p.warps_per_cta;  // whole CTAs
   p.nwarps = nw;
-  p.partials_bytes = ((size_t)nw * (3 + g.P) * es + 255) / 256 * 256;
+  p.partials_bytes = (((size_t)nw * generic_part_stride(g.P) + 4) * es + 255) / 256 * 256;
   p.params_t_bytes = ((size_t)g.P * es + 255) / 256 * 256;
   p.scratch_bytes = p.on_chip ? 0 : (size_t)nw * p.scratch_stride;
   p.total = p.partials_bytes + p.params_t_bytes + p.scratch_bytes;
@@ -931,14 +951,16 @@ int launch_generic_impl(const GpFlowDesc* d, int op, const T* params, const T* x
   ka.vec = make_gvec(a.g, d->n_steps);
   ka.vec_offset_bytes = pl.vec_offset;
   char* w = reinterpret_cast<char*>(ws);
-  a.partials = reinterpret_cast<T*>(w); w += pl.partials_bytes;
+  a.partials = reinterpret_cast<T*>(w) + 1; w += pl.partials_bytes;   // + 1: see generic_part_stride
   T* pt = reinterpret_cast<T*>(w); w += pl.params_t_bytes;
   a.scratch = w;
   a.scratch_stride = pl.scratch_stride;
   a.params = params; a.params_t = pt; a.x_in = x_in; a.x_data = x_data; a.grad_y = grad_y; a.reg_cotangent = reg_cot;
   a.zw = zw; a.y_out = y_out; a.logdet_out = logdet_out; a.traj_out = traj_out; a.grad_x_out = grad_x_out;
   a.v_out = v_out; a.t_eval = (T)t_eval;
-  a.B = B; a.n_steps = d->n_steps; a.npart = 3 + a.g.P; a.flags = d->flags;
+  a.B = B; a.n_steps = d->n_steps; a.npart = (int)generic_part_stride(a.g.P); a.flags = d->flags;
+  a.vec4 = (sizeof(T) == 4 && a.g.n[a.g.L] % 4 == 0 && a.g.woff[a.g.L] % 4 == 0 &&
+            (reinterpret_cast<uintptr_t>(params) & 15) == 0) ? 1 : 0;
   const bool rev = (d->flags & GPFLOW_FLAG_REVERSE) != 0;
   a.dt = rev ? -(T)d->dt : (T)d->dt;
   a.t0 = rev ? (T)(d->dt * (double)d->n_steps_nominal) : (T)0;
@@ -967,7 +989,7 @@ int launch_generic_impl(const GpFlowDesc* d, int op, const T* params, const T* x
   else if (op == GPFLOW_OP_TRAIN_STEP) rc = launch(gpflow_generic_kernel<T, MODE_TRAIN, EULER>);
   else rc = launch(gpflow_generic_kernel<T, MODE_BWD, EULER>);
   if (rc != GPFLOW_OK) return rc;
-  const int count = op == GPFLOW_OP_FORWARD ? 3 : a.npart;
+  const int count = op == GPFLOW_OP_FORWARD ? 3 : 3 + a.g.P;
   if (scalars_out != nullptr || grads_out != nullptr) {
     gpflow_finalize_kernel<T><<<(count + 127) / 128, 128, 0, st>>>(a.partials, (int)pl.nwarps, a.npart, count,
                                                                    scalars_out, grads_out);

@@ -147,4 +147,123 @@ GPF_DEV void gm_weight_grad(const float* __restrict__ yb0, const float* __restri
   }
 }
 
+// ---------------------------------------------------------------------------------------------------
+// fp32 last-layer passes with 128-bit accesses: lane owns input units m = 4 lane + 128 c.  Same arithmetic as the
+// scalar loops of Generic<T>::last_layer_forward / last_layer_reverse (see the formulas there); 4 kept rows per pass,
+// so 8-12 independent 16-byte loads are in flight per lane -- the passes are L2 / HBM latency bound.
+// ---------------------------------------------------------------------------------------------------
+GPF_DEV float4 gl_ld4(const float* p) { return *reinterpret_cast<const float4*>(p); }
+GPF_DEV void gl_st4(float* p, float4 v) { *reinterpret_cast<float4*>(p) = v; }
+GPF_DEV float gl_dot4(float4 a, float4 b, float acc) { return fmaf(a.x, b.x, fmaf(a.y, b.y, fmaf(a.z, b.z, fmaf(a.w, b.w, acc)))); }
+GPF_DEV float4 gl_fma4(float s, float4 a, float4 acc) {
+  return make_float4(fmaf(s, a.x, acc.x), fmaf(s, a.y, acc.y), fmaf(s, a.z, acc.z), fmaf(s, a.w, acc.w));
+}
+
+// f_p = W[p].h + b_p, g_p = W[p].R_n, D_p = W[p].T_L[i] for every kept row p = (i, n <= min(i, nb-1))
+GPF_DEV void gl_dots_v4(const float* __restrict__ W, const float* __restrict__ bias, const float* __restrict__ hL,
+                        const float* __restrict__ TL, const float* __restrict__ R, float* __restrict__ f,
+                        float* __restrict__ G, float* __restrict__ D, int d, int nb, int H, int lane) {
+  for (int i = 0; i < d; ++i) {
+    const int nmax = i < nb - 1 ? i : nb - 1;
+    for (int n0 = 0; n0 <= nmax; n0 += 4) {
+      float af[4] = {0.f, 0.f, 0.f, 0.f}, ag[4] = {0.f, 0.f, 0.f, 0.f}, ad[4] = {0.f, 0.f, 0.f, 0.f};
+      for (int m = 4 * lane; m < H; m += 128) {
+        float4 w[4], r[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const int nq = n0 + q <= nmax ? n0 + q : nmax;  // clamped rows are discarded below
+          w[q] = gl_ld4(W + (size_t)(i * nb + nq) * H + m);
+          r[q] = gl_ld4(R + nq * H + m);
+        }
+        const float4 hm = gl_ld4(hL + m), ti = gl_ld4(TL + i * H + m);
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          af[q] = gl_dot4(w[q], hm, af[q]);
+          ag[q] = gl_dot4(w[q], r[q], ag[q]);
+          ad[q] = gl_dot4(w[q], ti, ad[q]);
+        }
+      }
+      const float rf = warp_sum4(af, lane), rg = warp_sum4(ag, lane), rd = warp_sum4(ad, lane);
+      const int q = 2 * ((lane >> 4) & 1) + ((lane >> 3) & 1);
+      if ((lane & 7) == 0 && n0 + q <= nmax) {
+        const int p = i * nb + n0 + q;
+        f[p] = rf + bias[p];
+        G[p] = rg;
+        D[p] = rd;
+      }
+    }
+  }
+}
+
+// pass A (hb_L, D part of Tb_L, dW) and pass B (Rb_n, CR_n, R part of Tb_L and of sb) of the reverse last layer
+GPF_DEV void gl_reverse_v4(const float* __restrict__ W, float* __restrict__ gw, const float* __restrict__ hL,
+                           const float* __restrict__ TL, const float* __restrict__ R, const float* __restrict__ fb,
+                           const float* __restrict__ Qb, const float* __restrict__ s, const float* __restrict__ SQ,
+                           float* __restrict__ hb, float* __restrict__ Tb, float* sb, int d, int nb, int H, int lane) {
+  const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
+  for (int m0 = 0; m0 < H; m0 += 128) {
+    const int m = m0 + 4 * lane;
+    const bool act = m < H;
+    float4 hbm = z4;
+    const float4 hm = act ? gl_ld4(hL + m) : z4;
+    for (int i = 0; i < d; ++i) {
+      const int nmax = i < nb - 1 ? i : nb - 1;
+      const float4 Ti = act ? gl_ld4(TL + i * H + m) : z4;
+      const float qbi = Qb[i], nsi = -s[i];
+      float4 Ei = z4;
+      if (act) {
+        for (int n0 = 0; n0 <= nmax; n0 += 4) {
+          float4 w[4], go[4], r[4];
+          float fbp[4], dbp[4];
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {  // every load of the pass before its stores
+            const int nq = n0 + q <= nmax ? n0 + q : nmax;
+            const size_t p = (size_t)(i * nb + nq);
+            w[q] = gl_ld4(W + p * H + m);
+            go[q] = gl_ld4(gw + p * H + m);
+            r[q] = gl_ld4(R + nq * H + m);
+            fbp[q] = fb[p];
+            dbp[q] = nsi * SQ[nq];
+          }
+#pragma unroll
+          for (int q = 0; q < 4; ++q)
+            if (n0 + q <= nmax) {
+              hbm = gl_fma4(fbp[q], w[q], hbm);
+              Ei = gl_fma4(dbp[q], w[q], Ei);
+              gl_st4(gw + (size_t)(i * nb + n0 + q) * H + m, gl_fma4(fbp[q], hm, gl_fma4(qbi, r[q], gl_fma4(dbp[q], Ti, go[q]))));
+            }
+        }
+        gl_st4(Tb + i * H + m, Ei);
+      }
+    }
+    if (act) gl_st4(hb + m, hbm);
+    float4 CR = z4;
+    for (int n = 0; n < nb; ++n) {
+      float4 rb = z4;
+      if (act) {
+        int i = n;
+        for (; i + 4 <= d; i += 4) {
+          float4 w[4];
+#pragma unroll
+          for (int q = 0; q < 4; ++q) w[q] = gl_ld4(W + (size_t)((i + q) * nb + n) * H + m);
+#pragma unroll
+          for (int q = 0; q < 4; ++q) rb = gl_fma4(Qb[i + q], w[q], rb);
+        }
+        for (; i < d; ++i) rb = gl_fma4(Qb[i], gl_ld4(W + (size_t)(i * nb + n) * H + m), rb);
+      }
+      CR = make_float4(CR.x + rb.x, CR.y + rb.y, CR.z + rb.z, CR.w + rb.w);
+      const int jhi = (n == nb - 1) ? d - 1 : n;
+      for (int j = n; j <= jhi; ++j) {
+        float part = 0.0f;
+        if (act) {
+          part = gl_dot4(CR, gl_ld4(TL + j * H + m), 0.0f);
+          gl_st4(Tb + j * H + m, gl_fma4(s[j], CR, gl_ld4(Tb + j * H + m)));
+        }
+        part = warp_sum(part);
+        if (lane == 0) sb[j] = sb[j] + part;
+      }
+    }
+  }
+}
+
 }  // namespace gpflow
