@@ -98,6 +98,25 @@ template <typename T> __host__ __device__ constexpr int odd16_stride(int n) {
 }
 
 // ---- tiling of one weight-gradient contraction  C[M x NC] += sum_{s<32} L[s][M] (x) R[s][NC] -----
+#ifndef GPF_V1_NOINLINE
+#define GPF_V1_NOINLINE 1
+#endif
+// GPF_V1_ROLL: the two H2 x H1 contractions over the rows of W2 keep their row loop rolled (the row index then
+// addresses h2 / U2 / ab2 / Ub2 dynamically, i.e. in local memory) -- trades a few LDL/STL for 15x less code
+#ifndef GPF_V1_ROLL
+#define GPF_V1_ROLL 0   // measured: 9.6e6 vs 1.49e7 samples/s on the Euler row (LDL/STL on the critical path), kept as an option
+#endif
+#if GPF_V1_ROLL
+#define GPF_V1_ROLL_PRAGMA _Pragma("unroll 1")
+#else
+#define GPF_V1_ROLL_PRAGMA _Pragma("unroll")
+#endif
+#if GPF_V1_NOINLINE
+#define GPF_V1_CALL __device__ __noinline__
+#else
+#define GPF_V1_CALL GPF_DEV
+#endif
+
 template <int M_, int NC_>
 struct TileCfg {
   static constexpr int M = M_, NC = NC_;
@@ -163,7 +182,7 @@ struct SmallKernel {
 #pragma unroll
       for (int j = 0; j < D; ++j) T1[k][j] = sp * row[j];
     }
-#pragma unroll
+    GPF_V1_ROLL_PRAGMA
     for (int k = 0; k < H2; ++k) {
       T row[S2];
       lds_row<T, S2>(w + SM_W2 + k * S2, row);
@@ -233,8 +252,12 @@ struct SmallKernel {
     }
   }
 
+  // velocity / vjp_at are the units of code reuse: NOT inlined (GPF_V1_NOINLINE), so that the Euler kernels hold one
+  // copy of the dual-number forward and forward+reverse evaluation instead of 10 + 4 (53k SASS instructions, 850 KB:
+  // ncu showed 14 no-instruction stall cycles per issued instruction).  Arguments are D-vectors: the call costs a few
+  // local-memory moves.
   template <typename S>
-  GPF_DEV static void velocity(const T* __restrict__ w, const S (&x)[D], T t, T bnd, S (&v)[D]) {
+  GPF_V1_CALL static void velocity(const T* __restrict__ w, const S (&x)[D], T t, T bnd, S (&v)[D]) {
     EvalState<S> st;
     eval_forward<S>(w, x, t, bnd, v, st);
   }
@@ -479,7 +502,7 @@ struct SmallKernel {
 #pragma unroll
       for (int j = 0; j < D; ++j) Tb1[m][j] = S(T(0));
     }
-#pragma unroll
+    GPF_V1_ROLL_PRAGMA
     for (int k = 0; k < H2; ++k) {
       T row[S2];
       lds_row<T, S2>(w + SM_W2 + k * S2, row);
@@ -530,7 +553,7 @@ struct SmallKernel {
 
   // J_v(x,t)^T vbar with recomputed activations
   template <typename S>
-  GPF_DEV static void vjp_at(const T* __restrict__ w, const Sink& sk, const S (&x)[D], T t, T bnd, const S (&vbar)[D],
+  GPF_V1_CALL static void vjp_at(const T* __restrict__ w, const Sink& sk, const S (&x)[D], T t, T bnd, const S (&vbar)[D],
                              S (&xbar)[D]) {
     EvalState<S> st;
     S v[D];
