@@ -319,10 +319,22 @@ def main():
         "hbm": {"algorithmic_GBps": 12 * d * B / (ms_kernel * 1e-3) / 1e9,
                 "traffic_GBps": (traffic / (ms_kernel * 1e-3) / 1e9) if traffic else None,
                 "peak_GBps": peaks.get("hbm_gbs"), "peak_kind": "of measured (MEASURED_PEAKS.json copy bandwidth)",
-                "note": "algorithmic bytes = x_data + x_map + y (12 d B/sample); the measured DRAM traffic is the "
-                        "activation stash the kernel streams out in the forward sweep and back in the reverse sweep "
-                        "by TMA instead of recomputing 60 velocity evaluations (DESIGN.md section 4)"},
+                "note": "algorithmic bytes = x_data + x_map + y (12 d B/sample)" + (
+                    "; the measured DRAM traffic is the activation stash the kernel streams out in the forward sweep "
+                    "and back in the reverse sweep by TMA instead of recomputing 60 velocity evaluations (DESIGN.md "
+                    "section 4)" if traffic else "")},
     }
+    if "generic" in roofline["kernel"]:
+        # the wide shapes are judged against the tensor pipe at the precision actually used
+        # (3xTF32 => a third of the TF32 rate), measured live with the same mma.sync instruction
+        tf32 = ops.tf32_mma_peak_tflops()
+        roofline["tensor"] = {"bound": "tensor", "peak": tf32 / 3.0, "unit": "TFLOP/s fp32-equivalent (3xTF32)",
+                              "frac": achieved_tf / (tf32 / 3.0) if tf32 else None, "tf32_mma_sync_tflops": tf32,
+                              "peak_source": "mma.sync.m16n8k8 tf32 burn measured live in this run "
+                                             "(gpflow_tf32_mma_burn) / 3",
+                              "note": "hidden-layer contractions run on the tensor pipe (3xTF32 mma.sync), the "
+                                      "Jacobian-free last layer on the FP32 pipe; `achieved` counts the survey's "
+                                      "algorithmic flops, more than the kernel executes (DESIGN.md 4.3)"}
     cpu_baseline = None
     if not args.no_cpu_baseline and world == 1:
         threads = os.cpu_count() or 1

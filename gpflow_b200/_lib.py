@@ -21,7 +21,7 @@ SCALAR_OT, SCALAR_REG, SCALAR_LAGR, NUM_SCALARS = 0, 1, 2, 3
 
 EXPORTS = [
     "gpflow_param_count", "gpflow_query_workspace", "gpflow_forward", "gpflow_train_step", "gpflow_backward",
-    "gpflow_velocity", "gpflow_kernel_variant", "gpflow_launch_count", "gpflow_fp32_fma_burn", "gpflow_clock_probe",
+    "gpflow_velocity", "gpflow_kernel_variant", "gpflow_launch_count", "gpflow_fp32_fma_burn", "gpflow_tf32_mma_burn", "gpflow_clock_probe",
     "gpflow_adam_step", "gpflow_bnaf_param_count", "gpflow_bnaf_forward", "gpflow_error_string",
     "gpflow_abi_version",
 ]
@@ -96,6 +96,8 @@ def load():
     lib.gpflow_bnaf_forward.argtypes = [BD, ctypes.c_int64, P, P, P, P, P]
     lib.gpflow_adam_step.restype = ctypes.c_int
     lib.gpflow_adam_step.argtypes = [ctypes.c_int, ctypes.c_int64, P, P, P, P] + [ctypes.c_double] * 5 + [ctypes.c_int64, P]
+    lib.gpflow_tf32_mma_burn.restype = ctypes.c_int
+    lib.gpflow_tf32_mma_burn.argtypes = [ctypes.c_int64, P, ctypes.POINTER(ctypes.c_double), P]
     lib.gpflow_fp32_fma_burn.restype = ctypes.c_int
     lib.gpflow_fp32_fma_burn.argtypes = [ctypes.c_int64, P, ctypes.POINTER(ctypes.c_double), P]
     lib.gpflow_error_string.restype = ctypes.c_char_p

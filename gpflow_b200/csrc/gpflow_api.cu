@@ -151,6 +151,25 @@ __global__ void __launch_bounds__(256) fma_burn_kernel(long long iters, float* s
   if (s == 123.456f) sink[0] = s;
 }
 
+// ---- TF32 mma.sync burn (tensor-pipe roofline denominator of the generic kernel's 3xTF32 contractions) ----
+__global__ void __launch_bounds__(512) tf32_mma_burn_kernel(long long iters, float* sink) {
+  float c[8][4];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) c[i][0] = c[i][1] = c[i][2] = c[i][3] = 0.f;
+  const unsigned a0 = threadIdx.x, a1 = a0 + 1, a2 = a0 + 2, a3 = a0 + 3, b0 = a0 + 4, b1 = a0 + 5;
+  for (long long it = 0; it < iters; ++it) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+      asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                   : "+f"(c[i][0]), "+f"(c[i][1]), "+f"(c[i][2]), "+f"(c[i][3])
+                   : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+  }
+  float s = 0.f;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) s += c[i][0] + c[i][1] + c[i][2] + c[i][3];
+  if (s == 123.456f) sink[0] = s;
+}
+
 // ---- SM clock probe: (clock64 ticks, globaltimer ns) over a short spin; MHz = 1e3 * ticks / ns ----
 __global__ void clock_probe_kernel(unsigned long long* out) {
   unsigned long long c0 = clock64(), t0, t1;
@@ -286,6 +305,17 @@ int gpflow_fp32_fma_burn(int64_t iters, void* sink, double* host_flops_out, void
   fma_burn_kernel<<<grid, block, 0, reinterpret_cast<cudaStream_t>(stream)>>>((long long)iters, (float*)sink);
   if (cudaGetLastError() != cudaSuccess) return GPFLOW_ERR_CUDA;
   if (host_flops_out) *host_flops_out = 2.0 * 128.0 * (double)iters * (double)grid * (double)block;
+  return GPFLOW_OK;
+}
+
+int gpflow_tf32_mma_burn(int64_t iters, void* sink, double* host_flops_out, void* stream) {
+  if (sink == nullptr) return GPFLOW_ERR_NULL_POINTER;
+  if (iters < 1) return GPFLOW_ERR_BAD_DESC;
+  const DeviceInfo di = device_info();
+  const int grid = di.sm_count, block = 512;   // 16 warps per SM (measured: saturates from 8)
+  tf32_mma_burn_kernel<<<grid, block, 0, reinterpret_cast<cudaStream_t>(stream)>>>((long long)iters, (float*)sink);
+  if (cudaGetLastError() != cudaSuccess) return GPFLOW_ERR_CUDA;
+  if (host_flops_out) *host_flops_out = 2.0 * 16.0 * 8.0 * 8.0 * 8.0 * (double)iters * (double)grid * (double)(block / 32);
   return GPFLOW_OK;
 }
 

@@ -255,3 +255,21 @@ def fp32_fma_peak_tflops(iters: int = 4096, repeats: int = 5) -> float:
         if it > 0:
             best = max(best, flops.value / (e0.elapsed_time(e1) * 1e-3) / 1e12)
     return best
+
+
+def tf32_mma_peak_tflops(iters: int = 20000, repeats: int = 3) -> float:
+    """Measured dense TF32 rate of mma.sync.m16n8k8 on the current device (the instruction behind the generic kernel's
+    3xTF32 contractions); the fp32-equivalent roof of a 3xTF32 contraction is a third of it."""
+    lib = _lib.load()
+    sink = torch.zeros(1, dtype=torch.float32, device="cuda")
+    flops = ctypes.c_double(0.0)
+    best = 0.0
+    for it in range(repeats + 1):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        _lib.check(lib.gpflow_tf32_mma_burn(iters, _ptr(sink), ctypes.byref(flops), _stream()))
+        e1.record()
+        e1.synchronize()
+        if it > 0:
+            best = max(best, flops.value / (e0.elapsed_time(e1) * 1e-3) / 1e12)
+    return best

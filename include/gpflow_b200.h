@@ -156,6 +156,12 @@ int gpflow_launch_count(const GpFlowDesc* desc, int op);
  * flops enqueued (2 per FFMA) is returned through `host_flops_out` (HOST pointer).  Time it with CUDA events. */
 int gpflow_fp32_fma_burn(int64_t iters, void* sink, double* host_flops_out, void* cuda_stream);
 
+/* TF32 tensor-pipe micro-benchmark: every warp of a grid that fills all SMs issues `iters` x 8 independent
+ * mma.sync.m16n8k8 tf32 (fp32 accumulate), the instruction the generic kernel's 3xTF32 contractions use.  The dense
+ * tf32 flops enqueued are returned through `host_flops_out` (HOST pointer); the fp32-equivalent roof of a 3xTF32
+ * contraction is one third of the measured rate. */
+int gpflow_tf32_mma_burn(int64_t iters, void* sink, double* host_flops_out, void* cuda_stream);
+
 /* SM clock probe for benchmarks: one thread spins ~40k SM cycles and writes {clock64 ticks, globaltimer ns} to the
  * device uint64[2] `out2`; SM MHz = 1e3 * ticks / ns.  Enqueued between timed steps it samples the clock the GPU is
  * actually running at under load without the driver round trip of an NVML / nvidia-smi query. */
