@@ -332,7 +332,8 @@ int gpflow_adam_step(int dtype, int64_t n, void* params, const void* grads, void
   if (n == 0) return GPFLOW_OK;
   const double bc1 = 1.0 - pow(beta1, (double)step), bc2 = 1.0 - pow(beta2, (double)step);
   const double step_size = lr / bc1, bc2_sqrt = sqrt(bc2);
-  const unsigned grid = (unsigned)((n + 255) / 256 < 148 * 8 ? (n + 255) / 256 : 148 * 8);
+  const int64_t max_ctas = (int64_t)device_info().sm_count * 8;
+  const unsigned grid = (unsigned)((n + 255) / 256 < max_ctas ? (n + 255) / 256 : max_ctas);
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   if (dtype == GPFLOW_F32)
     adam_step_kernel<float><<<grid, 256, 0, st>>>(n, (float*)params, (const float*)grads, (float*)exp_avg, (float*)exp_avg_sq,

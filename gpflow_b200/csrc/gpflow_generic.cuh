@@ -77,6 +77,8 @@ struct GArgs {
   GLayout lay;
   const T* params;       // flat [P]
   const T* params_t;     // transposed weights: Wt_li [n[li]][n[li+1]] at woff[li] (biases not copied)
+  const T* w_split;      // fp32: [W_hi | W_lo | Wt_hi | Wt_lo], P floats each: tf32 hi / lo parts of the weights and of
+                         // their transposes (3xTF32 operands prepared once per call); nullptr otherwise
   const T* x_in; const T* x_data; const T* grad_y; const T* reg_cotangent; const T* zw;
   T* y_out; T* logdet_out; T* traj_out; T* grad_x_out; T* v_out;
   T* partials;           // [nwarps][3 + P]
@@ -92,18 +94,29 @@ struct GArgs {
 };
 
 template <typename T>
-__global__ void gpflow_transpose_params_kernel(GDims g, const T* __restrict__ p, T* __restrict__ pt) {
+__global__ void gpflow_transpose_params_kernel(GDims g, const T* __restrict__ p, T* __restrict__ pt, T* __restrict__ split) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= g.P) return;
+  int it = i;  // index of p[i] in the transposed copy (biases stay in place)
   for (int li = 0; li <= g.L; ++li) {
     const int nin = g.n[li], no = g.n[li + 1];
     if (i >= g.woff[li] && i < g.woff[li] + nin * no) {
       const int e = i - g.woff[li], k = e / nin, m = e % nin;
-      pt[g.woff[li] + m * no + k] = p[i];
-      return;
+      it = g.woff[li] + m * no + k;
+      break;
     }
   }
-  pt[i] = p[i];  // biases
+  pt[it] = p[i];
+  if constexpr (std::is_same<T, float>::value) {
+    if (split != nullptr) {
+      uint32_t hi, lo;
+      tf32_split(p[i], hi, lo);
+      split[i] = __uint_as_float(hi);
+      split[(size_t)g.P + i] = __uint_as_float(lo);
+      split[2 * (size_t)g.P + it] = __uint_as_float(hi);
+      split[3 * (size_t)g.P + it] = __uint_as_float(lo);
+    }
+  }
 }
 
 // flat parameters as the kernels read them: the CTA's shared-memory copy in on-chip mode, else the caller's buffer
@@ -171,6 +184,9 @@ struct Generic {
       S* y0 = sc + l.h[li + 1];
       S* Y = sc + l.U[li + 1];
       if (a.on_chip) gm_rows_times_w<false>(hin, Tin, nin, d, nin, no, gparams(a) + g.woff[li], nin, bias, y0, Y, no, lane);
+      else if (a.w_split != nullptr && nin % 8 == 0 && no % 64 == 0 && g.woff[li] % 4 == 0)
+        gm_rows_times_w_fast(hin, Tin, nin, d, nin, no, a.w_split + 2 * (size_t)g.P + g.woff[li],
+                             a.w_split + 3 * (size_t)g.P + g.woff[li], no, bias, y0, Y, no, lane);
       else gm_rows_times_w<true>(hin, Tin, nin, d, nin, no, Wt, no, bias, y0, Y, no, lane);
       for (int k = lane; k < no; k += 32) {
         const S h = act_tanh(y0[k]);
@@ -357,7 +373,10 @@ struct Generic {
     const int nin = g.n[li], no = g.n[li + 1], d = g.d;
     const T* __restrict__ W = gparams(a) + g.woff[li];
     if constexpr (std::is_same<S, float>::value && GPF_GENERIC_MMA) {
-      gm_rows_times_w<true>(ab, Ub, no, d, no, nin, W, nin, nullptr, sc + l.hb[li], sc + l.Tb[li], nin, lane);
+      if (!a.on_chip && a.w_split != nullptr && no % 8 == 0 && nin % 64 == 0 && g.woff[li] % 4 == 0)
+        gm_rows_times_w_fast(ab, Ub, no, d, no, nin, a.w_split + g.woff[li], a.w_split + (size_t)g.P + g.woff[li], nin,
+                             nullptr, sc + l.hb[li], sc + l.Tb[li], nin, lane);
+      else gm_rows_times_w<true>(ab, Ub, no, d, no, nin, W, nin, nullptr, sc + l.hb[li], sc + l.Tb[li], nin, lane);
       return;
     }
     for (int m = lane; m < nin; m += 32) {
@@ -926,7 +945,7 @@ inline GenericPlan generic_plan(const GpFlowDesc* d, int64_t B, int op, int sm_c
   nw = (nw + p.warps_per_cta - 1) / p.warps_per_cta * p.warps_per_cta;  // whole CTAs
   p.nwarps = nw;
   p.partials_bytes = (((size_t)nw * generic_part_stride(g.P) + 4) * es + 255) / 256 * 256;
-  p.params_t_bytes = ((size_t)g.P * es + 255) / 256 * 256;
+  p.params_t_bytes = ((size_t)g.P * es * (es == 4 ? 5 : 1) + 255) / 256 * 256;   // Wt (+ the 4 tf32 split copies in fp32)
   p.scratch_bytes = p.on_chip ? 0 : (size_t)nw * p.scratch_stride;
   p.total = p.partials_bytes + p.params_t_bytes + p.scratch_bytes;
   return p;
@@ -966,7 +985,8 @@ int launch_generic_impl(const GpFlowDesc* d, int op, const T* params, const T* x
   a.t0 = rev ? (T)(d->dt * (double)d->n_steps_nominal) : (T)0;
   a.dt_constraint = (T)d->dt_constraint; a.sigma = (T)d->sigma; a.euler_coef = (T)d->euler_coef;
   a.loss_scale = (T)d->loss_scale;
-  gpflow_transpose_params_kernel<T><<<(a.g.P + 255) / 256, 256, 0, st>>>(a.g, params, pt);
+  a.w_split = sizeof(T) == 4 ? pt + a.g.P : nullptr;
+  gpflow_transpose_params_kernel<T><<<(a.g.P + 255) / 256, 256, 0, st>>>(a.g, params, pt, const_cast<T*>(a.w_split));
   if (cudaGetLastError() != cudaSuccess) return GPFLOW_ERR_CUDA;
   a.on_chip = pl.on_chip;
   a.smem_scratch_off = (unsigned)pl.smem_scratch_off;
