@@ -575,7 +575,7 @@ template <typename T> template <typename S>
 GPF_DEV T Generic<T>::eps_part(const S& a) { return comp<IsDual<S>::value ? 1 : 0>(a); }
 
 // per-warp real-valued work vectors (elements of T), after the scalar scratch
-struct GVec { int xcur, ys, ksum, xb, ybsum, ybprev, kb, ystage, traj, aw, az, ub, total; };
+struct GVec { int xcur, ys, ksum, xb, ybsum, ybprev, kb, ystage, traj, aw, az, ub, stg, total; };
 inline GVec make_gvec(const GDims& g, int n_steps) {
   GVec v;
   int off = 0;
@@ -583,6 +583,7 @@ inline GVec make_gvec(const GDims& g, int n_steps) {
   v.xcur = take(g.d); v.ys = take(g.d); v.ksum = take(g.d); v.xb = take(g.d); v.ybsum = take(g.d);
   v.ybprev = take(g.d); v.kb = take(g.d); v.ystage = take(4 * g.d); v.traj = take((n_steps + 1) * g.d);
   v.aw = take(g.d); v.az = take(g.d); v.ub = take(g.d);
+  v.stg = take(n_steps * 4 * g.d);   // RK4 stage points of every step (kept for the reverse sweep)
   v.total = off;
   return v;
 }
@@ -700,10 +701,13 @@ __global__ void __launch_bounds__(kGenericMaxThreads, 1) gpflow_generic_kernel(c
   T ot_acc = T(0), pen_acc = T(0), lagr_acc = T(0);  // lane-partial sums
 
   T* xcur = vec + vv.xcur; T* ys = vec + vv.ys; T* ksum = vec + vv.ksum; T* xb = vec + vv.xb;
-  T* ybsum = vec + vv.ybsum; T* ybprev = vec + vv.ybprev; T* ystage = vec + vv.ystage; T* traj = vec + vv.traj;
-  T* aw = vec + vv.aw; T* az = vec + vv.az; T* ub = vec + vv.ub;
+  T* ybsum = vec + vv.ybsum; T* ybprev = vec + vv.ybprev; T* pen_tmp = vec + vv.ystage; T* traj = vec + vv.traj;
+  T* aw = vec + vv.aw; T* az = vec + vv.az; T* ub = vec + vv.ub; T* stg = vec + vv.stg;
 
-  for (long long b = gwarp; b < a.B; b += nwarps) {
+  const int wic = threadIdx.x >> 5, wpc = blockDim.x >> 5;
+  for (long long bb = (long long)blockIdx.x * wpc; bb < a.B; bb += nwarps) {
+    if (bb + wic >= a.B) break;
+    const long long b = bb + wic;
     for (int j = lane; j < d; j += 32) {
       const T xi = a.x_in[b * d + j];
       xcur[j] = wrap ? erf_real(xi / sq2s) : xi;
@@ -720,7 +724,10 @@ __global__ void __launch_bounds__(kGenericMaxThreads, 1) gpflow_generic_kernel(c
       __syncwarp();
       for (int sg = 0; sg < 4; ++sg) {
         const T ts = sg == 0 ? t : (sg == 3 ? t + dt : t + hdt);
-        for (int j = lane; j < d; j += 32) sc[l.x + j] = ys[j];
+        for (int j = lane; j < d; j += 32) {
+          sc[l.x + j] = ys[j];
+          if (MODE != MODE_FWD) stg[(i * 4 + sg) * d + j] = ys[j];
+        }
         __syncwarp();
         Generic<T>::template eval_forward<T>(a, sc, ts, bnd, lane);
         const T wk = (sg == 1 || sg == 2) ? T(2) : T(1);
@@ -816,23 +823,13 @@ __global__ void __launch_bounds__(kGenericMaxThreads, 1) gpflow_generic_kernel(c
         const T gq = T(2) * q * pen_w * reg_cot;
         for (int j = lane; j < d; j += 32) ub[j] = gq * zv[j];
         __syncwarp();
-        g_pen_reverse<T>(a, wscr, gacc, xn, wv, ub, ti, bnd, delta, xb, ystage /* scratch 2d */, lane);
+        g_pen_reverse<T>(a, wscr, gacc, xn, wv, ub, ti, bnd, delta, xb, pen_tmp /* scratch 2d */, lane);
         for (int j = lane; j < d; j += 32) ub[j] = -gq * wv[j];
         __syncwarp();
-        g_pen_reverse<T>(a, wscr, gacc, xn, zv, ub, ti, bnd, delta, xb, ystage, lane);
+        g_pen_reverse<T>(a, wscr, gacc, xn, zv, ub, ti, bnd, delta, xb, pen_tmp, lane);
       }
-      const T* x0 = traj + (size_t)i * d;
-      for (int j = lane; j < d; j += 32) ystage[j] = x0[j];
-      __syncwarp();
-      for (int sg = 0; sg < 3; ++sg) {
-        const T ts = sg == 0 ? ti : ti + hdt;
-        for (int j = lane; j < d; j += 32) sc[l.x + j] = ystage[sg * d + j];
-        __syncwarp();
-        Generic<T>::template eval_forward<T>(a, sc, ts, bnd, lane);
-        const T ak = sg == 2 ? dt : hdt;
-        for (int j = lane; j < d; j += 32) ystage[(sg + 1) * d + j] = x0[j] + ak * sc[l.v + j];
-        __syncwarp();
-      }
+      // the four RK4 stage points of step i were kept by the forward sweep (no re-integration of the step)
+      const T* ystage = stg + (size_t)i * 4 * d;
       for (int j = lane; j < d; j += 32) { ybsum[j] = T(0); ybprev[j] = T(0); }
       __syncwarp();
       for (int sg = 3; sg >= 0; --sg) {
@@ -925,8 +922,11 @@ inline GenericPlan generic_plan(const GpFlowDesc* d, int64_t B, int op, int sm_c
   p.vec_offset = ((size_t)l.total * es * (dual ? 2 : 1) + 255) / 256 * 256;
   p.scratch_stride = (p.vec_offset + (size_t)v.total * es + 255) / 256 * 256;
   p.smem_scratch_off = ((size_t)g.P * es + 255) / 256 * 256;
-  p.warps_per_cta = 4;
-  long long nw = (long long)sm_count * 4 * 4;  // 4 CTAs of 4 warps per SM
+  // global mode: 16 warps per SM as CTAs of GPFLOW_GENERIC_WPC warps
+  static const int wpc_env = [] { const char* e = getenv("GPFLOW_GENERIC_WPC"); const int v = e ? atoi(e) : 16;
+                                  return (v == 1 || v == 2 || v == 4 || v == 8 || v == 16) ? v : 16; }();
+  p.warps_per_cta = wpc_env;
+  long long nw = (long long)sm_count * 16;
   static const int on_chip_allowed = [] { const char* e = getenv("GPFLOW_GENERIC_ONCHIP"); return e == nullptr || e[0] != '0'; }();
   if (on_chip_allowed && (size_t)kGenericSmemBudget > p.smem_scratch_off + 12 * p.scratch_stride) {
     int w = (int)(((size_t)kGenericSmemBudget - p.smem_scratch_off) / p.scratch_stride);
