@@ -14,6 +14,8 @@ from .network import GPFlowNetwork  # noqa: F401
 from .host_stream import HostBatchStream  # noqa: F401
 from .optim import FlatAdam  # noqa: F401
 from .bnaf import BNAFMap  # noqa: F401
+from .ffjord import FFJORDMap, gaussian_noise_dataset  # noqa: F401
 
 __all__ = ["FlowConfig", "flow_forward", "flow_backward", "fused_train_step", "kernel_variant", "get_gp_flow",
-           "ResNet", "VelocityField", "VectorField", "GPFlowNetwork", "HostBatchStream", "FlatAdam", "BNAFMap"]
+           "ResNet", "VelocityField", "VectorField", "GPFlowNetwork", "HostBatchStream", "FlatAdam", "BNAFMap", "FFJORDMap",
+           "gaussian_noise_dataset"]

@@ -22,7 +22,8 @@ SCALAR_OT, SCALAR_REG, SCALAR_LAGR, NUM_SCALARS = 0, 1, 2, 3
 EXPORTS = [
     "gpflow_param_count", "gpflow_query_workspace", "gpflow_forward", "gpflow_train_step", "gpflow_backward",
     "gpflow_velocity", "gpflow_kernel_variant", "gpflow_launch_count", "gpflow_fp32_fma_burn", "gpflow_tf32_mma_burn", "gpflow_clock_probe",
-    "gpflow_adam_step", "gpflow_bnaf_param_count", "gpflow_bnaf_forward", "gpflow_error_string",
+    "gpflow_adam_step", "gpflow_bnaf_param_count", "gpflow_bnaf_forward", "gpflow_ffjord_param_count",
+    "gpflow_ffjord_integrate", "gpflow_error_string",
     "gpflow_abi_version",
 ]
 
@@ -31,6 +32,16 @@ class GpFlowBnafDesc(ctypes.Structure):
     """include/gpflow_b200.h: GpFlowBnafDesc."""
     _fields_ = [("abi_version", ctypes.c_int32), ("dtype", ctypes.c_int32), ("dim", ctypes.c_int32),
                 ("hidden_per_dim", ctypes.c_int32), ("n_layers", ctypes.c_int32), ("reserved0", ctypes.c_int32)]
+
+
+FFJORD_MAX_HIDDEN, FFJORD_MAX_BLOCKS = 7, 8
+
+
+class GpFlowFfjordDesc(ctypes.Structure):
+    """include/gpflow_b200.h: GpFlowFfjordDesc."""
+    _fields_ = [("abi_version", ctypes.c_int32), ("dtype", ctypes.c_int32), ("dim", ctypes.c_int32),
+                ("n_hidden", ctypes.c_int32), ("hidden", ctypes.c_int32 * FFJORD_MAX_HIDDEN), ("n_blocks", ctypes.c_int32),
+                ("n_steps", ctypes.c_int32), ("reverse", ctypes.c_int32), ("t_end", ctypes.c_double * FFJORD_MAX_BLOCKS)]
 
 
 class GpFlowDesc(ctypes.Structure):
@@ -94,6 +105,11 @@ def load():
     lib.gpflow_bnaf_param_count.argtypes = [BD, ctypes.POINTER(ctypes.c_int64)]
     lib.gpflow_bnaf_forward.restype = ctypes.c_int
     lib.gpflow_bnaf_forward.argtypes = [BD, ctypes.c_int64, P, P, P, P, P]
+    FD = ctypes.POINTER(GpFlowFfjordDesc)
+    lib.gpflow_ffjord_param_count.restype = ctypes.c_int
+    lib.gpflow_ffjord_param_count.argtypes = [FD, ctypes.POINTER(ctypes.c_int64)]
+    lib.gpflow_ffjord_integrate.restype = ctypes.c_int
+    lib.gpflow_ffjord_integrate.argtypes = [FD, ctypes.c_int64, P, P, P, P, P]
     lib.gpflow_adam_step.restype = ctypes.c_int
     lib.gpflow_adam_step.argtypes = [ctypes.c_int, ctypes.c_int64, P, P, P, P] + [ctypes.c_double] * 5 + [ctypes.c_int64, P]
     lib.gpflow_tf32_mma_burn.restype = ctypes.c_int

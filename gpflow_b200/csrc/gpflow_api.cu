@@ -11,6 +11,7 @@
 
 #include "gpflow_dispatch.h"
 #include "gpflow_bnaf.cuh"
+#include "gpflow_ffjord.cuh"
 
 using namespace gpflow;
 
@@ -371,6 +372,57 @@ int gpflow_bnaf_forward(const GpFlowBnafDesc* d, int64_t B, const void* params, 
   if (reinterpret_cast<uintptr_t>(params) & 3) return GPFLOW_ERR_MISALIGNED;
   return launch_bnaf_forward<2, 16>(d->n_layers, (const float*)params, (const float*)x, (float*)y_out, (float*)logdet_out,
                                     B, reinterpret_cast<cudaStream_t>(stream), device_info().sm_count);
+}
+
+static int ffjord_check(const GpFlowFfjordDesc* d) {
+  if (d == nullptr) return GPFLOW_ERR_NULL_POINTER;
+  if (d->abi_version != GPFLOW_ABI_VERSION || d->dim < 1 || d->n_hidden < 0 || d->n_hidden > GPFLOW_FFJORD_MAX_HIDDEN ||
+      d->n_blocks < 1 || d->n_blocks > GPFLOW_FFJORD_MAX_BLOCKS || d->n_steps < 1 ||
+      (d->dtype != GPFLOW_F32 && d->dtype != GPFLOW_F64))
+    return GPFLOW_ERR_BAD_DESC;
+  for (int l = 0; l < d->n_hidden; ++l)
+    if (d->hidden[l] < 1) return GPFLOW_ERR_BAD_DESC;
+  return GPFLOW_OK;
+}
+
+int gpflow_ffjord_param_count(const GpFlowFfjordDesc* d, int64_t* count) {
+  if (count == nullptr) return GPFLOW_ERR_NULL_POINTER;
+  const int rc = ffjord_check(d);
+  if (rc != GPFLOW_OK) return rc;
+  int64_t n = 0;
+  int in = d->dim;
+  for (int l = 0; l <= d->n_hidden; ++l) {
+    const int out = l < d->n_hidden ? d->hidden[l] : d->dim;
+    n += (int64_t)in * out + 4 * out;
+    in = out;
+  }
+  *count = n * d->n_blocks;
+  return GPFLOW_OK;
+}
+
+int gpflow_ffjord_integrate(const GpFlowFfjordDesc* d, int64_t B, const void* params, const void* x, void* y_out,
+                            void* logdet_out, void* stream) {
+  const int rc = ffjord_check(d);
+  if (rc != GPFLOW_OK) return rc;
+  if (B < 0) return GPFLOW_ERR_BAD_DESC;
+  if (B == 0) return GPFLOW_OK;
+  if (params == nullptr || x == nullptr || y_out == nullptr) return GPFLOW_ERR_NULL_POINTER;
+  const size_t es = d->dtype == GPFLOW_F64 ? 8 : 4;
+  const void* all[] = {params, x, y_out, logdet_out};
+  for (const void* q : all)
+    if (q != nullptr && (reinterpret_cast<uintptr_t>(q) % es) != 0) return GPFLOW_ERR_MISALIGNED;
+  FfjordArgs a;
+  a.params = params; a.x = x; a.y = y_out; a.logdet = logdet_out; a.B = B;
+  a.d = d->dim; a.n_linear = d->n_hidden + 1; a.n_blocks = d->n_blocks; a.n_steps = d->n_steps; a.reverse = d->reverse != 0;
+  a.width[0] = d->dim;
+  for (int l = 0; l < d->n_hidden; ++l) a.width[l + 1] = d->hidden[l];
+  a.width[d->n_hidden + 1] = d->dim;
+  for (int l = d->n_hidden + 2; l <= kFfjMaxLinear; ++l) a.width[l] = 0;
+  for (int b = 0; b < kFfjMaxBlocks; ++b) a.t_end[b] = b < d->n_blocks ? d->t_end[b] : 0.0;
+  const size_t smem_limit = 227 * 1024;
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  return d->dtype == GPFLOW_F64 ? launch_ffjord<double>(a, st, device_info().sm_count, smem_limit)
+                                : launch_ffjord<float>(a, st, device_info().sm_count, smem_limit);
 }
 
 const char* gpflow_error_string(int status) {

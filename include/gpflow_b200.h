@@ -199,6 +199,36 @@ int gpflow_bnaf_param_count(const GpFlowBnafDesc* desc, int64_t* count);
 int gpflow_bnaf_forward(const GpFlowBnafDesc* desc, int64_t B, const void* params, const void* x, void* y_out,
                         void* logdet_out, void* cuda_stream);
 
+/* The frozen FFJORD map either side of the GP flow: `FFJORD.forward(x) -> (z, log_det)` --
+ * `x_map, log_det = self.map(x)` of `Network.loss_gp_flow` (src/gp_flows/network.py:76-78, flow_models/ffjord/ffjord.py:50-53)
+ * -- and `FFJORD.backward(z) -> x` (ffjord.py:55-56), the `map.backward` that builds the Gaussian-noise training set
+ * (src/data_module.py:161-186).  The map is a chain of `n_blocks` CNF blocks (layers/container.py:14-26, layers/cnf.py:44-98)
+ * whose vector field is an ODEnet of `n_hidden + 1` ConcatSquashLinear layers with tanh in between
+ * (layers/odefunc.py:160-174, layers/diffeq_layers/basic.py:76-86); log_det integrates the exact trace of df/dy
+ * (`divergence_bf`, odefunc.py:13-17).  Each block is integrated over [0, t_end[b]] (reverse: blocks in reverse order,
+ * each over [t_end[b], 0]) with `n_steps` classical RK4 steps; the reference's adaptive torchdiffeq dopri5 is not
+ * reproduced (see oracle/ffjord_oracle.py).
+ * `params` = for each block, for each layer: `_layer.weight [out][in]`, `_layer.bias [out]`, `_hyper_bias.weight [out]`,
+ * `_hyper_gate.weight [out]`, `_hyper_gate.bias [out]` (state_dict order).  Writes y_out [B, dim] and, if not NULL,
+ * logdet_out [B] (log|det dy/dx| of the direction integrated).  One launch, no workspace.  Shapes whose per-thread
+ * state does not fit in shared memory return GPFLOW_ERR_UNSUPPORTED. */
+#define GPFLOW_FFJORD_MAX_HIDDEN 7
+#define GPFLOW_FFJORD_MAX_BLOCKS 8
+typedef struct GpFlowFfjordDesc {
+  int32_t abi_version;     /* GPFLOW_ABI_VERSION */
+  int32_t dtype;           /* GPFLOW_F32 / GPFLOW_F64 */
+  int32_t dim;
+  int32_t n_hidden;        /* hidden layers of the ODEnet, 0..GPFLOW_FFJORD_MAX_HIDDEN */
+  int32_t hidden[GPFLOW_FFJORD_MAX_HIDDEN];
+  int32_t n_blocks;        /* CNF blocks, 1..GPFLOW_FFJORD_MAX_BLOCKS */
+  int32_t n_steps;         /* RK4 steps per block */
+  int32_t reverse;         /* 0: FFJORD.forward, 1: FFJORD.backward */
+  double t_end[GPFLOW_FFJORD_MAX_BLOCKS]; /* sqrt_end_time^2 of each block (cnf.py:49-52) */
+} GpFlowFfjordDesc;
+int gpflow_ffjord_param_count(const GpFlowFfjordDesc* desc, int64_t* count);
+int gpflow_ffjord_integrate(const GpFlowFfjordDesc* desc, int64_t B, const void* params, const void* x, void* y_out,
+                            void* logdet_out, void* cuda_stream);
+
 const char* gpflow_error_string(int status);
 int gpflow_abi_version(void);
 
