@@ -179,3 +179,31 @@ def test_ffjord_errors():
         G.FFJORDMap(spec.d, spec.hidden, spec.n_blocks, torch.zeros(5))
     z, ld = m(torch.zeros(0, spec.d).cuda())
     assert z.shape == (0, spec.d) and ld.shape == (0,)
+
+
+@pytest.mark.gpu
+def test_c3_pipeline_dataset_to_train_step():
+    """C3 end to end on the device: Gaussian points -> FFJORDMap.backward (data set) -> FFJORDMap.map_only (x_map) ->
+    fused GP-flow train step at the dsprites-latent shape (d=10, nb=9, H=[50,50,50], N=15), every stage against its oracle."""
+    _need_cuda()
+    import gpflow_b200 as G
+    import gpflow_oracle as O
+    g, fspec = _golden("f32")
+    m = _map(g, fspec, n_steps=32)
+    fspec.n_steps = 32
+    gauss = torch.randn(192, fspec.d, generator=torch.Generator().manual_seed(21))
+    x_data = m.backward(gauss.cuda())
+    x_map = m.map_only(x_data)
+    fp = torch.from_numpy(g["params"]).double()
+    xo, _ = FO.integrate(fp, gauss.double(), fspec, reverse=True)
+    assert _rel(x_data.cpu().double(), xo) < 1e-5
+    zo, _ = FO.integrate(fp, x_data.cpu().double(), fspec)
+    assert _rel(x_map.cpu().double(), zo) < 1e-5
+    assert _rel(x_map.cpu(), gauss) < 1e-3            # round trip up to the 32-step integrator error
+    spec = O.FlowSpec(d=10, nb=9, hidden=[50, 50, 50], n_steps=15)
+    cfg = G.FlowConfig(d=10, nb=9, hidden=(50, 50, 50), n_steps=15)
+    params = O.init_params(spec, 0.05, 0, torch.float32)
+    res = G.fused_train_step(cfg, O.flatten_params(params).cuda(), x_data, x_map)
+    ref = O.train_step([p.double() for p in params], x_data.cpu().double(), x_map.cpu().double(), spec)
+    assert abs(float(res["scalars"][0]) - float(ref["ot"])) < 1e-5 * abs(float(ref["ot"]))
+    assert _rel(res["grads"].cpu().double(), ref["grads"]) < 1e-5
