@@ -29,6 +29,7 @@ constexpr int kGenericSmemBudget = 226 * 1024;
 
 struct GDims {
   int d, nb, L, nout, P;
+  int Ps;               // P rounded up to 4: stride of the tf32-split weight copies (keeps them 16-byte aligned)
   int n[GMAXL + 1];     // widths: n[0] = d+1, n[1..L] hidden, n[L+1] = nout
   int woff[GMAXL];      // offset of W_li in the flat parameters, li = 0..L  (row-major [n[li+1]][n[li]])
   int boff[GMAXL];
@@ -53,6 +54,7 @@ inline GDims make_gdims(const GpFlowDesc* d) {
     g.boff[li] = off; off += g.n[li + 1];
   }
   g.P = off;
+  g.Ps = (off + 3) / 4 * 4;
   return g;
 }
 inline GLayout make_glayout(const GDims& g) {
@@ -112,9 +114,9 @@ __global__ void gpflow_transpose_params_kernel(GDims g, const T* __restrict__ p,
       uint32_t hi, lo;
       tf32_split(p[i], hi, lo);
       split[i] = __uint_as_float(hi);
-      split[(size_t)g.P + i] = __uint_as_float(lo);
-      split[2 * (size_t)g.P + it] = __uint_as_float(hi);
-      split[3 * (size_t)g.P + it] = __uint_as_float(lo);
+      split[(size_t)g.Ps + i] = __uint_as_float(lo);
+      split[2 * (size_t)g.Ps + it] = __uint_as_float(hi);
+      split[3 * (size_t)g.Ps + it] = __uint_as_float(lo);
     }
   }
 }
@@ -185,8 +187,8 @@ struct Generic {
       S* Y = sc + l.U[li + 1];
       if (a.on_chip) gm_rows_times_w<false>(hin, Tin, nin, d, nin, no, gparams(a) + g.woff[li], nin, bias, y0, Y, no, lane);
       else if (a.w_split != nullptr && nin % 8 == 0 && no % 64 == 0 && g.woff[li] % 4 == 0)
-        gm_rows_times_w_fast(hin, Tin, nin, d, nin, no, a.w_split + 2 * (size_t)g.P + g.woff[li],
-                             a.w_split + 3 * (size_t)g.P + g.woff[li], no, bias, y0, Y, no, lane);
+        gm_rows_times_w_fast(hin, Tin, nin, d, nin, no, a.w_split + 2 * (size_t)g.Ps + g.woff[li],
+                             a.w_split + 3 * (size_t)g.Ps + g.woff[li], no, bias, y0, Y, no, lane);
       else gm_rows_times_w<true>(hin, Tin, nin, d, nin, no, Wt, no, bias, y0, Y, no, lane);
       for (int k = lane; k < no; k += 32) {
         const S h = act_tanh(y0[k]);
@@ -374,7 +376,7 @@ struct Generic {
     const T* __restrict__ W = gparams(a) + g.woff[li];
     if constexpr (std::is_same<S, float>::value && GPF_GENERIC_MMA) {
       if (!a.on_chip && a.w_split != nullptr && no % 8 == 0 && nin % 64 == 0 && g.woff[li] % 4 == 0)
-        gm_rows_times_w_fast(ab, Ub, no, d, no, nin, a.w_split + g.woff[li], a.w_split + (size_t)g.P + g.woff[li], nin,
+        gm_rows_times_w_fast(ab, Ub, no, d, no, nin, a.w_split + g.woff[li], a.w_split + (size_t)g.Ps + g.woff[li], nin,
                              nullptr, sc + l.hb[li], sc + l.Tb[li], nin, lane);
       else gm_rows_times_w<true>(ab, Ub, no, d, no, nin, W, nin, nullptr, sc + l.hb[li], sc + l.Tb[li], nin, lane);
       return;
@@ -945,7 +947,7 @@ inline GenericPlan generic_plan(const GpFlowDesc* d, int64_t B, int op, int sm_c
   nw = (nw + p.warps_per_cta - 1) / p.warps_per_cta * p.warps_per_cta;  // whole CTAs
   p.nwarps = nw;
   p.partials_bytes = (((size_t)nw * generic_part_stride(g.P) + 4) * es + 255) / 256 * 256;
-  p.params_t_bytes = ((size_t)g.P * es * (es == 4 ? 5 : 1) + 255) / 256 * 256;   // Wt (+ the 4 tf32 split copies in fp32)
+  p.params_t_bytes = ((size_t)g.Ps * es * (es == 4 ? 5 : 1) + 255) / 256 * 256;   // Wt (+ the 4 tf32 split copies in fp32)
   p.scratch_bytes = p.on_chip ? 0 : (size_t)nw * p.scratch_stride;
   p.total = p.partials_bytes + p.params_t_bytes + p.scratch_bytes;
   return p;
@@ -985,7 +987,7 @@ int launch_generic_impl(const GpFlowDesc* d, int op, const T* params, const T* x
   a.t0 = rev ? (T)(d->dt * (double)d->n_steps_nominal) : (T)0;
   a.dt_constraint = (T)d->dt_constraint; a.sigma = (T)d->sigma; a.euler_coef = (T)d->euler_coef;
   a.loss_scale = (T)d->loss_scale;
-  a.w_split = sizeof(T) == 4 ? pt + a.g.P : nullptr;
+  a.w_split = sizeof(T) == 4 ? pt + a.g.Ps : nullptr;
   gpflow_transpose_params_kernel<T><<<(a.g.P + 255) / 256, 256, 0, st>>>(a.g, params, pt, const_cast<T*>(a.w_split));
   if (cudaGetLastError() != cudaSuccess) return GPFLOW_ERR_CUDA;
   a.on_chip = pl.on_chip;

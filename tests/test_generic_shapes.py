@@ -21,6 +21,8 @@ SHAPES = [
     (12, 12, (33, 31), 9, 0.03),         # nb = d, odd widths
     (20, 4, (128, 128), 300, 0.012),     # does not fit on chip -> global scratch; vec4; several n-blocks of 64 columns
     (2, 1, (15, 15), 70, 0.12),          # the sf2 shape through the generic kernel
+    (3, 2, (64, 64), 150, 0.04),         # aligned mma fast path with P % 4 == 2 (regression: split copies misaligned)
+    (10, 9, (64, 64, 64), 40, 0.03),     # the zero-padded C3 shape: fast path, P = 14938
 ]
 
 
