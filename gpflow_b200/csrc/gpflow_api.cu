@@ -296,7 +296,8 @@ int gpflow_launch_count(const GpFlowDesc* d, int op) {
   if (validate(d) != GPFLOW_OK) return -1;
   (void)op;
   SmallShape s;
-  return small_match(d, &s) ? 2 : 3;  // [weight transpose +] main kernel + deterministic finalize
+  if (small_match(d, &s)) return 2;            // main kernel + deterministic finalize
+  return generic_runs_padded(d) ? 4 : 3;       // [zero-padding scatter +] weight transpose + main kernel + finalize
 }
 
 int gpflow_fp32_fma_burn(int64_t iters, void* sink, double* host_flops_out, void* stream) {

@@ -51,5 +51,6 @@ GPF_DECL_GENERIC(generic_f64, double);
 GPF_DECL_GENERIC(generic_f64_euler, double);
 
 size_t generic_workspace_bytes(const GpFlowDesc* d, int64_t B, int op);
+bool generic_runs_padded(const GpFlowDesc* d);   // hidden widths zero-padded to the aligned mma shape (one more launch)
 
 }  // namespace gpflow

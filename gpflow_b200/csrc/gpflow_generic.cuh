@@ -95,6 +95,68 @@ struct GArgs {
   T dt, t0, dt_constraint, sigma, euler_coef, loss_scale, t_eval;
 };
 
+// ---- zero-padding of the hidden widths to the aligned tensor-core shape (fp32, no Euler) ----
+// A hidden unit with zero incoming weights, zero bias and zero outgoing weights is exactly inert (h = tanh(0) = 0, its
+// tangent row is 0, every adjoint that reaches it is multiplied by a zero weight), so a network whose hidden widths are
+// rounded up to a multiple of 64 computes the same flow and the same gradients for the original parameters.  The aligned
+// mma fast paths (pre-split weights, 128-bit operand loads, no bounds predicates) and the 128-bit last-layer passes need
+// exactly that shape; measured at C3 (d=10, nb=9, H=[50,50,50] -> [64,64,64], B = 2^14): 242 -> 184 ms per train step.
+// Applied when it costs at most 30 % more units per layer; GPFLOW_GENERIC_PAD=0 disables it (A/B measurements).
+inline bool generic_padded_desc(const GpFlowDesc* d, GpFlowDesc* out) {
+  static const int allowed = [] { const char* e = getenv("GPFLOW_GENERIC_PAD"); return e == nullptr || e[0] != '0'; }();
+  *out = *d;
+  if (!allowed || d->dtype != GPFLOW_F32 || d->n_hidden < 2 || (d->flags & GPFLOW_FLAG_EULER_PEN) || !GPF_GENERIC_MMA)
+    return false;
+  bool changed = false;
+  for (int l = 0; l < d->n_hidden; ++l) {
+    const int h = d->hidden[l], hp = (h + 63) / 64 * 64;
+    if (hp == h) continue;
+    if (10 * hp > 13 * h) return false;
+    out->hidden[l] = hp;
+    changed = true;
+  }
+  return changed;
+}
+
+// scatter the caller's flat parameters into the (pre-zeroed) padded layout; map[i] = padded index of parameter i
+template <typename T>
+__global__ void gpflow_pad_params_kernel(GDims g, GDims gp, const T* __restrict__ p, T* __restrict__ pp, int* __restrict__ map) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= g.P) return;
+  int idx = 0;
+  for (int li = 0; li <= g.L; ++li) {
+    const int nin = g.n[li], no = g.n[li + 1];
+    if (i >= g.woff[li] && i < g.woff[li] + nin * no) {
+      const int e = i - g.woff[li], k = e / nin, m = e - k * nin;
+      idx = gp.woff[li] + k * gp.n[li] + m;
+      break;
+    }
+    if (i >= g.boff[li] && i < g.boff[li] + no) {
+      idx = gp.boff[li] + (i - g.boff[li]);
+      break;
+    }
+  }
+  pp[idx] = p[i];
+  map[i] = idx;
+}
+
+// gpflow_finalize_kernel with the gradients gathered back from the padded layout
+template <typename T>
+__global__ void gpflow_finalize_mapped_kernel(const T* __restrict__ partials, int n_cta, int npart, int count,
+                                              const int* __restrict__ map, T* __restrict__ scalars_out,
+                                              T* __restrict__ grads_out) {
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= count) return;
+  const int src = e < 3 ? e : 3 + map[e - 3];
+  T s = T(0);
+  for (int c = 0; c < n_cta; ++c) s += partials[(size_t)c * npart + src];
+  if (e < 3) {
+    if (scalars_out != nullptr) scalars_out[e] = s;
+  } else if (grads_out != nullptr) {
+    grads_out[e - 3] = s;
+  }
+}
+
 template <typename T>
 __global__ void gpflow_transpose_params_kernel(GDims g, const T* __restrict__ p, T* __restrict__ pt, T* __restrict__ split) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -952,17 +1014,37 @@ inline GenericPlan generic_plan(const GpFlowDesc* d, int64_t B, int op, int sm_c
   p.total = p.partials_bytes + p.params_t_bytes + p.scratch_bytes;
   return p;
 }
+inline size_t generic_pad_bytes(const GpFlowDesc* d, const GpFlowDesc* dp) {   // [padded params | index map]
+  return ((size_t)make_gdims(dp).P * 4 + 255) / 256 * 256 + ((size_t)make_gdims(d).P * 4 + 255) / 256 * 256;
+}
 inline size_t generic_workspace(const GpFlowDesc* d, int64_t B, int op) {
+  GpFlowDesc dp;
+  if (generic_padded_desc(d, &dp)) return generic_plan(&dp, B, op, 160).total + generic_pad_bytes(d, &dp);
   return generic_plan(d, B, op, 160).total;  // device-independent upper bound (B200 has 148 SMs)
 }
 
 template <typename T, bool EULER>
-int launch_generic_impl(const GpFlowDesc* d, int op, const T* params, const T* x_in, const T* x_data, const T* grad_y,
+int launch_generic_impl(const GpFlowDesc* d_user, int op, const T* params, const T* x_in, const T* x_data, const T* grad_y,
                    const T* reg_cot, const T* zw, T* y_out, T* logdet_out, T* traj_out, T* grad_x_out, T* grads_out,
                    T* scalars_out, int64_t B, void* ws, size_t wsb, cudaStream_t st, int sm_count, T* v_out,
                    double t_eval) {
-  if (ws == nullptr || wsb < generic_workspace(d, B, op)) return GPFLOW_ERR_WORKSPACE;
+  if (ws == nullptr || wsb < generic_workspace(d_user, B, op)) return GPFLOW_ERR_WORKSPACE;
   if (reinterpret_cast<uintptr_t>(ws) & 15) return GPFLOW_ERR_MISALIGNED;
+  GpFlowDesc d_pad;
+  const bool padded = !EULER && generic_padded_desc(d_user, &d_pad);
+  const GpFlowDesc* d = padded ? &d_pad : d_user;
+  const int* pad_map = nullptr;
+  if (padded) {   // the padded parameters and the index map live at the END of the workspace
+    const GDims g0 = make_gdims(d_user), gp = make_gdims(d);
+    char* tail = reinterpret_cast<char*>(ws) + generic_plan(d, B, op, 160).total;
+    T* pp = reinterpret_cast<T*>(tail);
+    int* map = reinterpret_cast<int*>(tail + ((size_t)gp.P * 4 + 255) / 256 * 256);
+    if (cudaMemsetAsync(pp, 0, (size_t)gp.P * sizeof(T), st) != cudaSuccess) { cudaGetLastError(); return GPFLOW_ERR_CUDA; }
+    gpflow_pad_params_kernel<T><<<(g0.P + 255) / 256, 256, 0, st>>>(g0, gp, params, pp, map);
+    if (cudaGetLastError() != cudaSuccess) return GPFLOW_ERR_CUDA;
+    params = pp;
+    pad_map = map;
+  }
   const GenericPlan pl = generic_plan(d, B, op, sm_count);
   GKernelArgs<T> ka;
   memset(&ka, 0, sizeof(ka));
@@ -1011,10 +1093,14 @@ int launch_generic_impl(const GpFlowDesc* d, int op, const T* params, const T* x
   else if (op == GPFLOW_OP_TRAIN_STEP) rc = launch(gpflow_generic_kernel<T, MODE_TRAIN, EULER>);
   else rc = launch(gpflow_generic_kernel<T, MODE_BWD, EULER>);
   if (rc != GPFLOW_OK) return rc;
-  const int count = op == GPFLOW_OP_FORWARD ? 3 : 3 + a.g.P;
+  const int count = op == GPFLOW_OP_FORWARD ? 3 : 3 + make_gdims(d_user).P;
   if (scalars_out != nullptr || grads_out != nullptr) {
-    gpflow_finalize_kernel<T><<<(count + 127) / 128, 128, 0, st>>>(a.partials, (int)pl.nwarps, a.npart, count,
-                                                                   scalars_out, grads_out);
+    if (padded)
+      gpflow_finalize_mapped_kernel<T><<<(count + 127) / 128, 128, 0, st>>>(a.partials, (int)pl.nwarps, a.npart, count,
+                                                                          pad_map, scalars_out, grads_out);
+    else
+      gpflow_finalize_kernel<T><<<(count + 127) / 128, 128, 0, st>>>(a.partials, (int)pl.nwarps, a.npart, count,
+                                                                     scalars_out, grads_out);
     if (cudaGetLastError() != cudaSuccess) return GPFLOW_ERR_CUDA;
   }
   return GPFLOW_OK;

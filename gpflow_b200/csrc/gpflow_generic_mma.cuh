@@ -114,37 +114,72 @@ GPF_DEV void gm_rows_times_w(const float* __restrict__ x0, const float* __restri
 }
 
 // gw[k * N + m] += sum_{r <= d} Yb[r][k] * X[r][m], k < M (outputs), m < N (inputs); rows as in row_elem.
-GPF_DEV void gm_weight_grad(const float* __restrict__ yb0, const float* __restrict__ Yb, int ldyb, const float* __restrict__ x0,
-                            const float* __restrict__ X, int ldx, int d, int M, int N, float* __restrict__ gw, int lane) {
+// KS > 0: the 1 + d rows fit in KS k-steps of 8 (d <= 8 KS - 1): the A fragments of a 16-output strip (already split into
+// tf32 hi / lo) are fetched once and kept in registers across all the m-tiles of the strip.  KS = 0: any d.
+template <int KS>
+GPF_DEV void gm_weight_grad_impl(const float* __restrict__ yb0, const float* __restrict__ Yb, int ldyb,
+                                 const float* __restrict__ x0, const float* __restrict__ X, int ldx, int d, int M, int N,
+                                 float* __restrict__ gw, int lane) {
   const int g = lane >> 2, t = lane & 3;
   const int R = d + 1;
+  const bool full_m = (N & 7) == 0;
   for (int k0 = 0; k0 < M; k0 += 16) {
+    uint32_t Ah[KS > 0 ? KS : 1][4], Al[KS > 0 ? KS : 1][4];
+    if (KS > 0) {
+#pragma unroll
+      for (int s = 0; s < KS; ++s) {
+        const int r0 = 8 * s;
+        tf32_split(row_elem(yb0, Yb, ldyb, d, r0 + t, k0 + g, M), Ah[s][0], Al[s][0]);
+        tf32_split(row_elem(yb0, Yb, ldyb, d, r0 + t, k0 + g + 8, M), Ah[s][1], Al[s][1]);
+        tf32_split(row_elem(yb0, Yb, ldyb, d, r0 + t + 4, k0 + g, M), Ah[s][2], Al[s][2]);
+        tf32_split(row_elem(yb0, Yb, ldyb, d, r0 + t + 4, k0 + g + 8, M), Ah[s][3], Al[s][3]);
+      }
+    }
+    const bool full_k = k0 + 16 <= M;
     for (int m0 = 0; m0 < N; m0 += 8) {
       float c[4] = {0.0f, 0.0f, 0.0f, 0.0f}, go[4];
+      const bool full = full_k && full_m;
 #pragma unroll
       for (int q = 0; q < 4; ++q) {  // the accumulator's old values travel while the tile is computed
         const int k = k0 + g + ((q & 2) ? 8 : 0), m = m0 + 2 * t + (q & 1);
-        go[q] = (k < M && m < N) ? gw[k * N + m] : 0.0f;
+        go[q] = (full || (k < M && m < N)) ? gw[k * N + m] : 0.0f;
       }
-      for (int r0 = 0; r0 < R; r0 += 8) {
-        uint32_t ah[4], al[4], bh[2], bl[2];
-        // A[k][r] = Yb[r][k]
-        tf32_split(row_elem(yb0, Yb, ldyb, d, r0 + t, k0 + g, M), ah[0], al[0]);
-        tf32_split(row_elem(yb0, Yb, ldyb, d, r0 + t, k0 + g + 8, M), ah[1], al[1]);
-        tf32_split(row_elem(yb0, Yb, ldyb, d, r0 + t + 4, k0 + g, M), ah[2], al[2]);
-        tf32_split(row_elem(yb0, Yb, ldyb, d, r0 + t + 4, k0 + g + 8, M), ah[3], al[3]);
-        // B[r][m] = X[r][m]
-        tf32_split(row_elem(x0, X, ldx, d, r0 + t, m0 + g, N), bh[0], bl[0]);
-        tf32_split(row_elem(x0, X, ldx, d, r0 + t + 4, m0 + g, N), bh[1], bl[1]);
-        mma_3xtf32(c, ah, al, bh, bl);
+      if (KS > 0) {
+#pragma unroll
+        for (int s = 0; s < KS; ++s) {
+          const int r0 = 8 * s;
+          uint32_t bh[2], bl[2];
+          tf32_split(row_elem(x0, X, ldx, d, r0 + t, m0 + g, N), bh[0], bl[0]);
+          tf32_split(row_elem(x0, X, ldx, d, r0 + t + 4, m0 + g, N), bh[1], bl[1]);
+          mma_3xtf32(c, Ah[s], Al[s], bh, bl);
+        }
+      } else {
+        for (int r0 = 0; r0 < R; r0 += 8) {
+          uint32_t ah[4], al[4], bh[2], bl[2];
+          // A[k][r] = Yb[r][k]
+          tf32_split(row_elem(yb0, Yb, ldyb, d, r0 + t, k0 + g, M), ah[0], al[0]);
+          tf32_split(row_elem(yb0, Yb, ldyb, d, r0 + t, k0 + g + 8, M), ah[1], al[1]);
+          tf32_split(row_elem(yb0, Yb, ldyb, d, r0 + t + 4, k0 + g, M), ah[2], al[2]);
+          tf32_split(row_elem(yb0, Yb, ldyb, d, r0 + t + 4, k0 + g + 8, M), ah[3], al[3]);
+          // B[r][m] = X[r][m]
+          tf32_split(row_elem(x0, X, ldx, d, r0 + t, m0 + g, N), bh[0], bl[0]);
+          tf32_split(row_elem(x0, X, ldx, d, r0 + t + 4, m0 + g, N), bh[1], bl[1]);
+          mma_3xtf32(c, ah, al, bh, bl);
+        }
       }
 #pragma unroll
       for (int q = 0; q < 4; ++q) {
         const int k = k0 + g + ((q & 2) ? 8 : 0), m = m0 + 2 * t + (q & 1);
-        if (k < M && m < N) gw[k * N + m] = go[q] + c[q];
+        if (full || (k < M && m < N)) gw[k * N + m] = go[q] + c[q];
       }
     }
   }
+}
+GPF_DEV void gm_weight_grad(const float* __restrict__ yb0, const float* __restrict__ Yb, int ldyb, const float* __restrict__ x0,
+                            const float* __restrict__ X, int ldx, int d, int M, int N, float* __restrict__ gw, int lane) {
+  if (d <= 7) gm_weight_grad_impl<1>(yb0, Yb, ldyb, x0, X, ldx, d, M, N, gw, lane);
+  else if (d <= 15) gm_weight_grad_impl<2>(yb0, Yb, ldyb, x0, X, ldx, d, M, N, gw, lane);
+  else gm_weight_grad_impl<0>(yb0, Yb, ldyb, x0, X, ldx, d, M, N, gw, lane);
 }
 
 // ---------------------------------------------------------------------------------------------------

@@ -7,4 +7,8 @@ GPF_DECL_GENERIC(generic_f32, float) {
                                       grad_x_out, grads_out, scalars_out, B, ws, wsb, st, sm_count, v_out, t_eval);
 }
 size_t generic_workspace_bytes(const GpFlowDesc* d, int64_t B, int op) { return generic_workspace(d, B, op); }
+bool generic_runs_padded(const GpFlowDesc* d) {
+  GpFlowDesc dp;
+  return generic_padded_desc(d, &dp);
+}
 }  // namespace gpflow

@@ -23,6 +23,8 @@ SHAPES = [
     (2, 1, (15, 15), 70, 0.12),          # the sf2 shape through the generic kernel
     (3, 2, (64, 64), 150, 0.04),         # aligned mma fast path with P % 4 == 2 (regression: split copies misaligned)
     (10, 9, (64, 64, 64), 40, 0.03),     # the zero-padded C3 shape: fast path, P = 14938
+    (10, 9, (50, 50, 50), 40, 0.03),     # C3: runs zero-padded to [64,64,64] (fp32), gradients gathered back
+    (6, 3, (50, 100), 33, 0.04),         # zero-padded to [64,128] (fp32)
 ]
 
 
