@@ -74,13 +74,16 @@ __host__ __device__ inline FfjordPlan ffjord_plan(const int* width, int n_linear
   return p;
 }
 
-GPF_DEV void ffj_load8(const float* p, float (&w)[8]) {
-  const float4 a = *reinterpret_cast<const float4*>(p), b = *reinterpret_cast<const float4*>(p + 4);
-  w[0] = a.x; w[1] = a.y; w[2] = a.z; w[3] = a.w; w[4] = b.x; w[5] = b.y; w[6] = b.z; w[7] = b.w;
-}
-GPF_DEV void ffj_load8(const double* p, double (&w)[8]) {
+template <int OB> GPF_DEV void ffj_loadw(const float* p, float (&w)[OB]) {   // OB consecutive weights, 16-byte aligned
 #pragma unroll
-  for (int i = 0; i < 4; ++i) {
+  for (int i = 0; i < OB / 4; ++i) {
+    const float4 a = *reinterpret_cast<const float4*>(p + 4 * i);
+    w[4 * i] = a.x; w[4 * i + 1] = a.y; w[4 * i + 2] = a.z; w[4 * i + 3] = a.w;
+  }
+}
+template <int OB> GPF_DEV void ffj_loadw(const double* p, double (&w)[OB]) {
+#pragma unroll
+  for (int i = 0; i < OB / 2; ++i) {
     const double2 a = *reinterpret_cast<const double2*>(p + 2 * i);
     w[2 * i] = a.x; w[2 * i + 1] = a.y;
   }
@@ -96,50 +99,88 @@ GPF_DEV double ffj_tanh(double x) { return tanh(x); }
 GPF_DEV float ffj_sigmoid(float z) { return 1.0f / (1.0f + expf(-z)); }
 GPF_DEV double ffj_sigmoid(double z) { return 1.0 / (1.0 + exp(-z)); }
 
-// out_col[o] = act( (W in + b)[o] * gate[o] + hbt[o] ), o < outp (padded outputs come out as act(0)); BIAS = false gives
+// out_col[o] = act( (W in + b)[o] * gate[o] + hbt[o] ), o < outp (padded outputs come out as act(0)); TANGENT gives
 // the tangent form  out_col[o] = (1 - h[o]^2) * gate[o] * (W in)[o]  with h = `h_col` (hidden layers only).
-template <typename T, bool TANGENT>
-GPF_DEV void ffj_matvec(const T* __restrict__ Wt, const T* __restrict__ vec, int in, int outp, const T* in_col,
-                        T* out_col, const T* h_col, bool hidden, int NT) {
+// A thread owns S samples (columns `q * NTH` apart, column stride VT = S * NTH) and OB outputs per register block, so a
+// k-step is S activation loads + OB/4 warp-uniform 128-bit weight loads (2 shared-memory wavefronts each) for S * OB
+// FMAs: with S = 1 the LSU data pipe caps the FMA pipe at ~45 % (ncu: 66 % LSU wavefronts at 28 % FMA), S = 2 halves
+// the weight traffic per FMA.  The operands of k-step k+1 are fetched before the FMAs of k-step k issue (register double
+// buffer); addresses advance by pointer increments.
+template <typename T, int S, int OB, bool TANGENT>
+GPF_DEV void ffj_matvec_ob(const T* __restrict__ Wt, const T* __restrict__ vec, int in, int outp, const T* in_col,
+                           T* out_col, const T* h_col, bool hidden, int NTH, int VT) {
   const T* b = vec;
   const T* gate = vec + 4 * outp;
   const T* hbt = vec + 5 * outp;
-  for (int o0 = 0; o0 < outp; o0 += kFfjOB) {
-    T acc[kFfjOB];
+  for (int o0 = 0; o0 < outp; o0 += OB) {
+    T acc[S][OB];
 #pragma unroll
-    for (int i = 0; i < kFfjOB; ++i) acc[i] = TANGENT ? T(0) : b[o0 + i];
-    const T* wp = Wt + o0;
-#pragma unroll 4
-    for (int k = 0; k < in; ++k) {
-      const T hk = in_col[k * NT];
-      T w[kFfjOB];
-      ffj_load8(wp + k * outp, w);
+    for (int q = 0; q < S; ++q)
 #pragma unroll
-      for (int i = 0; i < kFfjOB; ++i) acc[i] = fma(w[i], hk, acc[i]);
+      for (int i = 0; i < OB; ++i) acc[q][i] = TANGENT ? T(0) : b[o0 + i];
+    const T* ip = in_col;
+    const T* wq = Wt + o0;
+    T hc[S], wc[OB];
+#pragma unroll
+    for (int q = 0; q < S; ++q) hc[q] = ip[q * NTH];
+    ffj_loadw<OB>(wq, wc);
+#pragma unroll 2
+    for (int k = 1; k < in; ++k) {
+      ip += VT;
+      wq += outp;
+      T hn[S], wn[OB];
+#pragma unroll
+      for (int q = 0; q < S; ++q) hn[q] = ip[q * NTH];
+      ffj_loadw<OB>(wq, wn);
+#pragma unroll
+      for (int q = 0; q < S; ++q)
+#pragma unroll
+        for (int i = 0; i < OB; ++i) acc[q][i] = fma(wc[i], hc[q], acc[q][i]);
+#pragma unroll
+      for (int q = 0; q < S; ++q) hc[q] = hn[q];
+#pragma unroll
+      for (int i = 0; i < OB; ++i) wc[i] = wn[i];
     }
 #pragma unroll
-    for (int i = 0; i < kFfjOB; ++i) {
-      T r;
-      if (TANGENT) {
-        const T h = h_col[(o0 + i) * NT];
-        r = (T(1) - h * h) * (gate[o0 + i] * acc[i]);
-      } else {
-        r = acc[i] * gate[o0 + i] + hbt[o0 + i];
-        if (hidden) r = ffj_tanh(r);
+    for (int q = 0; q < S; ++q)
+#pragma unroll
+      for (int i = 0; i < OB; ++i) acc[q][i] = fma(wc[i], hc[q], acc[q][i]);
+#pragma unroll
+    for (int i = 0; i < OB; ++i) {
+      const T gt = gate[o0 + i], hb = TANGENT ? T(0) : hbt[o0 + i];
+#pragma unroll
+      for (int q = 0; q < S; ++q) {
+        T r;
+        if (TANGENT) {
+          const T h = h_col[(o0 + i) * VT + q * NTH];
+          r = (T(1) - h * h) * (gt * acc[q][i]);
+        } else {
+          r = acc[q][i] * gt + hb;
+          if (hidden) r = ffj_tanh(r);
+        }
+        out_col[(o0 + i) * VT + q * NTH] = r;
       }
-      out_col[(o0 + i) * NT] = r;
     }
   }
 }
+template <typename T, int S, bool TANGENT>
+GPF_DEV void ffj_matvec(const T* __restrict__ Wt, const T* __restrict__ vec, int in, int outp, const T* in_col,
+                        T* out_col, const T* h_col, bool hidden, int NTH, int VT) {
+  if (sizeof(T) == 4 && (outp & 15) == 0)
+    ffj_matvec_ob<T, S, 16, TANGENT>(Wt, vec, in, outp, in_col, out_col, h_col, hidden, NTH, VT);
+  else
+    ffj_matvec_ob<T, S, kFfjOB, TANGENT>(Wt, vec, in, outp, in_col, out_col, h_col, hidden, NTH, VT);
+}
 
-template <typename T>
+template <typename T, int S>
 __global__ void __launch_bounds__(kFfjMaxThreads, 1) gpflow_ffjord_kernel(const FfjordArgs a) {
   extern __shared__ __align__(16) unsigned char ffj_smem_raw[];
   T* sw = reinterpret_cast<T*>(ffj_smem_raw);
   const bool want_ld = a.logdet != nullptr;
   const FfjordPlan P = ffjord_plan(a.width, a.n_linear, want_ld);
-  const int NT = blockDim.x, tid = threadIdx.x;
-  T* cols = sw + P.weights_total + tid;     // column c of this thread: cols[c * NT]
+  const int NTH = blockDim.x, tid = threadIdx.x;
+  const int VT = S * NTH;                   // samples per CTA tile = column stride
+  T* cols = sw + P.weights_total + tid;     // column c of this thread's sample q: cols[c * VT + q * NTH]
   const int d = a.d, nl = a.n_linear;
   const T* gx = static_cast<const T*>(a.x);
   T* gy = static_cast<T*>(a.y);
@@ -148,13 +189,16 @@ __global__ void __launch_bounds__(kFfjMaxThreads, 1) gpflow_ffjord_kernel(const 
   long long block_params = 0;
   for (int l = 0; l < nl; ++l) block_params += (long long)a.width[l] * a.width[l + 1] + 4 * a.width[l + 1];
 
-  const long long n_tiles = (a.B + NT - 1) / NT;
+  const long long n_tiles = (a.B + VT - 1) / VT;
   for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-    const long long s = tile * NT + tid;
-    const bool live = s < a.B;
     // state
-    for (int j = 0; j < P.dp; ++j) cols[(P.col_y + j) * NT] = (live && j < d) ? gx[s * d + j] : T(0);
-    T logp = T(0);
+    T logp[S];
+#pragma unroll
+    for (int q = 0; q < S; ++q) {
+      const long long s = tile * VT + q * NTH + tid;
+      for (int j = 0; j < P.dp; ++j) cols[(P.col_y + j) * VT + q * NTH] = (s < a.B && j < d) ? gx[s * d + j] : T(0);
+      logp[q] = T(0);
+    }
     for (int bb = 0; bb < a.n_blocks; ++bb) {
       const int bi = a.reverse ? a.n_blocks - 1 - bb : bb;
       // ---- stage the block's weights: transposed + zero-padded, vectors b | hb | gw | gb ----
@@ -165,11 +209,11 @@ __global__ void __launch_bounds__(kFfjMaxThreads, 1) gpflow_ffjord_kernel(const 
           const int in = a.width[l], out = a.width[l + 1], outp = P.outp[l];
           T* Wt = sw + P.w_off[l];
           T* vec = sw + P.v_off[l];
-          for (int e = tid; e < in * outp; e += NT) {
+          for (int e = tid; e < in * outp; e += NTH) {
             const int k = e / outp, o = e - k * outp;
             Wt[e] = o < out ? src[o * in + k] : T(0);
           }
-          for (int e = tid; e < 4 * outp; e += NT) {
+          for (int e = tid; e < 4 * outp; e += NTH) {
             const int v = e / outp, o = e - v * outp;
             vec[e] = o < out ? src[in * out + v * out + o] : T(0);
           }
@@ -182,8 +226,12 @@ __global__ void __launch_bounds__(kFfjMaxThreads, 1) gpflow_ffjord_kernel(const 
       const T h = (T)hd, hh = (T)(0.5 * hd), h6 = (T)(hd / 6.0);
       for (int step = 0; step < a.n_steps; ++step) {
         const double tk = t0 + step * hd;
-        for (int j = 0; j < P.dp; ++j) cols[(P.col_acc + j) * NT] = T(0);
-        T dacc = T(0);
+#pragma unroll
+        for (int q = 0; q < S; ++q)
+          for (int j = 0; j < P.dp; ++j) cols[(P.col_acc + j) * VT + q * NTH] = T(0);
+        T dacc[S];
+#pragma unroll
+        for (int q = 0; q < S; ++q) dacc[q] = T(0);
 #pragma unroll 1
         for (int st = 0; st < 4; ++st) {
           if (st != 2) {   // stages 1 and 2 share t + h/2
@@ -193,7 +241,7 @@ __global__ void __launch_bounds__(kFfjMaxThreads, 1) gpflow_ffjord_kernel(const 
             for (int l = 0; l < nl; ++l) {
               const int outp = P.outp[l];
               T* vec = sw + P.v_off[l];
-              for (int o = tid; o < outp; o += NT) {
+              for (int o = tid; o < outp; o += NTH) {
                 vec[4 * outp + o] = ffj_sigmoid(vec[2 * outp + o] * tt + vec[3 * outp + o]);
                 vec[5 * outp + o] = vec[outp + o] * tt;
               }
@@ -202,65 +250,109 @@ __global__ void __launch_bounds__(kFfjMaxThreads, 1) gpflow_ffjord_kernel(const 
           }
           // stage input
           const T cs = st == 0 ? T(0) : (st == 3 ? h : hh);
-          for (int j = 0; j < d; ++j)
-            cols[(P.col_ys + j) * NT] = st == 0 ? cols[(P.col_y + j) * NT]
-                                                : cols[(P.col_y + j) * NT] + cs * cols[(P.col_k + j) * NT];
+#pragma unroll
+          for (int q = 0; q < S; ++q) {
+            T* c = cols + q * NTH;
+            for (int j = 0; j < d; ++j)
+              c[(P.col_ys + j) * VT] = st == 0 ? c[(P.col_y + j) * VT] : c[(P.col_y + j) * VT] + cs * c[(P.col_k + j) * VT];
+          }
           // value pass
-          const T* in_col = cols + P.col_ys * NT;
+          const T* in_col = cols + P.col_ys * VT;
           for (int l = 0; l < nl; ++l) {
             const bool hidden = l < nl - 1;
-            T* out_col = cols + (hidden ? P.act_off[l] : P.col_k) * NT;
-            ffj_matvec<T, false>(sw + P.w_off[l], sw + P.v_off[l], a.width[l], P.outp[l], in_col, out_col, nullptr, hidden, NT);
+            T* out_col = cols + (hidden ? P.act_off[l] : P.col_k) * VT;
+            ffj_matvec<T, S, false>(sw + P.w_off[l], sw + P.v_off[l], a.width[l], P.outp[l], in_col, out_col, nullptr, hidden,
+                                    NTH, VT);
             in_col = out_col;
           }
           const T wgt = (st == 1 || st == 2) ? T(2) : T(1);
-          for (int j = 0; j < d; ++j) cols[(P.col_acc + j) * NT] += wgt * cols[(P.col_k + j) * NT];
+#pragma unroll
+          for (int q = 0; q < S; ++q) {
+            T* c = cols + q * NTH;
+            for (int j = 0; j < d; ++j) c[(P.col_acc + j) * VT] += wgt * c[(P.col_k + j) * VT];
+          }
           // exact trace of df/dy, one input direction at a time
           if (want_ld) {
-            T div = T(0);
+            T div[S];
+#pragma unroll
+            for (int q = 0; q < S; ++q) div[q] = T(0);
             for (int j = 0; j < d; ++j) {
-              T* ta = cols + P.col_ta * NT;
-              T* tb = cols + P.col_tb * NT;
+              T* ta = cols + P.col_ta * VT;
+              T* tb = cols + P.col_tb * VT;
               if (nl == 1) {
                 const int outp = P.outp[0];
-                div += (sw + P.v_off[0])[4 * outp + j] * (sw + P.w_off[0])[j * outp + j];
+                const T v = (sw + P.v_off[0])[4 * outp + j] * (sw + P.w_off[0])[j * outp + j];
+#pragma unroll
+                for (int q = 0; q < S; ++q) div[q] += v;
                 continue;
               }
               {  // first layer: column j of W_0
                 const int outp = P.outp[0];
                 const T* Wt = sw + P.w_off[0] + j * outp;
                 const T* gate = sw + P.v_off[0] + 4 * outp;
-                const T* hc = cols + P.act_off[0] * NT;
+                const T* hc = cols + P.act_off[0] * VT;
                 for (int o = 0; o < outp; ++o) {
-                  const T hv = hc[o * NT];
-                  ta[o * NT] = (T(1) - hv * hv) * (gate[o] * Wt[o]);
+                  const T gw = gate[o] * Wt[o];
+#pragma unroll
+                  for (int q = 0; q < S; ++q) {
+                    const T hv = hc[o * VT + q * NTH];
+                    ta[o * VT + q * NTH] = (T(1) - hv * hv) * gw;
+                  }
                 }
               }
               for (int l = 1; l < nl - 1; ++l) {
-                ffj_matvec<T, true>(sw + P.w_off[l], sw + P.v_off[l], a.width[l], P.outp[l], ta, tb, cols + P.act_off[l] * NT,
-                                    true, NT);
+                ffj_matvec<T, S, true>(sw + P.w_off[l], sw + P.v_off[l], a.width[l], P.outp[l], ta, tb,
+                                       cols + P.act_off[l] * VT, true, NTH, VT);
                 T* tmp = ta; ta = tb; tb = tmp;
               }
               {  // last layer: output row j only
                 const int l = nl - 1, outp = P.outp[l];
                 const T* Wt = sw + P.w_off[l] + j;
-                T acc = T(0);
-                for (int k = 0; k < a.width[l]; ++k) acc = fma(Wt[k * outp], ta[k * NT], acc);
-                div += (sw + P.v_off[l])[4 * outp + j] * acc;
+                T acc[S];
+#pragma unroll
+                for (int q = 0; q < S; ++q) acc[q] = T(0);
+                for (int k = 0; k < a.width[l]; ++k) {
+                  const T w = Wt[k * outp];
+#pragma unroll
+                  for (int q = 0; q < S; ++q) acc[q] = fma(w, ta[k * VT + q * NTH], acc[q]);
+                }
+                const T gt = (sw + P.v_off[l])[4 * outp + j];
+#pragma unroll
+                for (int q = 0; q < S; ++q) div[q] += gt * acc[q];
               }
             }
-            dacc += wgt * div;
+#pragma unroll
+            for (int q = 0; q < S; ++q) dacc[q] += wgt * div[q];
           }
         }
-        for (int j = 0; j < d; ++j) cols[(P.col_y + j) * NT] += h6 * cols[(P.col_acc + j) * NT];
-        logp -= h6 * dacc;
+#pragma unroll
+        for (int q = 0; q < S; ++q) {
+          T* c = cols + q * NTH;
+          for (int j = 0; j < d; ++j) c[(P.col_y + j) * VT] += h6 * c[(P.col_acc + j) * VT];
+          logp[q] -= h6 * dacc[q];
+        }
       }
     }
-    if (live) {
-      for (int j = 0; j < d; ++j) gy[s * d + j] = cols[(P.col_y + j) * NT];
-      if (want_ld) gld[s] = -logp;
+#pragma unroll
+    for (int q = 0; q < S; ++q) {
+      const long long s = tile * VT + q * NTH + tid;
+      if (s < a.B) {
+        for (int j = 0; j < d; ++j) gy[s * d + j] = cols[(P.col_y + j) * VT + q * NTH];
+        if (want_ld) gld[s] = -logp[q];
+      }
     }
   }
+}
+
+template <typename T, int S>
+int launch_ffjord_s(const FfjordArgs& a, cudaStream_t st, int nt, int grid, size_t smem) {
+  auto kern = gpflow_ffjord_kernel<T, S>;
+  if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) {
+    cudaGetLastError();
+    return GPFLOW_ERR_CUDA;
+  }
+  kern<<<(unsigned)grid, nt, smem, st>>>(a);
+  return cudaGetLastError() == cudaSuccess ? GPFLOW_OK : GPFLOW_ERR_CUDA;
 }
 
 template <typename T>
@@ -268,23 +360,24 @@ int launch_ffjord(const FfjordArgs& a, cudaStream_t st, int sm_count, size_t sme
   const FfjordPlan P = ffjord_plan(a.width, a.n_linear, a.logdet != nullptr);
   const size_t wbytes = (size_t)P.weights_total * sizeof(T);
   if (wbytes + (size_t)32 * P.cols * sizeof(T) > smem_limit) return GPFLOW_ERR_UNSUPPORTED;
-  int nt_max = (int)((smem_limit - wbytes) / ((size_t)P.cols * sizeof(T))) / 32 * 32;
-  if (nt_max > kFfjMaxThreads) nt_max = kFfjMaxThreads;
+  int vt_max = (int)((smem_limit - wbytes) / ((size_t)P.cols * sizeof(T))) / 32 * 32;   // samples per CTA tile
+  if (vt_max > kFfjMaxThreads) vt_max = kFfjMaxThreads;
   // spread small batches over the SMs
   long long per_sm = (a.B + sm_count - 1) / sm_count;
-  int nt = (int)((per_sm + 31) / 32 * 32);
-  if (nt > nt_max) nt = nt_max;
-  if (nt < 32) nt = 32;
-  const size_t smem = wbytes + (size_t)nt * P.cols * sizeof(T);
-  auto kern = gpflow_ffjord_kernel<T>;
-  if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_limit) != cudaSuccess) {
-    cudaGetLastError();
-    return GPFLOW_ERR_CUDA;
-  }
-  long long grid = (a.B + nt - 1) / nt;
+  int vt = (int)((per_sm + 31) / 32 * 32);
+  if (vt > vt_max) vt = vt_max;
+  if (vt < 32) vt = 32;
+  // fp32, full tiles: two samples per thread (weight loads shared by both; see ffj_matvec_ob)
+  static const int s2_allowed = [] { const char* e = getenv("GPFLOW_FFJORD_S2"); return e == nullptr || e[0] != '0'; }();
+  const int vt64 = vt_max / 64 * 64;
+  // (value-only launches; with the trace columns the tile shrinks 160 -> 128 samples and S = 2 measured slower)
+  const bool s2 = sizeof(T) == 4 && s2_allowed && a.logdet == nullptr && vt64 >= 64 && vt >= vt64;
+  if (s2) vt = vt64;
+  const size_t smem = wbytes + (size_t)vt * P.cols * sizeof(T);
+  long long grid = (a.B + vt - 1) / vt;
   if (grid > sm_count) grid = sm_count;
-  kern<<<(unsigned)grid, nt, smem, st>>>(a);
-  return cudaGetLastError() == cudaSuccess ? GPFLOW_OK : GPFLOW_ERR_CUDA;
+  if (s2) return launch_ffjord_s<T, sizeof(T) == 4 ? 2 : 1>(a, st, vt / 2, (int)grid, smem);
+  return launch_ffjord_s<T, 1>(a, st, vt, (int)grid, smem);
 }
 
 }  // namespace gpflow

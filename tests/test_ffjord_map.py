@@ -122,6 +122,26 @@ def test_cuda_matches_fp64_oracle_ragged(B):
     assert _rel(xb.cpu().double(), xo) < 1e-5
 
 
+@pytest.mark.gpu
+def test_cuda_full_tiles_two_samples_per_thread():
+    """a batch that fills every SM switches the fp32 kernel to two samples per thread: ragged last tile, fp64 oracle"""
+    _need_cuda()
+    g, spec = _golden("f32")
+    B = 148 * 256 + 77
+    spec.n_steps = 2
+    m = _map(g, spec, n_steps=2)
+    x = torch.randn(B, spec.d, generator=torch.Generator().manual_seed(5))
+    fp = torch.from_numpy(g["params"]).double()
+    z, ld = m(x.cuda())
+    zo, ldo = FO.integrate(fp, x.double(), spec, want_logdet=True)
+    assert _rel(z.cpu().double(), zo) < 1e-5
+    assert _rel(ld.cpu().double(), ldo) < 1e-5
+    xb = m.backward(x.cuda())
+    xo, _ = FO.integrate(fp, x.double(), spec, reverse=True)
+    assert _rel(xb.cpu().double(), xo) < 1e-5
+    assert float((xb.cpu().double() - xo).abs().max()) < 1e-4
+
+
 SHAPES = [  # d, hidden, blocks, steps
     (2, [], 1, 4), (2, [5], 2, 3), (3, [9, 17], 1, 5), (5, [8, 8, 8], 3, 2), (10, [64, 64], 1, 3), (17, [33], 2, 2),
     (7, [128, 40], 1, 2), (4, [16, 16, 16, 16], 1, 2)]
