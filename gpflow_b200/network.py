@@ -48,11 +48,17 @@ class GPFlowNetwork(torch.nn.Module):
         log_abs_det = ((y ** 2).sum(1) - (x ** 2).sum(1)) / (2.0 * self.sigma ** 2)
         return y, log_abs_det
 
+    def _map_points(self, x):
+        """`self.map(x)[0]` (network.py:76-78); a map mirror that can skip its log-determinant (FFJORDMap.map_only: no
+        trace pass) is asked for the points alone."""
+        fn = getattr(self.map, "map_only", None)
+        return fn(x) if callable(fn) else self.map(x)[0]
+
     # ---- network.py:70-84 ---------------------------------------------------------------------
     def loss_gp_flow(self, x, x_map: Optional[torch.Tensor] = None):
         if x_map is None:
             with torch.no_grad():
-                x_map = self.map(x)[0]
+                x_map = self._map_points(x)
         y, _ = self.gp_flow(x_map)
         return ((x - y) ** 2).sum(-1).mean()
 
@@ -64,7 +70,7 @@ class GPFlowNetwork(torch.nn.Module):
         Returns (loss_gp, reg) as 0-dim tensors (no host sync).  With a process group the [grads | scalars] buffer is
         all-reduced (SUM) once; `global_batch` defaults to B * world_size."""
         if x_map is None:
-            x_map = self.map(x)[0]
+            x_map = self._map_points(x)
         flow = self.flow
         cfg = flow.config(self.sigma)
         world = 1
@@ -139,7 +145,7 @@ class GPFlowNetwork(torch.nn.Module):
         return out
 
     def predict_map(self, x, reverse=False):
-        return self.map(x)[0] if not reverse else self.map.backward(x)
+        return self._map_points(x) if not reverse else self.map.backward(x)
 
     def get_flow_trajectories(self):
         return self.flow.get_trajectories()

@@ -227,3 +227,37 @@ def test_c3_pipeline_dataset_to_train_step():
     ref = O.train_step([p.double() for p in params], x_data.cpu().double(), x_map.cpu().double(), spec)
     assert abs(float(res["scalars"][0]) - float(ref["ot"])) < 1e-5 * abs(float(ref["ot"]))
     assert _rel(res["grads"].cpu().double(), ref["grads"]) < 1e-5
+
+
+@pytest.mark.gpu
+def test_network_mirror_with_ffjord_map():
+    """`GPFlowNetwork` with the FFJORD mirror as `self.map` (network.py:27,76-78,191-253): the fused step maps the batch
+    itself (points only, no trace), `ot_map` returns map + flow log-determinants, and `ot_map(reverse=True)` -- which needs
+    `map.backward` -- inverts it up to the integrators' round-trip errors."""
+    _need_cuda()
+    import gpflow_b200 as G
+    import gpflow_oracle as O
+    g, fspec = _golden("f32")
+    m = _map(g, fspec, n_steps=32)
+    spec = O.FlowSpec(d=10, nb=9, hidden=[50, 50, 50], n_steps=15)
+    params = O.init_params(spec, 0.05, 0, torch.float32)
+    flow = G.get_gp_flow(10, {"nb_neurons": [50, 50, 50], "nb_div_blocks": 9}, 15).cuda()
+    with torch.no_grad():
+        for p, q in zip(flow.parameters(), params):
+            p.copy_(q.reshape(p.shape))
+    net = G.GPFlowNetwork(flow, map_module=m)
+    x = m.backward(torch.randn(96, 10, generator=torch.Generator().manual_seed(4)).cuda())
+    loss, _ = net.fused_training_step(x)
+    grads = torch.cat([p.grad.reshape(-1) for p in flow.parameters()]).clone()
+    cfg = G.FlowConfig(d=10, nb=9, hidden=(50, 50, 50), n_steps=15)
+    res = G.fused_train_step(cfg, O.flatten_params(params).cuda(), x, m.map_only(x))
+    assert abs(float(loss) - float(res["scalars"][0])) < 1e-6 * abs(float(loss))
+    assert _rel(grads.cpu(), res["grads"].cpu()) < 1e-6
+    y, ld = net.ot_map(x, return_log_det=True)
+    _, ld_map = m(x)
+    assert y.shape == x.shape and ld.shape == (96,) and bool(torch.isfinite(ld).all())
+    y2, ld_gp = net.gp_flow(m.map_only(x))
+    assert _rel(y.cpu(), y2.cpu()) < 1e-6
+    assert float((ld - (ld_map + ld_gp)).abs().max()) < 1e-4 * max(1.0, float(ld.abs().max()))
+    xb = net.ot_map(y, reverse=True)
+    assert _rel(xb.cpu(), x.cpu()) < 2e-3
