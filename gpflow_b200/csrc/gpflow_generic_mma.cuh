@@ -175,9 +175,63 @@ GPF_DEV void gm_weight_grad_impl(const float* __restrict__ yb0, const float* __r
     }
   }
 }
+// Aligned fast path of gm_weight_grad (M % 16 == 0, N % 64 == 0, gw 8-byte aligned): one 16-output strip x 64-input block
+// per pass -- the A fragment of a k-step (4 loads, 4 splits) feeds 8 m-tiles, no column predicates, the 16 x 64 accumulator
+// block is read-modify-written once with 64-bit accesses.  ~13 instead of ~35 (+ predicates) instructions per 3 mma.
+GPF_DEV void gm_weight_grad_fast(const float* __restrict__ yb0, const float* __restrict__ Yb, int ldyb,
+                                 const float* __restrict__ x0, const float* __restrict__ X, int ldx, int d, int M, int N,
+                                 float* __restrict__ gw, int lane) {
+  const int g = lane >> 2, t = lane & 3;
+  const int R = d + 1;
+  for (int k0 = 0; k0 < M; k0 += 16) {
+    for (int mb = 0; mb < N; mb += 64) {
+      float c[8][4];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) c[i][0] = c[i][1] = c[i][2] = c[i][3] = 0.0f;
+      for (int r0 = 0; r0 < R; r0 += 8) {
+        const int ra = r0 + t, rb = r0 + t + 4;      // rb >= 4: always a tangent row
+        const bool va = ra <= d, vb = rb <= d;
+        const float* __restrict__ pa = ra == 0 ? yb0 : Yb + (size_t)(ra - 1) * ldyb;
+        const float* __restrict__ pb = Yb + (size_t)(rb - 1) * ldyb;
+        const float* __restrict__ qa = (ra == 0 ? x0 : X + (size_t)(ra - 1) * ldx) + mb + g;
+        const float* __restrict__ qb = X + (size_t)(rb - 1) * ldx + mb + g;
+        float av[4], bv[8][2];
+        av[0] = va ? pa[k0 + g] : 0.0f; av[1] = va ? pa[k0 + g + 8] : 0.0f;
+        av[2] = vb ? pb[k0 + g] : 0.0f; av[3] = vb ? pb[k0 + g + 8] : 0.0f;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) { bv[i][0] = va ? qa[8 * i] : 0.0f; bv[i][1] = vb ? qb[8 * i] : 0.0f; }
+        uint32_t ah[4], al[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) tf32_split(av[q], ah[q], al[q]);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          uint32_t bh[2], bl[2];
+          tf32_split(bv[i][0], bh[0], bl[0]);
+          tf32_split(bv[i][1], bh[1], bl[1]);
+          mma_3xtf32(c[i], ah, al, bh, bl);
+        }
+      }
+      float* __restrict__ g0 = gw + (size_t)(k0 + g) * N + mb + 2 * t;
+      float* __restrict__ g1 = g0 + (size_t)8 * N;
+      float2 o0[8], o1[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        o0[i] = *reinterpret_cast<const float2*>(g0 + 8 * i);
+        o1[i] = *reinterpret_cast<const float2*>(g1 + 8 * i);
+      }
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        *reinterpret_cast<float2*>(g0 + 8 * i) = make_float2(o0[i].x + c[i][0], o0[i].y + c[i][1]);
+        *reinterpret_cast<float2*>(g1 + 8 * i) = make_float2(o1[i].x + c[i][2], o1[i].y + c[i][3]);
+      }
+    }
+  }
+}
 GPF_DEV void gm_weight_grad(const float* __restrict__ yb0, const float* __restrict__ Yb, int ldyb, const float* __restrict__ x0,
                             const float* __restrict__ X, int ldx, int d, int M, int N, float* __restrict__ gw, int lane) {
-  if (d <= 7) gm_weight_grad_impl<1>(yb0, Yb, ldyb, x0, X, ldx, d, M, N, gw, lane);
+  if ((M & 15) == 0 && (N & 63) == 0 && (reinterpret_cast<uintptr_t>(gw) & 7) == 0)
+    gm_weight_grad_fast(yb0, Yb, ldyb, x0, X, ldx, d, M, N, gw, lane);
+  else if (d <= 7) gm_weight_grad_impl<1>(yb0, Yb, ldyb, x0, X, ldx, d, M, N, gw, lane);
   else if (d <= 15) gm_weight_grad_impl<2>(yb0, Yb, ldyb, x0, X, ldx, d, M, N, gw, lane);
   else gm_weight_grad_impl<0>(yb0, Yb, ldyb, x0, X, ldx, d, M, N, gw, lane);
 }
