@@ -987,10 +987,14 @@ inline GenericPlan generic_plan(const GpFlowDesc* d, int64_t B, int op, int sm_c
   p.scratch_stride = (p.vec_offset + (size_t)v.total * es + 255) / 256 * 256;
   p.smem_scratch_off = ((size_t)g.P * es + 255) / 256 * 256;
   // global mode: 16 warps per SM as CTAs of GPFLOW_GENERIC_WPC warps
-  static const int wpc_env = [] { const char* e = getenv("GPFLOW_GENERIC_WPC"); const int v = e ? atoi(e) : 16;
-                                  return (v == 1 || v == 2 || v == 4 || v == 8 || v == 16) ? v : 16; }();
-  p.warps_per_cta = wpc_env;
+  static const int wpc_env = [] { const char* e = getenv("GPFLOW_GENERIC_WPC"); const int v = e ? atoi(e) : 0;
+                                  return (v == 1 || v == 2 || v == 4 || v == 8 || v == 16) ? v : 0; }();
+  p.warps_per_cta = wpc_env ? wpc_env : 16;
   long long nw = (long long)sm_count * 16;
+  if (!wpc_env && B < nw) {   // small batch (one warp per sample): smaller CTAs so that the warps spread over all the SMs
+    const long long per_sm = (B + sm_count - 1) / sm_count;
+    while (p.warps_per_cta > 1 && p.warps_per_cta / 2 >= per_sm) p.warps_per_cta /= 2;
+  }
   static const int on_chip_allowed = [] { const char* e = getenv("GPFLOW_GENERIC_ONCHIP"); return e == nullptr || e[0] != '0'; }();
   if (on_chip_allowed && (size_t)kGenericSmemBudget > p.smem_scratch_off + 12 * p.scratch_stride) {
     int w = (int)(((size_t)kGenericSmemBudget - p.smem_scratch_off) / p.scratch_stride);
@@ -1006,8 +1010,12 @@ inline GenericPlan generic_plan(const GpFlowDesc* d, int64_t B, int op, int sm_c
   const long long cap = (long long)((size_t)16 << 30) / (long long)per_warp;
   if (nw > cap) nw = cap;
   if (nw < 1) nw = 1;
+  const long long nw16 = (nw + 15) / 16 * 16;
   nw = (nw + p.warps_per_cta - 1) / p.warps_per_cta * p.warps_per_cta;  // whole CTAs
   p.nwarps = nw;
+  // sizes: global mode rounds to 16 warps whatever the CTA size, so that the device-independent bound (160 SMs) covers
+  // every CTA size the real SM count may select
+  if (!p.on_chip) nw = nw16;
   p.partials_bytes = (((size_t)nw * generic_part_stride(g.P) + 4) * es + 255) / 256 * 256;
   p.params_t_bytes = ((size_t)g.Ps * es * (es == 4 ? 5 : 1) + 255) / 256 * 256;   // Wt (+ the 4 tf32 split copies in fp32)
   p.scratch_bytes = p.on_chip ? 0 : (size_t)nw * p.scratch_stride;
