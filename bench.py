@@ -132,13 +132,124 @@ def run_reference(args, wl, rank, world):
     print(json.dumps(line), flush=True)
 
 
+def run_ffjord_dataset(args, rank, world, local_rank):
+    """Extra row: the Gaussian-noise data set of the latent configs, `map.backward(gauss)` through
+    the frozen pretrained dsprites FFJORD (src/data_module.py:161-186), one gpflow_ffjord_integrate launch per step.
+    A step = one data-set build of 2^log2_batch points (default 2^18 ~ the reference's 240 000); ranks build independent
+    shards (no collective).  e2e adds the device->host copy of the data set (the reference keeps it in a CPU Dataset)."""
+    json_fd = os.dup(1)
+    os.dup2(2, 1)
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    import gpflow_b200 as G
+    from gpflow_b200 import ops
+
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    z = np.load(os.path.join(ROOT, "tests", "golden", "ffjord_dsprites_f32.npz"))
+    d, hidden, nblocks, n_steps = int(z["d"]), [int(h) for h in z["hidden"]], int(z["n_blocks"]), 64
+    t_end = [float(t) for t in z["t_end"]]
+    m = G.FFJORDMap(d, hidden, nblocks, torch.from_numpy(z["params"]), t_end, n_steps).to(dev)
+    B_global = 1 << (args.log2_batch or 18)
+    B = B_global // world
+    n_buf = 8                                   # 8 x 10 MB of distinct Gaussian points; the kernel is compute-bound (80 B/sample)
+    gauss = [torch.randn(B, d, device=dev, generator=torch.Generator(device=dev).manual_seed(1234 + rank + 1000 * i))
+             for i in range(n_buf)]
+    for i in range(args.warmup):
+        m.backward(gauss[i % n_buf])
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    clocks = ClockSampler(local_rank)
+    if rank == 0:
+        clocks.start()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    for i in range(args.steps):
+        x = m.backward(gauss[i % n_buf])
+    ev1.record()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    t = torch.tensor([ev0.elapsed_time(ev1)], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t[0]) / args.steps
+    clk = clocks.stop() if rank == 0 else None
+    # e2e: pinned HOST Gaussian points in, data set back on the host (the reference's Dataset lives on the CPU)
+    hin = [g.cpu().pin_memory() for g in gauss[:2]]
+    hout = torch.empty(B, d).pin_memory()
+    def e2e_run(n):
+        for i in range(n):
+            hout.copy_(m.backward(hin[i % 2].to(dev, non_blocking=True)), non_blocking=True)
+        torch.cuda.synchronize()
+    e2e_run(1)
+    if world > 1:
+        dist.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(); e2e_run(args.steps); e1.record(); torch.cuda.synchronize()
+    te = torch.tensor([e0.elapsed_time(e1)], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(te, op=dist.ReduceOp.MAX)
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    n = [d] + hidden + [d]
+    flops = 2.0 * sum(n[i] * n[i + 1] for i in range(len(n) - 1)) * 4 * n_steps * nblocks      # per sample, value only
+    peak_tf = ops.fp32_fma_peak_tflops()
+    achieved = flops * B / (ms * 1e-3) / 1e12
+    cpu_baseline = None
+    if not args.no_cpu_baseline and world == 1:
+        sys.path.insert(0, os.path.join(ROOT, "oracle"))      # CPU baseline leg only
+        import ffjord_oracle as FO
+        threads = os.cpu_count() or 1
+        torch.set_num_threads(threads)
+        spec = FO.FfjordSpec(d=d, hidden=hidden, n_blocks=nblocks, n_steps=n_steps, t_end=t_end)
+        xs = torch.randn(1 << 14, d)
+        with torch.no_grad():
+            FO.integrate(torch.from_numpy(z["params"]), xs[:1024], spec, reverse=True)
+            t0 = time.perf_counter()
+            FO.integrate(torch.from_numpy(z["params"]), xs, spec, reverse=True)
+            sec = time.perf_counter() - t0
+        cpu_baseline = {"value": xs.shape[0] / sec, "unit": "samples/s", "cores": threads, "kind": "port",
+                        "sample": "%d samples, same map and step count (oracle port, torch CPU, all host threads)" % xs.shape[0]}
+    line = {
+        "metric": "ffjord_gaussian_noise_dataset_samples_per_sec", "value": B_global / (ms * 1e-3), "unit": "samples/s",
+        "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
+        "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "ffjord_dataset: map.backward(gauss) through pretrained dsprites FFJORD (3 CNF blocks "
+                               "10->64->64->10), %d RK4 steps per block" % n_steps, "global_batch": B_global,
+                   "per_gpu_batch": B, "parallelism": "dp%d (independent shards, no collective)" % world,
+                   "l2": "compute-bound (80 B/sample); rotating through %d distinct input buffers" % n_buf},
+        "clocks": clk,
+        "e2e": {"value": B_global / (float(te[0]) / args.steps * 1e-3), "unit": "samples/s",
+                "h2d_bytes_per_step": B * d * 4 * world, "d2h_bytes_per_step": B * d * 4 * world,
+                "api": "pinned host gauss -> FFJORDMap.backward -> pinned host data set"},
+        "gpu_launches": args.steps,
+        "roofline": {"bound": "fp32_fma", "achieved": achieved, "peak": peak_tf, "unit": "TFLOP/s",
+                     "frac": achieved / peak_tf if peak_tf else None, "traffic": None,
+                     "kernel": "gpflow_ffjord_kernel<f32>", "kernel_ms": ms, "algorithmic_flops_per_sample": flops,
+                     "samples_per_launch": B,
+                     "peak_source": "FFMA burn micro-kernel measured live in this run (gpflow_fp32_fma_burn)"},
+        "cpu_baseline": cpu_baseline,
+    }
+    sys.stdout.flush()
+    os.write(json_fd, (json.dumps(line) + "\n").encode())
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="c4_2d_2p24", choices=sorted(WORKLOADS))
+    ap.add_argument("--workload", default="c4_2d_2p24", choices=sorted(WORKLOADS) + ["ffjord_dataset"])
     ap.add_argument("--log2-batch", type=int, default=None, help="override the global batch (log2)")
     ap.add_argument("--ref-log2-sample", type=int, default=15)
     ap.add_argument("--cpu-baseline-sample", type=int, default=1 << 17)
@@ -147,7 +258,7 @@ def main():
     ap.add_argument("--dbg", default="", help=argparse.SUPPRESS)   # developer toggles: nbuf1,noopt,noclk
     ap.add_argument("--euler", type=float, default=None, help="Euler penalization coefficient (extra row)")
     args = ap.parse_args()
-    wl = dict(WORKLOADS[args.workload])
+    wl = dict(WORKLOADS.get(args.workload, {}))
     if args.log2_batch is not None:
         wl["log2_batch"] = args.log2_batch
 
@@ -161,6 +272,14 @@ def main():
                "--master-addr", "127.0.0.1", "--master-port", str(port)] + sys.argv
         sys.exit(subprocess.call(cmd))
 
+    if args.workload == "ffjord_dataset":
+        if args.impl == "reference":
+            if rank == 0:
+                print(json.dumps({"impl": "reference", "unavailable": "ffjord_dataset is an extra row; its CPU leg is "
+                                  "the cpu_baseline object of the normal run"}))
+            return
+        run_ffjord_dataset(args, rank, world, local_rank)
+        return
     if args.impl == "reference":
         run_reference(args, wl, rank, world)
         return
