@@ -313,7 +313,8 @@ struct Generic {
     bool dots_done = false;
     if constexpr (std::is_same<S, float>::value) {
       if (a.vec4) {
-        gl_dots_v4(W, bias, hL, TL, sc + l.R, sc + l.f, sc + l.G, sc + l.D, d, nb, H, lane);
+        if (H <= 64) gl_dots_v<2>(W, bias, hL, TL, sc + l.R, sc + l.f, sc + l.G, sc + l.D, d, nb, H, lane);
+        else gl_dots_v<4>(W, bias, hL, TL, sc + l.R, sc + l.f, sc + l.G, sc + l.D, d, nb, H, lane);
         dots_done = true;
       }
     }
@@ -517,8 +518,12 @@ struct Generic {
     bool passes_done = false;
     if constexpr (std::is_same<S, float>::value) {
       if (a.vec4) {
-        gl_reverse_v4(W, gw, hL, TL, sc + l.R, sc + l.fb, sc + l.Qb, sc + l.s, sc + l.SQ, sc + l.hb[L], sc + l.Tb[L],
-                      sc + l.sb, d, nb, H, lane);
+        if (H <= 64)
+          gl_reverse_v<2>(W, gw, hL, TL, sc + l.R, sc + l.fb, sc + l.Qb, sc + l.s, sc + l.SQ, sc + l.hb[L], sc + l.Tb[L],
+                          sc + l.sb, d, nb, H, lane);
+        else
+          gl_reverse_v<4>(W, gw, hL, TL, sc + l.R, sc + l.fb, sc + l.Qb, sc + l.s, sc + l.SQ, sc + l.hb[L], sc + l.Tb[L],
+                          sc + l.sb, d, nb, H, lane);
         passes_done = true;
       }
     }

@@ -248,28 +248,54 @@ GPF_DEV float4 gl_fma4(float s, float4 a, float4 acc) {
   return make_float4(fmaf(s, a.x, acc.x), fmaf(s, a.y, acc.y), fmaf(s, a.z, acc.z), fmaf(s, a.w, acc.w));
 }
 
+// VW-wide lane vectors for the last-layer passes: VW = 4 (128-bit accesses, 128 input units per warp pass) or VW = 2
+// (64-bit, 64 units per pass -- all 32 lanes busy when H <= 64, e.g. the zero-padded C3 shape)
+template <int VW> struct GLv { float x[VW]; };
+template <int VW> GPF_DEV GLv<VW> gv_zero() { GLv<VW> r;
+#pragma unroll
+  for (int i = 0; i < VW; ++i) r.x[i] = 0.0f;
+  return r; }
+template <int VW> GPF_DEV GLv<VW> gv_ld(const float* p);
+template <> GPF_DEV GLv<4> gv_ld<4>(const float* p) { const float4 v = *reinterpret_cast<const float4*>(p); GLv<4> r; r.x[0] = v.x; r.x[1] = v.y; r.x[2] = v.z; r.x[3] = v.w; return r; }
+template <> GPF_DEV GLv<2> gv_ld<2>(const float* p) { const float2 v = *reinterpret_cast<const float2*>(p); GLv<2> r; r.x[0] = v.x; r.x[1] = v.y; return r; }
+GPF_DEV void gv_st(float* p, const GLv<4>& a) { *reinterpret_cast<float4*>(p) = make_float4(a.x[0], a.x[1], a.x[2], a.x[3]); }
+GPF_DEV void gv_st(float* p, const GLv<2>& a) { *reinterpret_cast<float2*>(p) = make_float2(a.x[0], a.x[1]); }
+template <int VW> GPF_DEV float gv_dot(const GLv<VW>& a, const GLv<VW>& b, float acc) {   // same nesting as gl_dot4
+#pragma unroll
+  for (int i = VW - 1; i >= 0; --i) acc = fmaf(a.x[i], b.x[i], acc);
+  return acc; }
+template <int VW> GPF_DEV GLv<VW> gv_fma(float s, const GLv<VW>& a, const GLv<VW>& acc) { GLv<VW> r;
+#pragma unroll
+  for (int i = 0; i < VW; ++i) r.x[i] = fmaf(s, a.x[i], acc.x[i]);
+  return r; }
+template <int VW> GPF_DEV GLv<VW> gv_add(const GLv<VW>& a, const GLv<VW>& b) { GLv<VW> r;
+#pragma unroll
+  for (int i = 0; i < VW; ++i) r.x[i] = a.x[i] + b.x[i];
+  return r; }
+
 // f_p = W[p].h + b_p, g_p = W[p].R_n, D_p = W[p].T_L[i] for every kept row p = (i, n <= min(i, nb-1))
-GPF_DEV void gl_dots_v4(const float* __restrict__ W, const float* __restrict__ bias, const float* __restrict__ hL,
+template <int VW>
+GPF_DEV void gl_dots_v(const float* __restrict__ W, const float* __restrict__ bias, const float* __restrict__ hL,
                         const float* __restrict__ TL, const float* __restrict__ R, float* __restrict__ f,
                         float* __restrict__ G, float* __restrict__ D, int d, int nb, int H, int lane) {
   for (int i = 0; i < d; ++i) {
     const int nmax = i < nb - 1 ? i : nb - 1;
     for (int n0 = 0; n0 <= nmax; n0 += 4) {
       float af[4] = {0.f, 0.f, 0.f, 0.f}, ag[4] = {0.f, 0.f, 0.f, 0.f}, ad[4] = {0.f, 0.f, 0.f, 0.f};
-      for (int m = 4 * lane; m < H; m += 128) {
-        float4 w[4], r[4];
+      for (int m = VW * lane; m < H; m += 32 * VW) {
+        GLv<VW> w[4], r[4];
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
           const int nq = n0 + q <= nmax ? n0 + q : nmax;  // clamped rows are discarded below
-          w[q] = gl_ld4(W + (size_t)(i * nb + nq) * H + m);
-          r[q] = gl_ld4(R + nq * H + m);
+          w[q] = gv_ld<VW>(W + (size_t)(i * nb + nq) * H + m);
+          r[q] = gv_ld<VW>(R + nq * H + m);
         }
-        const float4 hm = gl_ld4(hL + m), ti = gl_ld4(TL + i * H + m);
+        const GLv<VW> hm = gv_ld<VW>(hL + m), ti = gv_ld<VW>(TL + i * H + m);
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
-          af[q] = gl_dot4(w[q], hm, af[q]);
-          ag[q] = gl_dot4(w[q], r[q], ag[q]);
-          ad[q] = gl_dot4(w[q], ti, ad[q]);
+          af[q] = gv_dot<VW>(w[q], hm, af[q]);
+          ag[q] = gv_dot<VW>(w[q], r[q], ag[q]);
+          ad[q] = gv_dot<VW>(w[q], ti, ad[q]);
         }
       }
       const float rf = warp_sum4(af, lane), rg = warp_sum4(ag, lane), rd = warp_sum4(ad, lane);
@@ -285,68 +311,69 @@ GPF_DEV void gl_dots_v4(const float* __restrict__ W, const float* __restrict__ b
 }
 
 // pass A (hb_L, D part of Tb_L, dW) and pass B (Rb_n, CR_n, R part of Tb_L and of sb) of the reverse last layer
-GPF_DEV void gl_reverse_v4(const float* __restrict__ W, float* __restrict__ gw, const float* __restrict__ hL,
+template <int VW>
+GPF_DEV void gl_reverse_v(const float* __restrict__ W, float* __restrict__ gw, const float* __restrict__ hL,
                            const float* __restrict__ TL, const float* __restrict__ R, const float* __restrict__ fb,
                            const float* __restrict__ Qb, const float* __restrict__ s, const float* __restrict__ SQ,
                            float* __restrict__ hb, float* __restrict__ Tb, float* sb, int d, int nb, int H, int lane) {
-  const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
-  for (int m0 = 0; m0 < H; m0 += 128) {
-    const int m = m0 + 4 * lane;
+  const GLv<VW> z4 = gv_zero<VW>();
+  for (int m0 = 0; m0 < H; m0 += 32 * VW) {
+    const int m = m0 + VW * lane;
     const bool act = m < H;
-    float4 hbm = z4;
-    const float4 hm = act ? gl_ld4(hL + m) : z4;
+    GLv<VW> hbm = z4;
+    const GLv<VW> hm = act ? gv_ld<VW>(hL + m) : z4;
     for (int i = 0; i < d; ++i) {
       const int nmax = i < nb - 1 ? i : nb - 1;
-      const float4 Ti = act ? gl_ld4(TL + i * H + m) : z4;
+      const GLv<VW> Ti = act ? gv_ld<VW>(TL + i * H + m) : z4;
       const float qbi = Qb[i], nsi = -s[i];
-      float4 Ei = z4;
+      GLv<VW> Ei = z4;
       if (act) {
         for (int n0 = 0; n0 <= nmax; n0 += 4) {
-          float4 w[4], go[4], r[4];
+          GLv<VW> w[4], go[4], r[4];
           float fbp[4], dbp[4];
 #pragma unroll
           for (int q = 0; q < 4; ++q) {  // every load of the pass before its stores
             const int nq = n0 + q <= nmax ? n0 + q : nmax;
             const size_t p = (size_t)(i * nb + nq);
-            w[q] = gl_ld4(W + p * H + m);
-            go[q] = gl_ld4(gw + p * H + m);
-            r[q] = gl_ld4(R + nq * H + m);
+            w[q] = gv_ld<VW>(W + p * H + m);
+            go[q] = gv_ld<VW>(gw + p * H + m);
+            r[q] = gv_ld<VW>(R + nq * H + m);
             fbp[q] = fb[p];
             dbp[q] = nsi * SQ[nq];
           }
 #pragma unroll
           for (int q = 0; q < 4; ++q)
             if (n0 + q <= nmax) {
-              hbm = gl_fma4(fbp[q], w[q], hbm);
-              Ei = gl_fma4(dbp[q], w[q], Ei);
-              gl_st4(gw + (size_t)(i * nb + n0 + q) * H + m, gl_fma4(fbp[q], hm, gl_fma4(qbi, r[q], gl_fma4(dbp[q], Ti, go[q]))));
+              hbm = gv_fma<VW>(fbp[q], w[q], hbm);
+              Ei = gv_fma<VW>(dbp[q], w[q], Ei);
+              gv_st(gw + (size_t)(i * nb + n0 + q) * H + m, gv_fma<VW>(fbp[q], hm, gv_fma<VW>(qbi, r[q], gv_fma<VW>(dbp[q], Ti, go[q]))));
             }
         }
-        gl_st4(Tb + i * H + m, Ei);
+        gv_st(Tb + i * H + m, Ei);
       }
     }
-    if (act) gl_st4(hb + m, hbm);
-    float4 CR = z4;
+    if (act) gv_st(hb + m, hbm);
+    GLv<VW> CR = z4;
     for (int n = 0; n < nb; ++n) {
-      float4 rb = z4;
+      GLv<VW> rb = z4;
       if (act) {
         int i = n;
         for (; i + 4 <= d; i += 4) {
-          float4 w[4];
+          GLv<VW> w[4];
 #pragma unroll
-          for (int q = 0; q < 4; ++q) w[q] = gl_ld4(W + (size_t)((i + q) * nb + n) * H + m);
+          for (int q = 0; q < 4; ++q) w[q] = gv_ld<VW>(W + (size_t)((i + q) * nb + n) * H + m);
 #pragma unroll
-          for (int q = 0; q < 4; ++q) rb = gl_fma4(Qb[i + q], w[q], rb);
+          for (int q = 0; q < 4; ++q) rb = gv_fma<VW>(Qb[i + q], w[q], rb);
         }
-        for (; i < d; ++i) rb = gl_fma4(Qb[i], gl_ld4(W + (size_t)(i * nb + n) * H + m), rb);
+        for (; i < d; ++i) rb = gv_fma<VW>(Qb[i], gv_ld<VW>(W + (size_t)(i * nb + n) * H + m), rb);
       }
-      CR = make_float4(CR.x + rb.x, CR.y + rb.y, CR.z + rb.z, CR.w + rb.w);
+      CR = gv_add<VW>(CR, rb);
       const int jhi = (n == nb - 1) ? d - 1 : n;
       for (int j = n; j <= jhi; ++j) {
         float part = 0.0f;
         if (act) {
-          part = gl_dot4(CR, gl_ld4(TL + j * H + m), 0.0f);
-          gl_st4(Tb + j * H + m, gl_fma4(s[j], CR, gl_ld4(Tb + j * H + m)));
+          part = gv_dot<VW>(CR, gv_ld<VW>(TL + j * H + m), 0.0f);
+          gv_st(Tb + j * H + m, gv_fma<VW>(s[j], CR, gv_ld<VW>(Tb + j * H + m)));
         }
         part = warp_sum(part);
         if (lane == 0) sb[j] = sb[j] + part;
