@@ -1011,8 +1011,9 @@ inline GenericPlan generic_plan(const GpFlowDesc* d, int64_t B, int op, int sm_c
     const long long per_sm = (B + sm_count - 1) / sm_count;
     while (p.warps_per_cta > 1 && p.warps_per_cta / 2 >= per_sm) p.warps_per_cta /= 2;
   }
-  static const int on_chip_allowed = [] { const char* e = getenv("GPFLOW_GENERIC_ONCHIP"); return e == nullptr || e[0] != '0'; }();
-  if (on_chip_allowed && (size_t)kGenericSmemBudget > p.smem_scratch_off + 12 * p.scratch_stride) {
+  static const int on_chip_allowed = [] { const char* e = getenv("GPFLOW_GENERIC_ONCHIP"); return e == nullptr ? 1 : atoi(e); }();
+  const int on_chip_min_warps = on_chip_allowed >= 2 ? on_chip_allowed : 12;   // GPFLOW_GENERIC_ONCHIP=<n >= 2>: experiment knob
+  if (on_chip_allowed && (size_t)kGenericSmemBudget > p.smem_scratch_off + (size_t)on_chip_min_warps * p.scratch_stride) {
     int w = (int)(((size_t)kGenericSmemBudget - p.smem_scratch_off) / p.scratch_stride);
     if (w > kGenericMaxThreads / 32) w = kGenericMaxThreads / 32;
     p.on_chip = 1;

@@ -2,7 +2,7 @@
 import os, sys, torch
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import gpflow_b200 as G
-for d, nb, hidden in [(10, 9, (50, 50, 50)), (64, 63, (256, 256))]:
+for d, nb, hidden in [(10, 9, (50, 50, 50)), (64, 63, (256, 256))][: int(os.environ.get("SB_SHAPES", "2"))]:
     cfg = G.FlowConfig(d=d, nb=nb, hidden=hidden, n_steps=15)
     params = 0.03 * torch.randn(cfg.n_params, device="cuda")
     for B in (256, 1024, 2048):
