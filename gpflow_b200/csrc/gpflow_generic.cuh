@@ -86,6 +86,7 @@ struct GArgs {
   T* partials;           // [nwarps][3 + P]
   char* scratch;         // per-warp scratch, stride scratch_stride bytes (global mode)
   size_t scratch_stride;
+  int grad_red;          // 1: gradient partials accumulated with vector `red` instead of read-modify-write
   int cta_align;         // 1: named barrier between the CTA's active warps before every stage evaluation
   int on_chip;           // 1: the parameters and every warp's scratch live in the CTA's shared memory
   int vec4;              // 1: fp32, last hidden width and the last layer's parameter offset multiples of 4, 16-byte
@@ -409,7 +410,7 @@ struct Generic {
     const S* __restrict__ hin = sc + l.h[li];
     const S* __restrict__ Tin = sc + l.T[li];
     if constexpr (std::is_same<S, float>::value && GPF_GENERIC_MMA) {
-      gm_weight_grad(ab, Ub, no, hin, Tin, nin, d, no, nin, gw, lane);
+      gm_weight_grad(ab, Ub, no, hin, Tin, nin, d, no, nin, gw, lane, a.grad_red != 0);
       return;
     }
     for (int k0 = 0; k0 < no; k0 += KT) {
@@ -520,10 +521,10 @@ struct Generic {
       if (a.vec4) {
         if (H <= 64)
           gl_reverse_v<2>(W, gw, hL, TL, sc + l.R, sc + l.fb, sc + l.Qb, sc + l.s, sc + l.SQ, sc + l.hb[L], sc + l.Tb[L],
-                          sc + l.sb, d, nb, H, lane);
+                          sc + l.sb, d, nb, H, lane, a.grad_red != 0);
         else
           gl_reverse_v<4>(W, gw, hL, TL, sc + l.R, sc + l.fb, sc + l.Qb, sc + l.s, sc + l.SQ, sc + l.hb[L], sc + l.Tb[L],
-                          sc + l.sb, d, nb, H, lane);
+                          sc + l.sb, d, nb, H, lane, a.grad_red != 0);
         passes_done = true;
       }
     }
@@ -1102,6 +1103,9 @@ int launch_generic_impl(const GpFlowDesc* d_user, int op, const T* params, const
   // parameters) and -10 % at C5 (3260 -> 2920, 4.4 MB of parameters streamed per evaluation: free-running warps spread
   // that traffic) => on for parameter sets up to 256 KB.  GPFLOW_GENERIC_ALIGN=0/1 forces it (A/B measurements).
   static const int align_env = [] { const char* e = getenv("GPFLOW_GENERIC_ALIGN"); return e == nullptr ? -1 : (e[0] != '0'); }();
+  static const int red_env = [] { const char* e = getenv("GPFLOW_GENERIC_RED"); return e == nullptr ? -1 : (e[0] != '0'); }();
+  // same-box A/B: C3 1.39e5 -> 1.50e5 samples/s, C5 3357 -> 3496; GPFLOW_GENERIC_RED=0 restores the read-modify-write
+  a.grad_red = red_env >= 0 ? red_env : 1;
   a.cta_align = EULER ? 0 : (align_env >= 0 ? align_env : ((size_t)a.g.P * sizeof(T) <= 256 * 1024 ? 1 : 0));
   a.smem_scratch_off = (unsigned)pl.smem_scratch_off;
   const unsigned grid = (unsigned)(pl.nwarps / pl.warps_per_cta), threads = 32u * (unsigned)pl.warps_per_cta;

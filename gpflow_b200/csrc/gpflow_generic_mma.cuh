@@ -46,6 +46,21 @@ GPF_DEV float row_elem(const float* __restrict__ v0, const float* __restrict__ V
   return r == 0 ? v0[col] : V[(r - 1) * ld + col];
 }
 
+// Fire-and-forget accumulation into the warp's OWN gradient partial (no other warp touches it, and every address is
+// always updated by the same lane, so the sum order -- hence the result -- stays run-to-run deterministic): a vector
+// `red` instead of load + add + store takes the partial's L2 / HBM round trip off the warp's dependency chain.
+// GPF_GENERIC_RED=0 restores the read-modify-write.
+#ifndef GPF_GENERIC_RED
+#define GPF_GENERIC_RED 1
+#endif
+GPF_DEV void red_add_v2(float* p, float a, float b) {
+  asm volatile("red.global.add.v2.f32 [%0], {%1, %2};" ::"l"(__cvta_generic_to_global(p)), "f"(a), "f"(b) : "memory");
+}
+GPF_DEV void red_add_v4(float* p, float a, float b, float c, float d) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(__cvta_generic_to_global(p)), "f"(a), "f"(b), "f"(c), "f"(d)
+               : "memory");
+}
+
 constexpr int GM_NT = 8;  // n-tiles per accumulator block (64 output columns)
 
 // Y[r][n] = sum_k X[r][k] * Bm(k, n), r < 1 + d, n < N, k < K.  TRANS_B = false: Bm(k, n) = W[n * ldw + k] (forward:
@@ -180,7 +195,7 @@ GPF_DEV void gm_weight_grad_impl(const float* __restrict__ yb0, const float* __r
 // block is read-modify-written once with 64-bit accesses.  ~13 instead of ~35 (+ predicates) instructions per 3 mma.
 GPF_DEV void gm_weight_grad_fast(const float* __restrict__ yb0, const float* __restrict__ Yb, int ldyb,
                                  const float* __restrict__ x0, const float* __restrict__ X, int ldx, int d, int M, int N,
-                                 float* __restrict__ gw, int lane) {
+                                 float* __restrict__ gw, int lane, bool red) {
   const int g = lane >> 2, t = lane & 3;
   const int R = d + 1;
   for (int k0 = 0; k0 < M; k0 += 16) {
@@ -213,6 +228,14 @@ GPF_DEV void gm_weight_grad_fast(const float* __restrict__ yb0, const float* __r
       }
       float* __restrict__ g0 = gw + (size_t)(k0 + g) * N + mb + 2 * t;
       float* __restrict__ g1 = g0 + (size_t)8 * N;
+      if (GPF_GENERIC_RED && red) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          red_add_v2(g0 + 8 * i, c[i][0], c[i][1]);
+          red_add_v2(g1 + 8 * i, c[i][2], c[i][3]);
+        }
+        continue;
+      }
       float2 o0[8], o1[8];
 #pragma unroll
       for (int i = 0; i < 8; ++i) {
@@ -228,9 +251,10 @@ GPF_DEV void gm_weight_grad_fast(const float* __restrict__ yb0, const float* __r
   }
 }
 GPF_DEV void gm_weight_grad(const float* __restrict__ yb0, const float* __restrict__ Yb, int ldyb, const float* __restrict__ x0,
-                            const float* __restrict__ X, int ldx, int d, int M, int N, float* __restrict__ gw, int lane) {
+                            const float* __restrict__ X, int ldx, int d, int M, int N, float* __restrict__ gw, int lane,
+                            bool red) {
   if ((M & 15) == 0 && (N & 63) == 0 && (reinterpret_cast<uintptr_t>(gw) & 7) == 0)
-    gm_weight_grad_fast(yb0, Yb, ldyb, x0, X, ldx, d, M, N, gw, lane);
+    gm_weight_grad_fast(yb0, Yb, ldyb, x0, X, ldx, d, M, N, gw, lane, red);
   else if (d <= 7) gm_weight_grad_impl<1>(yb0, Yb, ldyb, x0, X, ldx, d, M, N, gw, lane);
   else if (d <= 15) gm_weight_grad_impl<2>(yb0, Yb, ldyb, x0, X, ldx, d, M, N, gw, lane);
   else gm_weight_grad_impl<0>(yb0, Yb, ldyb, x0, X, ldx, d, M, N, gw, lane);
@@ -260,6 +284,8 @@ template <> GPF_DEV GLv<4> gv_ld<4>(const float* p) { const float4 v = *reinterp
 template <> GPF_DEV GLv<2> gv_ld<2>(const float* p) { const float2 v = *reinterpret_cast<const float2*>(p); GLv<2> r; r.x[0] = v.x; r.x[1] = v.y; return r; }
 GPF_DEV void gv_st(float* p, const GLv<4>& a) { *reinterpret_cast<float4*>(p) = make_float4(a.x[0], a.x[1], a.x[2], a.x[3]); }
 GPF_DEV void gv_st(float* p, const GLv<2>& a) { *reinterpret_cast<float2*>(p) = make_float2(a.x[0], a.x[1]); }
+GPF_DEV void gv_red(float* p, const GLv<4>& a) { red_add_v4(p, a.x[0], a.x[1], a.x[2], a.x[3]); }
+GPF_DEV void gv_red(float* p, const GLv<2>& a) { red_add_v2(p, a.x[0], a.x[1]); }
 template <int VW> GPF_DEV float gv_dot(const GLv<VW>& a, const GLv<VW>& b, float acc) {   // same nesting as gl_dot4
 #pragma unroll
   for (int i = VW - 1; i >= 0; --i) acc = fmaf(a.x[i], b.x[i], acc);
@@ -315,7 +341,8 @@ template <int VW>
 GPF_DEV void gl_reverse_v(const float* __restrict__ W, float* __restrict__ gw, const float* __restrict__ hL,
                            const float* __restrict__ TL, const float* __restrict__ R, const float* __restrict__ fb,
                            const float* __restrict__ Qb, const float* __restrict__ s, const float* __restrict__ SQ,
-                           float* __restrict__ hb, float* __restrict__ Tb, float* sb, int d, int nb, int H, int lane) {
+                           float* __restrict__ hb, float* __restrict__ Tb, float* sb, int d, int nb, int H, int lane,
+                           bool red) {
   const GLv<VW> z4 = gv_zero<VW>();
   for (int m0 = 0; m0 < H; m0 += 32 * VW) {
     const int m = m0 + VW * lane;
@@ -336,7 +363,7 @@ GPF_DEV void gl_reverse_v(const float* __restrict__ W, float* __restrict__ gw, c
             const int nq = n0 + q <= nmax ? n0 + q : nmax;
             const size_t p = (size_t)(i * nb + nq);
             w[q] = gv_ld<VW>(W + p * H + m);
-            go[q] = gv_ld<VW>(gw + p * H + m);
+            go[q] = (GPF_GENERIC_RED && red) ? z4 : gv_ld<VW>(gw + p * H + m);
             r[q] = gv_ld<VW>(R + nq * H + m);
             fbp[q] = fb[p];
             dbp[q] = nsi * SQ[nq];
@@ -346,7 +373,11 @@ GPF_DEV void gl_reverse_v(const float* __restrict__ W, float* __restrict__ gw, c
             if (n0 + q <= nmax) {
               hbm = gv_fma<VW>(fbp[q], w[q], hbm);
               Ei = gv_fma<VW>(dbp[q], w[q], Ei);
-              gv_st(gw + (size_t)(i * nb + n0 + q) * H + m, gv_fma<VW>(fbp[q], hm, gv_fma<VW>(qbi, r[q], gv_fma<VW>(dbp[q], Ti, go[q]))));
+              {
+                const GLv<VW> u = gv_fma<VW>(fbp[q], hm, gv_fma<VW>(qbi, r[q], gv_fma<VW>(dbp[q], Ti, go[q])));
+                if (GPF_GENERIC_RED && red) gv_red(gw + (size_t)(i * nb + n0 + q) * H + m, u);
+                else gv_st(gw + (size_t)(i * nb + n0 + q) * H + m, u);
+              }
             }
         }
         gv_st(Tb + i * H + m, Ei);
