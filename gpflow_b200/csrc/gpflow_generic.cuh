@@ -396,14 +396,21 @@ struct Generic {
     const int nin = g.n[li], no = g.n[li + 1], d = g.d;
     T* __restrict__ gw = gacc + g.woff[li];
     T* __restrict__ gb = gacc + g.boff[li];
-    for (int k = lane; k < no; k += 32) gb[k] += eps_part<S>(ab[k]);
+    // every element of the partial is always updated by the same lane: `red` keeps the sum order (see red_add_v2)
+    auto acc_add = [&](T* p, T v) {
+      if constexpr (std::is_same<T, float>::value && GPF_GENERIC_RED) {
+        if (a.grad_red) { red_add_f32(p, v); return; }
+      }
+      *p += v;
+    };
+    for (int k = lane; k < no; k += 32) acc_add(gb + k, eps_part<S>(ab[k]));
     if (li == 0) {
       // W0[k][j] += ab[k] x_j + Ub[j][k];  W0[k][d] += ab[k] t      (lanes over k; rows are short)
       const S* x = sc + l.x;
       for (int k = lane; k < no; k += 32) {
         const S abk = ab[k];
-        for (int j = 0; j < d; ++j) gw[k * nin + j] += eps_part<S>(abk * x[j] + Ub[j * no + k]);
-        gw[k * nin + d] += eps_part<S>(abk * t);
+        for (int j = 0; j < d; ++j) acc_add(gw + k * nin + j, eps_part<S>(abk * x[j] + Ub[j * no + k]));
+        acc_add(gw + k * nin + d, eps_part<S>(abk * t));
       }
       return;
     }

@@ -53,6 +53,9 @@ GPF_DEV float row_elem(const float* __restrict__ v0, const float* __restrict__ V
 #ifndef GPF_GENERIC_RED
 #define GPF_GENERIC_RED 1
 #endif
+GPF_DEV void red_add_f32(float* p, float a) {
+  asm volatile("red.global.add.f32 [%0], %1;" ::"l"(__cvta_generic_to_global(p)), "f"(a) : "memory");
+}
 GPF_DEV void red_add_v2(float* p, float a, float b) {
   asm volatile("red.global.add.v2.f32 [%0], {%1, %2};" ::"l"(__cvta_generic_to_global(p)), "f"(a), "f"(b) : "memory");
 }
