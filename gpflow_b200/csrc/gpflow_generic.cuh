@@ -1013,7 +1013,9 @@ inline GenericPlan generic_plan(const GpFlowDesc* d, int64_t B, int op, int sm_c
   // global mode: 16 warps per SM as CTAs of GPFLOW_GENERIC_WPC warps
   static const int wpc_env = [] { const char* e = getenv("GPFLOW_GENERIC_WPC"); const int v = e ? atoi(e) : 0;
                                   return (v == 1 || v == 2 || v == 4 || v == 8 || v == 16) ? v : 0; }();
-  p.warps_per_cta = wpc_env ? wpc_env : 16;
+  // 16-warp CTAs where the warps are phase-aligned (small parameter sets, see launch_generic_impl); free-running warps do
+  // slightly better as 4 CTAs of 4 warps per SM (C5: 3616 -> 3738 samples/s, same box)
+  p.warps_per_cta = wpc_env ? wpc_env : ((size_t)g.P * es <= 256 * 1024 ? 16 : 4);
   long long nw = (long long)sm_count * 16;
   if (!wpc_env && B < nw) {   // small batch (one warp per sample): smaller CTAs so that the warps spread over all the SMs
     const long long per_sm = (B + sm_count - 1) / sm_count;
