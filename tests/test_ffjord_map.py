@@ -79,6 +79,28 @@ def test_step_halving_error_recorded_in_golden():
     assert g["err_halving"][0] < 2e-3      # 16 steps per block on the wide test points (integrator error, not parity)
 
 
+def test_abi_ffjord_desc_and_param_count_cpu():
+    """no compute: the library loads without a GPU, the ctypes descriptor matches the C struct (a wrong layout would move
+    n_blocks / hidden and change the count), bad descriptors come back as status codes, not exceptions"""
+    import ctypes
+    from gpflow_b200 import _lib
+    lib = _lib.load()
+    d = _lib.GpFlowFfjordDesc(abi_version=_lib.ABI_VERSION, dtype=_lib.F32, dim=10, n_hidden=2, n_blocks=3, n_steps=64, reverse=0)
+    d.hidden[0], d.hidden[1] = 64, 64
+    for i in range(3):
+        d.t_end[i] = 1.0
+    n = ctypes.c_int64(0)
+    assert lib.gpflow_ffjord_param_count(ctypes.byref(d), ctypes.byref(n)) == 0 and n.value == 17784
+    assert ctypes.sizeof(_lib.GpFlowFfjordDesc) == 4 * 4 + 7 * 4 + 3 * 4 + 8 * 8      # include/gpflow_b200.h: no padding
+    d.n_blocks = 9
+    assert lib.gpflow_ffjord_param_count(ctypes.byref(d), ctypes.byref(n)) == 1     # GPFLOW_ERR_BAD_DESC
+    d.n_blocks, d.abi_version = 3, 99
+    assert lib.gpflow_ffjord_param_count(ctypes.byref(d), ctypes.byref(n)) == 1
+    d.abi_version = _lib.ABI_VERSION
+    assert lib.gpflow_ffjord_integrate(ctypes.byref(d), ctypes.c_int64(4), None, None, None, None, None) == 3   # NULL pointer
+    assert lib.gpflow_ffjord_integrate(ctypes.byref(d), ctypes.c_int64(0), None, None, None, None, None) == 0   # empty batch
+
+
 # ---------------------------------------------------------------- GPU: the CUDA kernel
 def _need_cuda():
     if not torch.cuda.is_available():
