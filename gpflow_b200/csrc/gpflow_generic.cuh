@@ -434,7 +434,7 @@ struct Generic {
         }
 #pragma unroll
         for (int q = 0; q < KT; ++q)
-          if (k0 + q < no) gw[(k0 + q) * nin + m] += eps_part<S>(acc[q]);
+          if (k0 + q < no) acc_add(gw + (k0 + q) * nin + m, eps_part<S>(acc[q]));
       }
     }
   }
