@@ -63,6 +63,8 @@ class BNAFMap(torch.nn.Module):
         B = x.shape[0]
         y = torch.empty_like(x)
         logdet = torch.empty(B, dtype=torch.float32, device=x.device)
-        _lib.check(_lib.load().gpflow_bnaf_forward(ctypes.byref(self._desc), ctypes.c_int64(B), _ptr(self.flat), _ptr(x),
-                                                   _ptr(y), _ptr(logdet), _stream()))
+        flat = self.flat if self.flat.device == x.device else self.flat.to(x.device)
+        with torch.cuda.device(x.device):   # launch on x's device and its current stream
+            _lib.check(_lib.load().gpflow_bnaf_forward(ctypes.byref(self._desc), ctypes.c_int64(B), _ptr(flat), _ptr(x),
+                                                       _ptr(y), _ptr(logdet), _stream()))
         return y, logdet

@@ -97,8 +97,9 @@ class FFJORDMap(torch.nn.Module):
         y = torch.empty_like(x)
         logdet = torch.empty(B, dtype=x.dtype, device=x.device) if want_logdet else None
         desc = self._desc(x.dtype, reverse, n_steps)
-        _lib.check(_lib.load().gpflow_ffjord_integrate(ctypes.byref(desc), ctypes.c_int64(B), _ptr(flat), _ptr(x), _ptr(y),
-                                                       _ptr(logdet), _stream()))
+        with torch.cuda.device(x.device):   # launch on x's device and its current stream
+            _lib.check(_lib.load().gpflow_ffjord_integrate(ctypes.byref(desc), ctypes.c_int64(B), _ptr(flat), _ptr(x),
+                                                           _ptr(y), _ptr(logdet), _stream()))
         return y, logdet
 
     def forward(self, x, n_steps=None):

@@ -12,9 +12,11 @@ from __future__ import annotations
 from contextlib import ExitStack
 from typing import Optional
 
+import numpy as np
 import torch
 
 from . import _lib, data_parallel, ops
+from .res_net import Compose
 
 
 class GPFlowNetwork(torch.nn.Module):
@@ -42,7 +44,15 @@ class GPFlowNetwork(torch.nn.Module):
     def gp_flow(self, x, reverse=False, save_trajectories=False):
         if self.flow is None:
             return (x, torch.zeros_like(x).sum(1)) if not reverse else x
-        y = self.flow(x, reverse=reverse, save_trajectories=save_trajectories, _wrap=True, _sigma=self.sigma)
+        if isinstance(self.flow, Compose):
+            # nb_blocks != 1 (compose.py:5-69): erf once, every block in cube space, clip / erfinv once -- the literal
+            # sequence of network.py:174-182 (the blocks' kernels run without their erf / erfinv wrapper).
+            eps = ops.eps_of(x.dtype)
+            g = torch.erf(x / (np.sqrt(2.0) * self.sigma))
+            g = self.flow(g, reverse=reverse, save_trajectories=save_trajectories)
+            y = np.sqrt(2) * self.sigma * torch.erfinv(torch.clip(g, -1 + eps, 1 - eps))
+        else:
+            y = self.flow(x, reverse=reverse, save_trajectories=save_trajectories, _wrap=True, _sigma=self.sigma)
         if reverse:
             return y
         log_abs_det = ((y ** 2).sum(1) - (x ** 2).sum(1)) / (2.0 * self.sigma ** 2)
@@ -72,13 +82,15 @@ class GPFlowNetwork(torch.nn.Module):
         if x_map is None:
             x_map = self._map_points(x)
         flow = self.flow
-        cfg = flow.config(self.sigma)
         world = 1
         pg = self.process_group
         if pg is not None or (torch.distributed.is_available() and torch.distributed.is_initialized()):
             world = torch.distributed.get_world_size(pg)
         B = x.shape[0]
         gb = global_batch if global_batch is not None else B * world
+        if isinstance(flow, Compose):
+            return self._composed_training_step(x, x_map, gb, world, pg)
+        cfg = flow.config(self.sigma)
         euler = flow.euler_coef_penalization if flow._euler_active(x.dtype) else None
         zw = flow.draw_probes(cfg.n_eval, x) if euler is not None else None
         if world > 1:
@@ -106,11 +118,36 @@ class GPFlowNetwork(torch.nn.Module):
             else:
                 p.grad.copy_(g)
             off += n
-        sc = res["scalars"]
+        # fresh tensors, as the reference returns (the [grads | scalars] buffer is reused by the next step and mutated in
+        # place by the all-reduce; a caller that keeps losses across steps -- Lightning's self.log -- must not alias it)
+        sc = res["scalars"].clone()
         flow.regularization_value = sc[_lib.SCALAR_REG]
         if with_lagrangian:
             flow.lagrangian = sc[_lib.SCALAR_LAGR]
         return sc[_lib.SCALAR_OT], sc[_lib.SCALAR_REG]
+
+    def _composed_training_step(self, x, x_map, gb, world, pg):
+        """nb_blocks != 1: the blocks are chained through autograd (each block's forward / backward is one fused CUDA op,
+        `_FlowFunction`); loss mean over the GLOBAL batch, gradients summed over ranks."""
+        params = [q for q in self.flow.parameters()]
+        for q in params:
+            q.grad = None
+        with torch.enable_grad():
+            y, _ = self.gp_flow(x_map)
+            loss = ((x - y) ** 2).sum(-1).sum() / gb
+            reg = self.flow.regularization_coef()
+            (loss + reg).backward()
+        loss = loss.detach()
+        reg = torch.as_tensor(reg, dtype=x.dtype, device=x.device).detach().clone()
+        if world > 1:
+            flat = torch.cat([q.grad.reshape(-1) for q in params] + [loss.reshape(1)])
+            torch.distributed.all_reduce(flat, group=pg)
+            off = 0
+            for q in params:
+                q.grad.copy_(flat[off:off + q.numel()].view_as(q))
+                off += q.numel()
+            loss = flat[-1].clone()
+        return loss, reg
 
     # ---- network.py:191-253 -------------------------------------------------------------------
     def ot_map(self, x, reverse=False, no_grad_map=False, no_grad_gp_flow=False, return_log_det=False):

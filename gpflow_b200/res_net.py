@@ -18,7 +18,7 @@ import torch
 
 from . import _lib, ops
 from .ops import FlowConfig
-from .velocity_field import VelocityField
+from .velocity_field import CONTINUOUS_TIME, VelocityField
 
 
 class Compose(torch.nn.Module):
@@ -137,7 +137,7 @@ class ResNet(torch.nn.Module):
             raise NotImplementedError("gpflow_b200: the debug divergence accumulator (res_net.py:304-317) is not on the CUDA path")
         self.v = VelocityField(dim, velocity_dict.get("nb_neurons", [10]),
                                activ_func=velocity_dict.get("activ_func", "tanh"),
-                               time_state=velocity_dict.get("time_state", "continuous_time"),
+                               time_state=velocity_dict.get("time_state", CONTINUOUS_TIME),
                                incompressible=velocity_dict.get("incompressible", True),
                                nb_div_blocks=velocity_dict.get("nb_div_blocks", 1), dtype=dtype)
         self.dim = dim
@@ -192,6 +192,11 @@ class ResNet(torch.nn.Module):
         if id_final_layer != -1:
             if _wrap:
                 raise ValueError("id_final_layer is a cube-space option")
+            if torch.is_grad_enabled() and (x.requires_grad or any(q.requires_grad for q in params)):
+                # the reference's x_full[id] carries gradients (res_net.py:227-233); the trajectory output of the CUDA op
+                # does not, so a differentiable call integrates exactly id_final_layer steps instead
+                raise NotImplementedError("gpflow_b200: id_final_layer under autograd -- call with torch.no_grad(), or "
+                                          "use set_nb_layers_eval for a differentiable partial integration")
             return traj[id_final_layer]
         return y
 

@@ -10,12 +10,21 @@ import torch
 from .vector_field import VectorField
 
 
+# src/case.py:3-4 -- the reference's constants are the strings below ("continuous time" has a SPACE); the underscore
+# spelling is accepted as an alias because round-1 callers of this mirror used it.
+CONTINUOUS_TIME = "continuous time"
+STATIONARY = "stationary"
+_CONTINUOUS_ALIASES = (CONTINUOUS_TIME, "continuous_time")
+
+
 class VelocityField(torch.nn.Module):
-    def __init__(self, dim, nb_neurons, activ_func="tanh", time_state="continuous_time", incompressible=True,
+    def __init__(self, dim, nb_neurons, activ_func="tanh", time_state=CONTINUOUS_TIME, incompressible=True,
                  nb_div_blocks=1, dtype=torch.float32):
         super().__init__()
-        if str(time_state) != "continuous_time":
-            raise NotImplementedError("gpflow_b200: only Case.continuous_time is on the CUDA path")
+        if str(time_state) not in _CONTINUOUS_ALIASES:
+            raise NotImplementedError("gpflow_b200: only Case.continuous_time (%r) is on the CUDA path, got %r"
+                                      % (CONTINUOUS_TIME, time_state))
+        time_state = CONTINUOUS_TIME
         if not incompressible:
             raise NotImplementedError("gpflow_b200: only the incompressible (Gaussian-preserving) velocity is on the CUDA path")
         self.time_state, self.incompressible = time_state, incompressible
