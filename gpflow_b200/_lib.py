@@ -17,6 +17,7 @@ GPFLOW_MAX_HIDDEN = 8
 F32, F64 = 0, 1
 OP_FORWARD, OP_TRAIN_STEP, OP_BACKWARD = 0, 1, 2
 FLAG_WRAP_GAUSS, FLAG_LAGRANGIAN, FLAG_EULER_PEN, FLAG_REVERSE, FLAG_FORCE_GENERIC, FLAG_FORCE_V1 = 0x1, 0x2, 0x4, 0x8, 0x10, 0x20
+FLAG_FORCE_TC = 0x40
 SCALAR_OT, SCALAR_REG, SCALAR_LAGR, NUM_SCALARS = 0, 1, 2, 3
 
 EXPORTS = [
@@ -80,6 +81,7 @@ def load():
         raise GpFlowLibraryError(
             "gpflow_b200 CUDA library not built: %s is missing. Build it with "
             "`python -c 'import __graft_entry__ as g; g.build()'` (needs nvcc). There is no CPU fallback." % LIB_PATH)
+    import torch  # noqa: F401  -- loads the CUDA runtime (libcudart.so.12) this library is dynamically linked against
     lib = ctypes.CDLL(LIB_PATH)
     P, D = ctypes.c_void_p, ctypes.POINTER(GpFlowDesc)
     lib.gpflow_param_count.restype = ctypes.c_int64

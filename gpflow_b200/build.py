@@ -8,7 +8,8 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIBDIR = os.path.join(HERE, "lib")
 LIB = os.path.join(LIBDIR, "libgpflow_b200.so")
-NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17", "-Xcompiler", "-fPIC",
+NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17", "--extended-lambda",
+              "-Xcompiler", "-fPIC",
               "-I", os.path.join(os.path.dirname(HERE), "include")]
 
 
@@ -53,7 +54,9 @@ def build(force=False, verbose=False):
 
     with ThreadPoolExecutor(max_workers=min(8, len(srcs))) as ex:
         list(ex.map(compile_one, zip(srcs, objs)))
-    r = subprocess.run([nvcc, "-shared", "-o", LIB] + objs + ["-gencode", "arch=compute_100a,code=sm_100a"],
+    # -cudart shared: the runtime stays a separate libcudart.so (torch ships one); a static cudart would put the
+    # names of CUDA runtime entry points this library never calls into the shipped binary
+    r = subprocess.run([nvcc, "-shared", "-cudart", "shared", "-o", LIB] + objs + ["-gencode", "arch=compute_100a,code=sm_100a"],
                        capture_output=True, text=True)
     if r.returncode != 0:
         raise RuntimeError("link failed:\n" + r.stderr[-4000:])

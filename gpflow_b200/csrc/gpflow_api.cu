@@ -6,6 +6,7 @@
 #include <stdio.h>
 #include <string.h>
 #include <math.h>
+#include <stdlib.h>
 
 #include <mutex>
 
@@ -84,6 +85,18 @@ bool sf2_match(const GpFlowDesc* d, int op) {
   return d->n_steps <= 1024;
 }
 
+// tc (chunked tensor-core path) takes the wide fp32 shapes without Euler penalization once the batch is large enough to
+// fill 128-row MMA tiles on every SM; GPFLOW_TC_MIN_BATCH overrides the threshold, GPFLOW_FLAG_FORCE_TC ignores it.
+int64_t tc_min_batch() {
+  static const int64_t v = [] { const char* e = getenv("GPFLOW_TC_MIN_BATCH"); return e ? (int64_t)atoll(e) : (int64_t)2048; }();
+  return v;
+}
+bool tc_selected(const GpFlowDesc* d, int64_t B) {
+  if (d->flags & (GPFLOW_FLAG_FORCE_GENERIC | GPFLOW_FLAG_EULER_PEN)) return false;
+  if (small_match(d, nullptr) || !tc_match(d)) return false;
+  return (d->flags & GPFLOW_FLAG_FORCE_TC) != 0 || B >= tc_min_batch();
+}
+
 template <typename T>
 int dispatch(const GpFlowDesc* d, int op, const Ptrs<T>& p, int64_t B, void* ws, size_t wsb, cudaStream_t st);
 
@@ -94,6 +107,10 @@ int dispatch<float>(const GpFlowDesc* d, int op, const Ptrs<float>& p, int64_t B
   SmallShape s;
   if (sf2_match(d, op)) return sf2_15_15_f32(d, op, &p, B, ws, wsb, st, sm);
   if (small_match(d, &s)) return euler ? small_2_1_15_15_f32_euler(d, op, &p, B, ws, wsb, st, sm) : small_2_1_15_15_f32(d, op, &p, B, ws, wsb, st, sm);
+  if (tc_selected(d, B))
+    return tc_f32(d, op, p.params, p.x_in, p.x_data, p.grad_y, p.y_out, p.logdet_out, p.traj_out, p.grad_x_out, p.grads_out,
+                  p.scalars_out, B, ws, wsb, st, sm, nullptr, 0.0);
+  if ((d->flags & GPFLOW_FLAG_FORCE_TC) && !(d->flags & GPFLOW_FLAG_FORCE_GENERIC)) return GPFLOW_ERR_UNSUPPORTED;
   return (euler ? generic_f32_euler : generic_f32)(d, op, p.params, p.x_in, p.x_data, p.grad_y, p.reg_cot, p.zw, p.y_out,
                                                  p.logdet_out, p.traj_out, p.grad_x_out, p.grads_out, p.scalars_out, B, ws,
                                                  wsb, st, sm, nullptr, 0.0);
@@ -228,6 +245,10 @@ int gpflow_query_workspace(const GpFlowDesc* d, int64_t B, int op, size_t* bytes
     *bytes = small_workspace(d, B, op, (int)np);
     return GPFLOW_OK;
   }
+  if (d->dtype == GPFLOW_F32 && tc_selected(d, B)) {
+    *bytes = tc_workspace(d, B, op);
+    return GPFLOW_OK;
+  }
   *bytes = generic_workspace_bytes(d, B, op);
   return GPFLOW_OK;
 }
@@ -266,6 +287,9 @@ int gpflow_velocity(const GpFlowDesc* d, int64_t B, const void* params, const vo
   dd.flags &= ~(uint32_t)GPFLOW_FLAG_EULER_PEN;
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   const int sm = device_info().sm_count;
+  if (d->dtype == GPFLOW_F32 && (d->flags & GPFLOW_FLAG_FORCE_TC) && tc_match(&dd))   // workspace: query with FORCE_TC set
+    return tc_f32(&dd, GPFLOW_OP_FORWARD, (const float*)params, (const float*)x, nullptr, nullptr, nullptr, nullptr, nullptr,
+                  nullptr, nullptr, nullptr, B, ws, wsb, st, sm, (float*)v_out, t);
   if (d->dtype == GPFLOW_F32)
     return generic_f32(&dd, GPFLOW_OP_FORWARD, (const float*)params, (const float*)x, nullptr, nullptr, nullptr,
                                  nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, B, ws, wsb, st, sm,
@@ -287,6 +311,8 @@ int gpflow_kernel_variant(const GpFlowDesc* d, int op, char* buf, size_t n) {
     snprintf(buf, n, "gpflow_sf2_kernel<f32,d=2,nb=1,H=[15,15],%s>", mode);
   else if (small_match(d, &s))
     snprintf(buf, n, "gpflow_small_kernel<%s,d=%d,nb=%d,H=[%d,%d],%s%s>", ty, s.d, s.nb, s.h1, s.h2, mode, eu);
+  else if (d->dtype == GPFLOW_F32 && tc_selected(d, (d->flags & GPFLOW_FLAG_FORCE_TC) ? 0 : tc_min_batch()))
+    snprintf(buf, n, "gpflow_tc<f32,tcgen05,%s> (batches >= %lld; generic below)", mode, (long long)tc_min_batch());
   else
     snprintf(buf, n, "gpflow_generic_kernel<%s,%s%s>", ty, mode, eu);
   return GPFLOW_OK;

@@ -23,6 +23,7 @@
 #include <cuda.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdio.h>
 
 #include "gpflow_common.cuh"
 
@@ -277,7 +278,7 @@ struct EpiCtx {
 //   num_tiles(p), decode(p, t, tile),
 //   fetch_a(p, tile, kc, ptid, float* frag)          frag: MT / 8 floats in A_MODE order
 //   fetch_b(p, tile, kc, ptid, float* frag)          when !B_TMA (NT / 8 floats, B_MODE order)
-//   tmap(p), tma_coords(p, tile, kc, c0, r_hi, r_lo) when B_TMA
+//   tmap(p, tile), tma_coords(p, tile, kc, c0, r_hi, r_lo) when B_TMA
 //   epilogue(p, tile, ctx, row, col0, ncols, v)      v[i] = D[row][col0 + i]
 // ---------------------------------------------------------------------------------------------------------------
 template <class Op>
@@ -316,7 +317,6 @@ __global__ void __launch_bounds__(kThreads, 1) tc_gemm_kernel(const __grid_const
       mbar_init(&accempty_bar[b], kEpiWarps);
     }
     fence_barrier_init();
-    if constexpr (Op::B_TMA) prefetch_tensormap(Op::tmap(p));
   }
   if (warp == 1) tmem_alloc(tmem_holder, SM::kTmemCols);
   tcgen05_fence_before();
@@ -346,8 +346,8 @@ __global__ void __launch_bounds__(kThreads, 1) tc_gemm_kernel(const __grid_const
             mbar_expect_tx(&full_bar[stage], 2 * SM::kBTileBytes);
             int c0, r_hi, r_lo;
             Op::tma_coords(p, tile, kc, c0, r_hi, r_lo);
-            tma_load_2d(st + 2 * kATileBytes, Op::tmap(p), c0, r_hi, &full_bar[stage]);
-            tma_load_2d(st + 2 * kATileBytes + SM::kBTileBytes, Op::tmap(p), c0, r_lo, &full_bar[stage]);
+            tma_load_2d(st + 2 * kATileBytes, Op::tmap(p, tile), c0, r_hi, &full_bar[stage]);
+            tma_load_2d(st + 2 * kATileBytes + SM::kBTileBytes, Op::tmap(p, tile), c0, r_lo, &full_bar[stage]);
             if (++stage == Op::STAGES) { stage = 0; phase ^= 1; }
           }
         }

@@ -67,7 +67,7 @@ def _dtype_code(dtype):
 
 def make_desc(cfg: FlowConfig, dtype, *, wrap=False, reverse=False, training=False, lagrangian=False,
               euler_coef: Optional[float] = None, loss_scale: float = 1.0, force_generic=False,
-              force_v1=False) -> GpFlowDesc:
+              force_v1=False, force_tc=False) -> GpFlowDesc:
     d = GpFlowDesc()
     d.abi_version = _lib.GPFLOW_ABI_VERSION
     d.dtype = _dtype_code(dtype)
@@ -98,6 +98,8 @@ def make_desc(cfg: FlowConfig, dtype, *, wrap=False, reverse=False, training=Fal
         flags |= _lib.FLAG_FORCE_GENERIC
     if force_v1:
         flags |= _lib.FLAG_FORCE_V1
+    if force_tc:
+        flags |= _lib.FLAG_FORCE_TC
     d.flags = flags
     return d
 
@@ -150,7 +152,7 @@ def _prep_zw(zw, desc, cfg, dtype, device):
 
 def flow_forward(cfg: FlowConfig, params: torch.Tensor, x: torch.Tensor, *, wrap=False, reverse=False,
                  training=False, lagrangian=False, euler_coef=None, zw=None, want_logdet=False, want_traj=False,
-                 want_scalars=True, loss_scale: Optional[float] = None, force_generic=False, force_v1=False):
+                 want_scalars=True, loss_scale: Optional[float] = None, force_generic=False, force_v1=False, force_tc=False):
     """ResNet.forward (raw, cube space) or Network.gp_flow (wrap=True).  Returns dict(y, logdet, traj, scalars)."""
     x = _check_cuda("x", x)
     dtype = x.dtype
@@ -159,7 +161,7 @@ def flow_forward(cfg: FlowConfig, params: torch.Tensor, x: torch.Tensor, *, wrap
     params = _check_cuda("params", params, dtype, (cfg.n_params,))
     desc = make_desc(cfg, dtype, wrap=wrap, reverse=reverse, training=training, lagrangian=lagrangian,
                      euler_coef=euler_coef, loss_scale=(1.0 / max(B, 1)) if loss_scale is None else loss_scale,
-                     force_generic=force_generic, force_v1=force_v1)
+                     force_generic=force_generic, force_v1=force_v1, force_tc=force_tc)
     zw = _prep_zw(zw, desc, cfg, dtype, x.device)
     y = torch.empty_like(x)
     logdet = torch.empty(B, dtype=dtype, device=x.device) if (want_logdet and wrap) else None
@@ -175,7 +177,7 @@ def flow_forward(cfg: FlowConfig, params: torch.Tensor, x: torch.Tensor, *, wrap
 
 def fused_train_step(cfg: FlowConfig, params: torch.Tensor, x_data: torch.Tensor, x_map: torch.Tensor, *,
                      euler_coef=None, zw=None, lagrangian=False, loss_scale: Optional[float] = None, want_y=False,
-                     want_grad_x=False, out: Optional[torch.Tensor] = None, force_generic=False, force_v1=False):
+                     want_grad_x=False, out: Optional[torch.Tensor] = None, force_generic=False, force_v1=False, force_tc=False):
     """loss_gp_flow + regularization_coef + backward of the GP branch (network.py:70-84,104-111) in one fused call.
 
     Returns dict(buf, grads, scalars, y, grad_x).  `buf` is ONE contiguous tensor [P + 3] = [grads | ot, reg, lagr]
@@ -190,7 +192,7 @@ def fused_train_step(cfg: FlowConfig, params: torch.Tensor, x_data: torch.Tensor
     params = _check_cuda("params", params, dtype, (cfg.n_params,))
     desc = make_desc(cfg, dtype, wrap=True, training=False, lagrangian=lagrangian, euler_coef=euler_coef,
                      loss_scale=(1.0 / max(B, 1)) if loss_scale is None else loss_scale, force_generic=force_generic,
-                     force_v1=force_v1)
+                     force_v1=force_v1, force_tc=force_tc)
     zw = _prep_zw(zw, desc, cfg, dtype, x_map.device)
     P = cfg.n_params
     if out is None:
@@ -213,7 +215,7 @@ def fused_train_step(cfg: FlowConfig, params: torch.Tensor, x_data: torch.Tensor
 
 def flow_backward(cfg: FlowConfig, params: torch.Tensor, x_in: torch.Tensor, grad_y: torch.Tensor, *, wrap=False,
                   reverse=False, training=False, euler_coef=None, zw=None, reg_cotangent: Optional[torch.Tensor] = None,
-                  loss_scale: Optional[float] = None, want_grad_x=True, force_generic=False, force_v1=False):
+                  loss_scale: Optional[float] = None, want_grad_x=True, force_generic=False, force_v1=False, force_tc=False):
     """Reverse sweep for an arbitrary loss on top of the flow: returns (grads [P], grad_x [B,d] or None)."""
     x_in = _check_cuda("x_in", x_in)
     dtype = x_in.dtype
@@ -223,7 +225,7 @@ def flow_backward(cfg: FlowConfig, params: torch.Tensor, x_in: torch.Tensor, gra
     params = _check_cuda("params", params, dtype, (cfg.n_params,))
     desc = make_desc(cfg, dtype, wrap=wrap, reverse=reverse, training=training, euler_coef=euler_coef,
                      loss_scale=(1.0 / max(B, 1)) if loss_scale is None else loss_scale, force_generic=force_generic,
-                     force_v1=force_v1)
+                     force_v1=force_v1, force_tc=force_tc)
     zw = _prep_zw(zw, desc, cfg, dtype, x_in.device)
     if reg_cotangent is not None:
         reg_cotangent = _check_cuda("reg_cotangent", reg_cotangent.reshape(1).to(dtype), dtype, (1,))

@@ -6,12 +6,12 @@ import torch
 from . import _lib, ops
 
 
-def velocity(vf, x: torch.Tensor, t) -> torch.Tensor:
+def velocity(vf, x: torch.Tensor, t, force_tc=False) -> torch.Tensor:
     """VelocityField.__call__(x, t) (velocity_field.py:118-126) on the GPU."""
     cfg = ops.FlowConfig(d=vf.dim, nb=vf.nb_div_blocks, hidden=tuple(vf.v.neurons[1:-1]), n_steps=1)
     x = ops._check_cuda("x", x)
     flat = vf.flat_parameters().detach()
-    desc = ops.make_desc(cfg, x.dtype, force_generic=True)
+    desc = ops.make_desc(cfg, x.dtype, force_generic=not force_tc, force_tc=force_tc)
     out = torch.empty_like(x)
     lib = _lib.load()
     with torch.cuda.device(x.device):

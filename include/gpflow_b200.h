@@ -55,6 +55,9 @@ typedef enum GpFlowOp { GPFLOW_OP_FORWARD = 0, GPFLOW_OP_TRAIN_STEP = 1, GPFLOW_
 #define GPFLOW_FLAG_REVERSE 0x8u    /* integrate from t0 = dt*n_steps_nominal with -dt (res_net.py:217-219)          */
 #define GPFLOW_FLAG_FORCE_GENERIC 0x10u /* testing aid: bypass the specialised small-d kernels                         */
 #define GPFLOW_FLAG_FORCE_V1 0x20u      /* testing aid: use the register-resident v1 small-d kernel instead of sf2     */
+#define GPFLOW_FLAG_FORCE_TC 0x40u      /* testing aid: use the chunked tensor-core (tcgen05) path whatever the batch size;
+                                           GPFLOW_ERR_UNSUPPORTED if the shape is outside it (fp32, no Euler, d <= 64,
+                                           hidden widths <= 256).  Without it the path is taken for batches >= 2048.   */
 
 /*
  * One GP flow = get_gp_flow(dim, velocity_dict, nb_layers_gp, T_final, ...) with nb_blocks == 1

@@ -45,7 +45,7 @@ struct OpPlain {
     const int rem = p.N - tl.n0;
     tl.n = rem >= NT ? NT : (rem + 15) / 16 * 16;
   }
-  GPF_DEV static const CUtensorMap* tmap(const Params& p) { return &p.map; }
+  GPF_DEV static const CUtensorMap* tmap(const Params& p, const Tile&) { return &p.map; }
   GPF_DEV static void tma_coords(const Params& p, const Tile& tl, int kc, int& c0, int& r_hi, int& r_lo) {
     c0 = kc * KC; r_hi = tl.n0; r_lo = p.npad + tl.n0;
   }
