@@ -336,37 +336,35 @@ __global__ void tc_tb_mid_kernel(TcDims g, int l, const float* __restrict__ Tl, 
   const size_t o = ((size_t)d * S + s) * H + k;
   Ub[o] = fmaf(Ub[o], sp, acc * (-2.f * Tl[o]));
 }
-// first layer, reverse (A.4, l = 1): in Ub: Tb_1 rows and hb_1; ab_1 = hb sp + (sum_j Tb_1[j] W1x[:, j]) (-2 h sp),
-// dW1x[:, j] += sum_s (ab_1 x_j + sp Tb_1[j]),  dw1t += sum_s ab_1 t,  db1 += sum_s ab_1,  xbar_j += W1x[:, j] . ab_1.
-// Block = 8 samples x Hp1 units; per-block partial gradients [Hp1][d + 2] (summed by tc_l1_reduce_kernel).
-__global__ void tc_layer1_bwd_kernel(TcDims g, const float* __restrict__ W1T, const float* __restrict__ T1, const float* __restrict__ sp1,
-                                     const float* __restrict__ Ub, const float* __restrict__ x, float t, float* __restrict__ part,
-                                     float* __restrict__ ybar) {
-  __shared__ float xs[TC_DMAX][TC_L1_SPB];
+// first layer, reverse (A.4, l = 1), part a.  In Ub: Tb_1 rows and hb_1 (row block d).
+//   ab_1 = hb sp + (sum_j Tb_1[j] W1x[:, j]) (-2 h sp)   -> written over hb_1 (row block d of Ub)
+//   xbar_j += W1x[:, j] . ab_1
+// Block = 4 samples x Hp1 units.
+constexpr int TC_L1B_SPB = 4;
+__global__ void tc_layer1_bwd_a_kernel(TcDims g, const float* __restrict__ W1T, const float* __restrict__ T1, const float* __restrict__ sp1,
+                                       float* __restrict__ Ub, float* __restrict__ ybar) {
   __shared__ float xbs[8][TC_DMAX];   // per-warp partial dots, summed in a fixed order
   const int H = g.Hp[1], d = g.d, S = g.S;
-  const int s0 = blockIdx.x * TC_L1_SPB, k = threadIdx.x, lane = k & 31, warp = k >> 5, nwarp = H >> 5;
-  for (int e = threadIdx.x; e < d * TC_L1_SPB; e += blockDim.x) xs[e / TC_L1_SPB][e % TC_L1_SPB] = x[(size_t)(e / TC_L1_SPB) * S + s0 + e % TC_L1_SPB];
-  __syncthreads();
-  float w[TC_DMAX], gw[TC_DMAX];
+  const int k = threadIdx.x, lane = k & 31, warp = k >> 5, nwarp = H >> 5;
+  float w[TC_DMAX];
 #pragma unroll
-  for (int j = 0; j < TC_DMAX; ++j) { w[j] = j < d ? W1T[j * H + k] : 0.f; gw[j] = 0.f; }
-  float gt = 0.f, gb = 0.f;
-  for (int q = 0; q < TC_L1_SPB; ++q) {
-    const int s = s0 + q;
+  for (int j = 0; j < TC_DMAX; ++j) w[j] = j < d ? W1T[j * H + k] : 0.f;
+  for (int q = 0; q < TC_L1B_SPB; ++q) {
+    const int s = blockIdx.x * TC_L1B_SPB + q;
     const float sp = sp1[(size_t)s * H + k];
     const float h = T1[((size_t)d * S + s) * H + k];
-    float acc = 0.f;
+    float acc0 = 0.f, acc1 = 0.f;
 #pragma unroll
-    for (int j = 0; j < TC_DMAX; ++j)
-      if (j < d) acc = fmaf(Ub[((size_t)j * S + s) * H + k], w[j], acc);
-    const float ab = fmaf(Ub[((size_t)d * S + s) * H + k], sp, acc * (-2.f * h * sp));
-    gt = fmaf(ab, t, gt);
-    gb += ab;
+    for (int j = 0; j < TC_DMAX; j += 2) {
+      if (j < d) acc0 = fmaf(Ub[((size_t)j * S + s) * H + k], w[j], acc0);
+      if (j + 1 < d) acc1 = fmaf(Ub[((size_t)(j + 1) * S + s) * H + k], w[j + 1], acc1);
+    }
+    const size_t o = ((size_t)d * S + s) * H + k;
+    const float ab = fmaf(Ub[o], sp, (acc0 + acc1) * (-2.f * h * sp));
+    Ub[o] = ab;
 #pragma unroll
     for (int j = 0; j < TC_DMAX; ++j)
       if (j < d) {
-        gw[j] += fmaf(ab, xs[j][q], sp * Ub[((size_t)j * S + s) * H + k]);
         const float dot = warp_sum(w[j] * ab);
         if (lane == 0) xbs[warp][j] = dot;
       }
@@ -378,43 +376,77 @@ __global__ void tc_layer1_bwd_kernel(TcDims g, const float* __restrict__ W1T, co
     }
     __syncthreads();
   }
-  float* o = part + ((size_t)blockIdx.x * H + k) * (d + 2);
-#pragma unroll
-  for (int j = 0; j < TC_DMAX; ++j)
-    if (j < d) o[j] = gw[j];
-  o[d] = gt;
-  o[d + 1] = gb;
 }
-__global__ void tc_l1_reduce_kernel(int nblk, int n, const float* __restrict__ part, float* __restrict__ gW1) {
+// part b: dW1x[:, j] += sum_s (ab_1 x_j + sp Tb_1[j]),  dw1t += sum_s ab_1 t,  db1 += sum_s ab_1.
+// Grid (Hp1 / 32, ceil(d / 8), nz): a block reduces 8 tangent directions over its sample range (8 warps stride the
+// samples), partials [nz][Hp1][d + 2] are summed in a fixed order by tc_reduce_add_kernel.
+__global__ void __launch_bounds__(256) tc_layer1_bwd_b_kernel(TcDims g, const float* __restrict__ sp1, const float* __restrict__ Ub,
+                                                               const float* __restrict__ x, float t, int s_per_z, float* __restrict__ part) {
+  __shared__ float red[8][10][33];
+  const int H = g.Hp[1], d = g.d, S = g.S;
+  const int lane = threadIdx.x, wy = threadIdx.y, k = blockIdx.x * 32 + lane, j0 = blockIdx.y * 8;
+  const int s_lo = blockIdx.z * s_per_z, s_hi = s_lo + s_per_z < S ? s_lo + s_per_z : S;
+  float acc[8], gt = 0.f, gb = 0.f;
+#pragma unroll
+  for (int e = 0; e < 8; ++e) acc[e] = 0.f;
+  for (int s = s_lo + wy; s < s_hi; s += 8) {
+    const float sp = sp1[(size_t)s * H + k];
+    const float ab = Ub[((size_t)d * S + s) * H + k];
+    gt = fmaf(ab, t, gt);
+    gb += ab;
+#pragma unroll
+    for (int e = 0; e < 8; ++e)
+      if (j0 + e < d) acc[e] += fmaf(ab, x[(size_t)(j0 + e) * S + s], sp * Ub[((size_t)(j0 + e) * S + s) * H + k]);
+  }
+#pragma unroll
+  for (int e = 0; e < 8; ++e) red[wy][e][lane] = acc[e];
+  red[wy][8][lane] = gt;
+  red[wy][9][lane] = gb;
+  __syncthreads();
+  if (wy == 0) {
+    float* o = part + ((size_t)blockIdx.z * H + k) * (d + 2);
+    for (int e = 0; e < 10; ++e) {
+      float v = 0.f;
+      for (int r = 0; r < 8; ++r) v += red[r][e][lane];
+      if (e < 8) { if (j0 + e < d) o[j0 + e] = v; }
+      else if (blockIdx.y == 0) o[d + (e - 8)] = v;
+    }
+  }
+}
+// acc[e] += sum_z part[z][e]  (fixed order)
+__global__ void tc_reduce_add_kernel(int nz, int n, const float* __restrict__ part, float* __restrict__ acc) {
   const int e = blockIdx.x * blockDim.x + threadIdx.x;
   if (e >= n) return;
   float s = 0.f;
-  for (int b = 0; b < nblk; ++b) s += part[(size_t)b * n + e];
-  gW1[e] += s;
+  for (int z = 0; z < nz; ++z) s += part[(size_t)z * n + e];
+  acc[e] += s;
 }
-// bias gradients of the hidden layers: gb[k] += sum_s ab[s][k].  Block = 32 units x 8 sample strips.
-__global__ void tc_colsum_kernel(int S, int H, const float* __restrict__ ab, float* __restrict__ gb) {
+// bias gradients of the hidden layers: partial column sums part[z][k] = sum_{rows of split z} ab[r][k].
+// Grid (H / 32, nz), block (32, 8).
+__global__ void tc_colsum_kernel(int S, int H, int s_per_z, const float* __restrict__ ab, float* __restrict__ part) {
   __shared__ float red[8][33];
   const int k = blockIdx.x * 32 + threadIdx.x, y = threadIdx.y;
+  const int s_lo = blockIdx.y * s_per_z, s_hi = s_lo + s_per_z < S ? s_lo + s_per_z : S;
   float s = 0.f;
   if (k < H)
-    for (int r = y; r < S; r += 8) s += ab[(size_t)r * H + k];
+    for (int r = s_lo + y; r < s_hi; r += 8) s += ab[(size_t)r * H + k];
   red[y][threadIdx.x] = s;
   __syncthreads();
   if (y == 0 && k < H) {
     float t = 0.f;
     for (int q = 0; q < 8; ++q) t += red[q][threadIdx.x];
-    gb[k] += t;
+    part[(size_t)blockIdx.y * H + k] = t;
   }
 }
-// db_{L+1}[(i,n)] += sum_s fb_(i,n)[s],  fb = 2 (Qb_i SX_n - x_i SQ_n), kept rows only.  Block = 16 x 16 (i, n) tile.
+// db_{L+1}[(i,n)] = sum_s fb_(i,n)[s],  fb = 2 (Qb_i SX_n - x_i SQ_n), kept rows only: partial sums over 256-sample
+// splits, part[z][i nb + n].  Grid (ceil(nb / 16), ceil(d / 16), S / 256), block 16 x 16 (i, n).
 __global__ void tc_db3_kernel(TcDims g, const float* __restrict__ Qb, const float* __restrict__ x, const float* __restrict__ SX,
-                              const float* __restrict__ SQ, float* __restrict__ gb3) {
+                              const float* __restrict__ SQ, float* __restrict__ part) {
   __shared__ float a[4][16][65];
   const int S = g.S, i = blockIdx.y * 16 + threadIdx.y, n = blockIdx.x * 16 + threadIdx.x;
   const int tid = threadIdx.y * 16 + threadIdx.x;
   float acc = 0.f;
-  for (int s0 = 0; s0 < S; s0 += 64) {
+  for (int s0 = blockIdx.z * 256; s0 < blockIdx.z * 256 + 256; s0 += 64) {
     for (int e = tid; e < 4 * 16 * 64; e += 256) {
       const int arr = e / 1024, r = (e / 64) % 16, c = e % 64;
       const int row = (arr < 2 ? blockIdx.y : blockIdx.x) * 16 + r;
@@ -428,7 +460,7 @@ __global__ void tc_db3_kernel(TcDims g, const float* __restrict__ Qb, const floa
       acc += a[0][threadIdx.y][c] * a[2][threadIdx.x][c] - a[1][threadIdx.y][c] * a[3][threadIdx.x][c];
     __syncthreads();
   }
-  if (i < g.d && n < g.nb && n <= i) gb3[i * g.nb + n] += 2.f * acc;
+  if (i < g.d && n < g.nb) part[(size_t)blockIdx.z * g.nout + i * g.nb + n] = n <= i ? 2.f * acc : 0.f;
 }
 
 // ---------------------------------------------------------------------------------------------------------------

@@ -13,6 +13,7 @@ namespace tc {
 //   mode 0  value rows     h_l = tanh(h_{l-1} W_l^T + b_l), sp_l = 1 - h_l^2                  (vector_field.py:84-88)
 //   mode 1  tangent rows   T_l[j] = sp_l (.) (T_{l-1}[j] W_l^T), rows r = j S + s              (vector_field.py:119-126)
 //   mode 2  plain          reverse through W_l: [Tb_{l-1}; hb_{l-1}] = [Ub_l; ab_l] W_l  (B operand = W_l^T copy)
+//   mode 3  last layer F   F[q][s] = W_{L+1}[q] . h_L[s] + b[q] for ALL output rows q (N tiles), column-layout store
 // ---------------------------------------------------------------------------------------------------------------
 template <int NT_, int ST_>
 struct OpLayer {
@@ -27,14 +28,20 @@ struct OpLayer {
     const float* aux;
     const float* bias;
     long long M;
-    int K, N, lo_row, mode, S;
+    int K, N, lo_row, mode, S, ntn;   // ntn: number of N tiles (1 for the hidden layers)
   };
-  struct Tile { int nk, n; long long m0; };
-  GPF_DEV static int num_tiles(const Params& p) { return (int)((p.M + MT - 1) / MT); }
-  GPF_DEV static void decode(const Params& p, int t, Tile& tl) { tl.m0 = (long long)t * MT; tl.nk = p.K / KC; tl.n = p.N; }
+  struct Tile { int nk, n, n0; long long m0; };
+  GPF_DEV static int num_tiles(const Params& p) { return (int)((p.M + MT - 1) / MT) * p.ntn; }
+  GPF_DEV static void decode(const Params& p, int t, Tile& tl) {
+    tl.m0 = (long long)(t / p.ntn) * MT;
+    tl.n0 = (t % p.ntn) * NT;
+    tl.nk = p.K / KC;
+    const int rem = p.N - tl.n0;
+    tl.n = rem >= NT ? NT : (rem + 15) / 16 * 16;
+  }
   GPF_DEV static const CUtensorMap* tmap(const Params& p, const Tile&) { return &p.map; }
-  GPF_DEV static void tma_coords(const Params& p, const Tile&, int kc, int& c0, int& r_hi, int& r_lo) {
-    c0 = kc * KC; r_hi = 0; r_lo = p.lo_row;
+  GPF_DEV static void tma_coords(const Params& p, const Tile& tl, int kc, int& c0, int& r_hi, int& r_lo) {
+    c0 = kc * KC; r_hi = tl.n0; r_lo = p.lo_row + tl.n0;
   }
   GPF_DEV static void fetch_a(const Params& p, const Tile& tl, int kc, int ptid, float* frag) {
     fetch_rows<MT>(frag, ptid, p.A, p.K, tl.m0, p.M, kc * KC, p.K - kc * KC);
@@ -45,6 +52,14 @@ struct OpLayer {
     auto rowptr = [&](float* base) {
       return [&p, &tl, base](int rr) -> float* { const long long R = tl.m0 + rr; return R < p.M ? base + R * p.N : nullptr; };
     };
+    if (p.mode == 3) {   // column layout: lanes = consecutive samples -> coalesced
+#pragma unroll
+      for (int i = 0; i < 32; ++i) {
+        const int q = tl.n0 + c0 + i;
+        if (i < nc && q < p.N && valid) p.out[(size_t)q * p.S + r] = v[i] + p.bias[q];
+      }
+      return;
+    }
     if (p.mode == 0) {
       float sp[32];
 #pragma unroll
@@ -88,18 +103,18 @@ struct OpLast {
     int d, nb, S, K, mt, lo3, loG;
   };
   struct Tile { int nk, n, fam, idx, cnt, m0; };
-  GPF_DEV static int num_tiles(const Params& p) { return (2 * p.d + p.nb) * p.mt; }
-  GPF_DEV static void decode(const Params& p, int t, Tile& tl) {
+  GPF_DEV static int num_tiles(const Params& p) { return (p.d + p.nb) * p.mt; }
+  GPF_DEV static void decode(const Params& p, int t, Tile& tl) {   // F (fam 0) is a dense GEMM now: OpLayer mode 3
     const int grp = t / p.mt;
     tl.m0 = (t % p.mt) * MT;
     tl.nk = p.K / KC;
-    if (grp < 2 * p.d) {
-      tl.fam = grp < p.d ? 0 : 1;
-      tl.idx = grp < p.d ? grp : grp - p.d;
+    if (grp < p.d) {
+      tl.fam = 1;
+      tl.idx = grp;
       tl.cnt = (tl.idx < p.nb - 1 ? tl.idx : p.nb - 1) + 1;
     } else {
       tl.fam = 2;
-      tl.idx = grp - 2 * p.d;
+      tl.idx = grp - p.d;
       tl.cnt = p.d - tl.idx;
     }
     tl.n = (tl.cnt + 15) / 16 * 16;
@@ -233,16 +248,18 @@ struct OpW3 {
   struct Params {
     const float *TL, *R;
     const float *Qb, *SX, *SQ, *x, *sj;
-    float* gW3;
-    int d, nb, S, K, mtk, nseg, n_out, G, rounds;
+    float* gW3;        // [nsplit][nout][K] partial accumulators
+    int d, nb, S, K, mtk, nseg, n_out, G, rounds, nsplit, nout;
   };
-  struct Tile { int nk, n, fam, idx, cnt, km, chunk0; };
+  struct Tile { int nk, n, fam, idx, cnt, km, chunk0, sp; };
   GPF_DEV static int num_tiles(const Params& p) { return p.rounds * p.G; }
   GPF_DEV static void decode(const Params& p, int t, Tile& tl) {
     const int r = t / p.G, b = t % p.G;
-    const int o = (r / p.nseg) * p.G + b, seg = r % p.nseg;
+    int o, seg;
+    if (p.nsplit == 1) { o = (r / p.nseg) * p.G + b; seg = r % p.nseg; tl.sp = 0; }
+    else { o = b / p.nsplit; tl.sp = b % p.nsplit; seg = r * p.nsplit + tl.sp; }   // G = n_out * nsplit: one output tile per CTA
     tl.nk = 0; tl.n = 16; tl.fam = 0; tl.idx = 0; tl.cnt = 0; tl.km = 0; tl.chunk0 = seg * TC_SEG;
-    if (o >= p.n_out) return;
+    if (o >= p.n_out || seg >= p.nseg) return;
     const int grp = o / p.mtk;
     tl.km = o % p.mtk;
     if (grp < p.d) {
@@ -311,7 +328,7 @@ struct OpW3 {
       const int q = c0 + i;
       if (i < nc && q < tl.cnt) {
         const int prow = tl.fam == 0 ? tl.idx * p.nb + q : (tl.idx + q) * p.nb + tl.idx;
-        atomicAdd(p.gW3 + (size_t)prow * p.K + k, v[i]);
+        atomicAdd(p.gW3 + ((size_t)tl.sp * p.nout + prow) * p.K + k, v[i]);
       }
     }
   }
@@ -369,7 +386,7 @@ struct OpW {
 };
 
 // gather the padded gradient accumulators into the caller's flat layout; scalars
-struct TcTabs { const float* gWp[TC_MAXL + 1]; const float* gb[TC_MAXL + 1]; int ns[TC_MAXL + 1]; };
+struct TcTabs { const float* gWp[TC_MAXL + 1]; const float* gb[TC_MAXL + 1]; int ns[TC_MAXL + 1]; int ns3; };
 __global__ void tc_finalize_kernel(TcDims g, const float* __restrict__ gW1, TcTabs tabs,
                                    const float* __restrict__ gW3, const float* __restrict__ gb3, const float* __restrict__ scal,
                                    float loss_scale, float lagr_scale, float* __restrict__ grads_out, float* __restrict__ scalars_out) {
@@ -383,7 +400,7 @@ __global__ void tc_finalize_kernel(TcDims g, const float* __restrict__ gW1, TcTa
     if (e >= g.woff[li] && e < g.woff[li] + ni * no) {
       const int q = e - g.woff[li], k = q / ni, m = q % ni;
       if (li == 0) val = gW1[k * (g.d + 2) + m];
-      else if (li == g.L) val = gW3[(size_t)k * g.Hp[g.L] + m];
+      else if (li == g.L) { for (int sp = 0; sp < tabs.ns3; ++sp) val += gW3[((size_t)sp * g.nout + k) * g.Hp[g.L] + m]; }
       else {
         const int l = li + 1, ns = tabs.ns[l], Nl = g.Hp[l - 1];
         const float* gp = tabs.gWp[l];
@@ -413,26 +430,29 @@ struct TcPlan {
 };
 struct TcBuf {   // offsets in floats
   size_t W1T, bp[TC_MAXL + 1], Ws[TC_MAXL + 1], WTs[TC_MAXL + 1], W3s, W3Gs, W3Ts, W3GTs, W3JTs, weights_end;
-  size_t gW1, l1part, gWp[TC_MAXL + 1], gb[TC_MAXL + 1], gW3, gb3, scal, grads_end;
+  size_t gW1, zpart, gWp[TC_MAXL + 1], gb[TC_MAXL + 1], gW3, gb3, scal, grads_end;
   size_t stash, sj, sp[TC_MAXL + 1], T[TC_MAXL + 1], Ub[TC_MAXL + 1], R, Rb, hbp, F, G, D, SX, FX, SD, Q, v, ksum;
   size_t vbar, Qb, SQ, SXb, ybar, ybsum, ybprev, xb, ot_s, lg_s, total;
-  int nseg_hb, nchunk_p, npad[TC_MAXL + 1], npadT[TC_MAXL + 1], wsplit_G[TC_MAXL + 1];
+  int nseg_hb, nchunk_p, npad[TC_MAXL + 1], npadT[TC_MAXL + 1], wsplit_G[TC_MAXL + 1], w3_nsplit, nz, s_per_z;
 };
 
 inline size_t tc_per_sample_floats(const TcDims& g, int n_steps, bool train) {
   size_t f = (size_t)(4 * n_steps + 1) * g.d;
-  for (int l = 1; l <= g.L; ++l) f += (size_t)(g.d + 1) * g.Hp[l] * (train ? 2 : 1) + g.Hp[l];
+  for (int l = 1; l <= g.L; ++l) {
+    f += (size_t)(g.d + 1) * g.Hp[l] + g.Hp[l];
+    if (train && !(l < g.L && g.Hp[l + 1] >= g.Hp[l])) f += (size_t)(g.d + 1) * g.Hp[l];   // Ub_l (else aliased to T_{l+1})
+  }
   const int nchunk_p = (g.nout + KC - 1) / KC, nseg_hb = (nchunk_p + TC_SEG - 1) / TC_SEG;
   f += (size_t)g.nb * g.Hp[g.L] * (train ? 2 : 1) + (train ? (size_t)nseg_hb * g.Hp[g.L] : 0);
   f += (size_t)3 * g.nout + 3 * g.nb + 3 * g.d + g.d;
   if (train) f += (size_t)7 * g.d + 2 * g.nb;
   return f + 2;
 }
-// slab size: a multiple of 256 samples, the workspace of one slab bounded by ~640 MB, as few padded samples as possible
+// slab size: a multiple of 256 samples, the per-slab buffers bounded by ~880 MB (C5: 2048 samples), equal slabs
 inline int tc_slab_size(const GpFlowDesc* d, int64_t B, int op) {
   const TcDims g = tc_make_dims(d, 256);
   const size_t per = tc_per_sample_floats(g, d->n_steps, op != GPFLOW_OP_FORWARD) * 4;
-  long long smax = (long long)(((size_t)640 << 20) / per) / 256 * 256;
+  long long smax = (long long)(((size_t)880 << 20) / per) / 256 * 256;
   if (smax < 256) smax = 256;
   if (smax > 32768) smax = 32768;
   if (const char* e = getenv("GPFLOW_TC_SLAB")) {   // testing aid: force small slabs (multi-slab accumulation paths)
@@ -470,25 +490,41 @@ inline void tc_carve(const TcDims& g, int n_steps, bool train, int sm_count, TcB
   b.weights_end = off;
   if (train) {
     b.gW1 = take((size_t)g.Hp[1] * (d + 2));
-    b.l1part = take((size_t)(S / TC_L1_SPB) * g.Hp[1] * (d + 2));
     for (int l = 2; l <= L; ++l) {
       const int mt = (g.Hp[l] + MT - 1) / MT;
       b.wsplit_G[l] = (sm_count / mt < 1 ? 1 : sm_count / mt) * mt;   // upper bound on CTAs = partial buffers
       b.gWp[l] = take((size_t)b.wsplit_G[l] * MT * g.Hp[l - 1]);
       b.gb[l] = take(g.Hp[l]);
     }
-    b.gW3 = take((size_t)g.nout * HL);
+    {   // last-layer weight gradient: split-K partials when there are fewer output tiles than SMs
+      const int n_out = (d + g.nb) * ((HL + MT - 1) / MT);
+      b.w3_nsplit = sm_count / n_out < 1 ? 1 : sm_count / n_out;
+      const int nseg = 2 * S / (KC * TC_SEG);
+      if (b.w3_nsplit > nseg) b.w3_nsplit = nseg;
+    }
+    b.gW3 = take((size_t)b.w3_nsplit * g.nout * HL);
     b.gb3 = take(g.nout);
   }
   b.scal = take(4);
   b.grads_end = off;
+  // two-stage reductions over the samples (fixed order): nz splits of the slab, partials [nz][n]
+  b.nz = S / 256 < 32 ? S / 256 : 32;
+  b.s_per_z = (S + b.nz - 1) / b.nz;
+  if (train) {
+    size_t n = (size_t)g.Hp[1] * (d + 2);
+    for (int l = 2; l <= L; ++l) n = (size_t)g.Hp[l] > n ? g.Hp[l] : n;
+    const size_t n3 = (size_t)(S / 256) * g.nout;
+    b.zpart = take((size_t)b.nz * n > n3 ? (size_t)b.nz * n : n3);
+  }
   b.stash = take((size_t)(4 * n_steps + 1) * d * S);
   b.sj = take((size_t)d * S);
   for (int l = 1; l <= L; ++l) {
     b.sp[l] = take((size_t)S * g.Hp[l]);
     b.T[l] = take((size_t)(d + 1) * S * g.Hp[l]);
-    if (train) b.Ub[l] = take((size_t)(d + 1) * S * g.Hp[l]);
   }
+  if (train)   // Tb_l / Ub_l: T_{l+1} is dead once tb(l+1) has run, so Ub_l takes its place when it fits
+    for (int l = 1; l <= L; ++l)
+      b.Ub[l] = (l < L && g.Hp[l + 1] >= g.Hp[l]) ? b.T[l + 1] : take((size_t)(d + 1) * S * g.Hp[l]);
   b.R = take((size_t)g.nb * S * HL);
   if (train) {
     b.Rb = take((size_t)g.nb * S * HL);
@@ -572,12 +608,13 @@ int tc_run(const GpFlowDesc* d, int op, const float* params, const float* x_in, 
     tc_prep_last_kernel<<<(g.nout * HL + 255) / 256, 256, 0, st>>>(g, params, w);
     TC_KCK();
   }
-  CUtensorMap mapW[TC_MAXL + 1], mapWT[TC_MAXL + 1], map3, mapG, mapT, mapGT, mapJT;
+  CUtensorMap mapW[TC_MAXL + 1], mapWT[TC_MAXL + 1], map3, map3F, mapG, mapT, mapGT, mapJT;
   for (int l = 2; l <= L; ++l) {
     if (!make_tmap_2d(&mapW[l], w.Ws[l], (uint64_t)2 * b.npad[l], g.Hp[l - 1], g.Hp[l - 1], HT)) return GPFLOW_ERR_CUDA;
     if (!make_tmap_2d(&mapWT[l], w.WTs[l], (uint64_t)2 * b.npadT[l], g.Hp[l], g.Hp[l], HT)) return GPFLOW_ERR_CUDA;
   }
   if (!make_tmap_2d(&map3, w.W3s, (uint64_t)2 * g.rows3, HL, HL, 64)) return GPFLOW_ERR_CUDA;
+  if (!make_tmap_2d(&map3F, w.W3s, (uint64_t)2 * g.rows3, HL, HL, HT)) return GPFLOW_ERR_CUDA;
   if (!make_tmap_2d(&mapG, w.W3Gs, (uint64_t)2 * g.rowsG, HL, HL, 64)) return GPFLOW_ERR_CUDA;
   if (!make_tmap_2d(&mapT, w.W3Ts, (uint64_t)2 * g.HTp, g.ldT, g.ldT, HT)) return GPFLOW_ERR_CUDA;
   if (!make_tmap_2d(&mapGT, w.W3GTs, (uint64_t)nb * 2 * g.HTp, g.dpad, g.dpad, HT)) return GPFLOW_ERR_CUDA;
@@ -599,7 +636,7 @@ int tc_run(const GpFlowDesc* d, int op, const float* params, const float* x_in, 
     for (int l = 2; l <= L; ++l) {
       typename LayerOp::Params p;
       p.map = mapW[l];
-      p.K = g.Hp[l - 1]; p.N = g.Hp[l]; p.lo_row = b.npad[l]; p.S = S;
+      p.K = g.Hp[l - 1]; p.N = g.Hp[l]; p.lo_row = b.npad[l]; p.S = S; p.ntn = 1;
       p.bias = w.bp[l]; p.aux = P(b.sp[l]); p.out2 = P(b.sp[l]);
       p.A = P(b.T[l - 1]) + (size_t)dd * S * p.K; p.M = S; p.mode = 0; p.out = P(b.T[l]) + (size_t)dd * S * p.N;
       TC_CK(launch_gemm<LayerOp>(p, mt, sm_count, st));
@@ -608,12 +645,20 @@ int tc_run(const GpFlowDesc* d, int op, const float* params, const float* x_in, 
     }
     tc_rsum_kernel<<<S, HL, 0, st>>>(g, P(b.T[L]), P(b.sj), P(b.R));
     TC_KCK();
+    {   // F for every output row: one dense GEMM with column-layout stores
+      typename LayerOp::Params p;
+      p.map = map3F;
+      p.K = HL; p.N = g.nout; p.lo_row = g.rows3; p.S = S; p.ntn = (g.nout + HT - 1) / HT;
+      p.bias = w.b3; p.aux = nullptr; p.out2 = nullptr;
+      p.A = P(b.T[L]) + (size_t)dd * S * HL; p.M = S; p.mode = 3; p.out = P(b.F);
+      TC_CK(launch_gemm<LayerOp>(p, mt * p.ntn, sm_count, st));
+    }
     {
       typename LastOp::Params p;
       p.map3 = map3; p.mapG = mapG;
       p.TL = P(b.T[L]); p.R = P(b.R); p.b3 = w.b3; p.F = P(b.F); p.G = P(b.G); p.D = P(b.D);
       p.d = dd; p.nb = nb; p.S = S; p.K = HL; p.mt = mt; p.lo3 = g.rows3; p.loG = g.rowsG;
-      TC_CK(launch_gemm<LastOp>(p, (2 * dd + nb) * mt, sm_count, st));
+      TC_CK(launch_gemm<LastOp>(p, (dd + nb) * mt, sm_count, st));
     }
     tc_vel1_kernel<<<g_nS, eb, 0, st>>>(g, xpt, P(b.sj), P(b.F), P(b.D), P(b.SX), P(b.FX), P(b.SD));
     TC_KCK();
@@ -647,8 +692,10 @@ int tc_run(const GpFlowDesc* d, int op, const float* params, const float* x_in, 
       p.gW3 = P(b.gW3);
       p.d = dd; p.nb = nb; p.S = S; p.K = HL; p.mtk = (HL + MT - 1) / MT; p.nseg = 2 * S / (KC * TC_SEG);
       p.n_out = (dd + nb) * p.mtk;
-      p.G = p.n_out < sm_count ? p.n_out : sm_count;
-      p.rounds = (p.n_out + p.G - 1) / p.G * p.nseg;
+      p.nout = g.nout;
+      p.nsplit = b.w3_nsplit;
+      if (p.nsplit > 1) { p.G = p.n_out * p.nsplit; p.rounds = (p.nseg + p.nsplit - 1) / p.nsplit; }
+      else { p.G = p.n_out < sm_count ? p.n_out : sm_count; p.rounds = (p.n_out + p.G - 1) / p.G * p.nseg; }
       // the grid must be exactly G so that every output tile stays with one CTA
       using SMW = GemmSmem<W3Op>;
       static bool attr = false;
@@ -656,7 +703,9 @@ int tc_run(const GpFlowDesc* d, int op, const float* params, const float* x_in, 
       tc_gemm_kernel<W3Op><<<p.G, kThreads, SMW::kBytes, st>>>(p);
       TC_KCK();
     }
-    tc_db3_kernel<<<dim3((nb + 15) / 16, (dd + 15) / 16), dim3(16, 16), 0, st>>>(g, P(b.Qb), xpt, P(b.SX), P(b.SQ), P(b.gb3));
+    tc_db3_kernel<<<dim3((nb + 15) / 16, (dd + 15) / 16, S / 256), dim3(16, 16), 0, st>>>(g, P(b.Qb), xpt, P(b.SX), P(b.SQ), P(b.zpart));
+    TC_KCK();
+    tc_reduce_add_kernel<<<(g.nout + 255) / 256, 256, 0, st>>>(S / 256, g.nout, P(b.zpart), P(b.gb3));
     TC_KCK();
     tc_tb_last_kernel<<<S, HL, 0, st>>>(g, P(b.T[L]), P(b.sp[L]), P(b.Rb), P(b.hbp), b.nseg_hb, P(b.sj), xpt, P(b.Ub[L]),
                                         P(b.ybar), L == 1 ? 1 : 0);
@@ -680,12 +729,15 @@ int tc_run(const GpFlowDesc* d, int op, const float* params, const float* x_in, 
         tc_gemm_kernel<WOp><<<p.G, kThreads, SMW::kBytes, st>>>(p);
         TC_KCK();
       }
-      tc_colsum_kernel<<<(g.Hp[l] + 31) / 32, dim3(32, 8), 0, st>>>(S, g.Hp[l], P(b.Ub[l]) + (size_t)dd * S * g.Hp[l], P(b.gb[l]));
+      tc_colsum_kernel<<<dim3((g.Hp[l] + 31) / 32, b.nz), dim3(32, 8), 0, st>>>(S, g.Hp[l], b.s_per_z,
+                                                                                P(b.Ub[l]) + (size_t)dd * S * g.Hp[l], P(b.zpart));
+      TC_KCK();
+      tc_reduce_add_kernel<<<(g.Hp[l] + 255) / 256, 256, 0, st>>>(b.nz, g.Hp[l], P(b.zpart), P(b.gb[l]));
       TC_KCK();
       {
         typename LayerOp::Params p;
         p.map = mapWT[l];
-        p.K = g.Hp[l]; p.N = g.Hp[l - 1]; p.lo_row = b.npadT[l]; p.S = S;
+        p.K = g.Hp[l]; p.N = g.Hp[l - 1]; p.lo_row = b.npadT[l]; p.S = S; p.ntn = 1;
         p.bias = nullptr; p.aux = nullptr; p.out2 = nullptr;
         p.A = P(b.Ub[l]); p.M = (long long)(dd + 1) * S; p.mode = 2; p.out = P(b.Ub[l - 1]);
         TC_CK(launch_gemm<LayerOp>(p, (dd + 1) * mt, sm_count, st));
@@ -695,11 +747,13 @@ int tc_run(const GpFlowDesc* d, int op, const float* params, const float* x_in, 
         TC_KCK();
       }
     }
-    tc_layer1_bwd_kernel<<<S / TC_L1_SPB, g.Hp[1], 0, st>>>(g, w.W1T, P(b.T[1]), P(b.sp[1]), P(b.Ub[1]), xpt, t, P(b.l1part),
-                                                             P(b.ybar));
+    tc_layer1_bwd_a_kernel<<<S / TC_L1B_SPB, g.Hp[1], 0, st>>>(g, w.W1T, P(b.T[1]), P(b.sp[1]), P(b.Ub[1]), P(b.ybar));
+    TC_KCK();
+    tc_layer1_bwd_b_kernel<<<dim3(g.Hp[1] / 32, (dd + 7) / 8, b.nz), dim3(32, 8), 0, st>>>(g, P(b.sp[1]), P(b.Ub[1]), xpt, t,
+                                                                                       b.s_per_z, P(b.zpart));
     TC_KCK();
     const int n1 = g.Hp[1] * (dd + 2);
-    tc_l1_reduce_kernel<<<(n1 + 255) / 256, 256, 0, st>>>(S / TC_L1_SPB, n1, P(b.l1part), P(b.gW1));
+    tc_reduce_add_kernel<<<(n1 + 255) / 256, 256, 0, st>>>(b.nz, n1, P(b.zpart), P(b.gW1));
     TC_KCK();
     return GPFLOW_OK;
   };
@@ -778,7 +832,10 @@ int tc_run(const GpFlowDesc* d, int op, const float* params, const float* x_in, 
     TcTabs tabs;
     memset(&tabs, 0, sizeof(tabs));
     if (train)
+    {
       for (int l = 2; l <= L; ++l) { tabs.gWp[l] = P(b.gWp[l]); tabs.gb[l] = P(b.gb[l]); tabs.ns[l] = wsplit_ns[l]; }
+      tabs.ns3 = b.w3_nsplit;
+    }
     const int count = (train && grads_out != nullptr) ? g.P : 3;
     tc_finalize_kernel<<<(count + 255) / 256, 256, 0, st>>>(
         g, train ? P(b.gW1) : nullptr, tabs, train ? P(b.gW3) : nullptr, train ? P(b.gb3) : nullptr, P(b.scal),

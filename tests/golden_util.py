@@ -13,9 +13,10 @@ GOLDEN_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 
 def golden_names(tag):
     """single-step cases (oracle/make_golden.py); the train_* files are training trajectories (make_golden_train.py),
-    the bnaf_* / ffjord_* files the frozen-map vectors (make_golden_bnaf.py, make_golden_ffjord.py)"""
+    the bnaf_* / ffjord_* files the frozen-map vectors (make_golden_bnaf.py, make_golden_ffjord.py), compose_* the
+    nb_blocks != 1 vectors (make_golden_compose.py), measured_* the bench-configuration vectors (make_golden_measured.py)"""
     names = sorted(os.path.basename(p)[: -len("_%s.npz" % tag)] for p in glob.glob(os.path.join(GOLDEN_DIR, "*_%s.npz" % tag)))
-    return [n for n in names if not n.startswith(("train_", "bnaf_", "ffjord_"))]
+    return [n for n in names if not n.startswith(("train_", "bnaf_", "ffjord_", "compose_", "measured_"))]
 
 
 def load_golden(name, tag):

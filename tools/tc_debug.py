@@ -17,13 +17,18 @@ def rel(a, b):
     return float((a - b).norm() / max(float(b.norm()), 1e-300))
 
 
-def run(d, nb, hidden, B, N, std):
-    print("=== d=%d nb=%d H=%s B=%d N=%d std=%g" % (d, nb, hidden, B, N, std), flush=True)
+def run(d, nb, hidden, B, N, std, bench_cfg=False):
+    print("=== d=%d nb=%d H=%s B=%d N=%d std=%g%s" % (d, nb, hidden, B, N, std, " (bench.py inputs)" if bench_cfg else ""), flush=True)
     spec = O.FlowSpec(d=d, nb=nb, hidden=list(hidden), n_steps=N)
-    params = [p.float().double() for p in O.init_params(spec, std=std, seed=11 + d, dtype=torch.float64)]
     gen = torch.Generator().manual_seed(100 + d * nb)
-    x_map = torch.randn(B, d, generator=gen, dtype=torch.float64).clamp(-2.5, 2.5).float().double()
-    x_data = (1.1 * x_map.flip(-1) + 0.1).float().double()
+    if bench_cfg:
+        from bench import synth_batch
+        params = [p.double() for p in O.init_params(spec, std, 0, torch.float32)]
+        x_data, x_map = [t.double() for t in synth_batch(B, d, 1234, "cpu")]
+    else:
+        params = [p.float().double() for p in O.init_params(spec, std=std, seed=11 + d, dtype=torch.float64)]
+        x_map = torch.randn(B, d, generator=gen, dtype=torch.float64).clamp(-2.5, 2.5).float().double()
+        x_data = (1.1 * x_map.flip(-1) + 0.1).float().double()
     cfg = G.FlowConfig(d=d, nb=nb, hidden=tuple(hidden), n_steps=N)
     flat = O.flatten_params(params).float().cuda()
     # 1. one velocity evaluation
@@ -77,4 +82,8 @@ if __name__ == "__main__":
         run(6, 6, (40,), 130, 3, 0.05)
         run(10, 9, (50, 50, 50), 200, 3, 0.03)
         run(17, 16, (100, 70), 260, 2, 0.02)
-        run(64, 63, (256, 256), 40, 2, 0.02)
+        os.environ["GPFLOW_TC_SLAB"] = "256"       # three slabs: accumulation across slabs
+        run(10, 9, (50, 50, 50), 700, 3, 0.03)
+        del os.environ["GPFLOW_TC_SLAB"]
+        run(10, 9, (50, 50, 50), 64, 15, 0.05, bench_cfg=True)
+        run(64, 63, (256, 256), 8, 15, 0.02, bench_cfg=True)
