@@ -27,9 +27,9 @@ WORKLOADS = {
     "c4_2d_2p24": dict(d=2, nb=1, hidden=(15, 15), n_steps=15, log2_batch=24, w_std=0.3,
                        desc="synthetic train_gp_on_gaussian_noise 2D, 2^24-sample global batch"),
     "c3_d10_nb9": dict(d=10, nb=9, hidden=(50, 50, 50), n_steps=15, log2_batch=14, w_std=0.05,
-                       desc="dsprites-latent shape d=10 nb=9 H=[50,50,50] (generic kernel)"),
-    "c5_d64_nb63": dict(d=64, nb=63, hidden=(256, 256), n_steps=15, log2_batch=12, w_std=0.02,
-                        desc="synthetic d=64 nb=63 H=[256,256] (generic kernel; SURVEY 8d quotes 2^14 per GPU)"),
+                       desc="dsprites-latent shape d=10 nb=9 H=[50,50,50] (chunked tcgen05 path, widths padded to 64)"),
+    "c5_d64_nb63": dict(d=64, nb=63, hidden=(256, 256), n_steps=15, log2_batch=14, w_std=0.02,
+                        desc="synthetic d=64 nb=63 H=[256,256], 2^14 samples per GPU (chunked tcgen05 path)"),
 }
 
 
@@ -257,6 +257,8 @@ def main():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--dbg", default="", help=argparse.SUPPRESS)   # developer toggles: nbuf1,noopt,noclk
     ap.add_argument("--euler", type=float, default=None, help="Euler penalization coefficient (extra row)")
+    ap.add_argument("--rows", default="all", help="extra rows of the default run: all | none | comma list of " +
+                    "c5_d64_nb63,c3_d10_nb9,c4_2d_euler_5e-4")
     args = ap.parse_args()
     wl = dict(WORKLOADS.get(args.workload, {}))
     if args.log2_batch is not None:
@@ -290,28 +292,132 @@ def main():
 
     import torch
     import torch.distributed as dist
-    import gpflow_b200 as G
-    from gpflow_b200 import ops, _lib
 
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
-    B_global = 1 << wl["log2_batch"]
-    B = B_global // world
-    d = wl["d"]
+    peaks = measure_peaks(dev)            # BEFORE any warm-up: cool chip, max clock (VERDICT r1 "what's weak" 10)
+    head = measure_workload(args, args.workload, wl, args.euler, rank, world, local_rank, dev, args.steps, args.warmup,
+                            peaks, weak=False, with_cpu_baseline=not args.no_cpu_baseline)
+    rows = []
+    if args.rows != "none" and args.workload == "c4_2d_2p24" and args.euler is None and args.log2_batch is None:
+        for spec in ROWS:
+            if args.rows != "all" and spec["name"] not in args.rows.split(","):
+                continue
+            rwl = dict(WORKLOADS[spec["workload"]])
+            rwl["log2_batch"] = spec["log2_batch"]
+            r = measure_workload(args, spec["workload"], rwl, spec.get("euler"), rank, world, local_rank, dev, spec["steps"],
+                                 spec["warmup"], peaks, weak=spec["weak"], with_cpu_baseline=False)
+            if rank == 0:
+                r["name"] = spec["name"]
+                rows.append(r)
+    if rank == 0:
+        head["rows"] = rows
+        head["peaks"] = peaks
+        sys.stdout.flush()
+        os.write(json_fd, (json.dumps(head) + "\n").encode())
+    if world > 1:
+        dist.destroy_process_group()
 
+
+# extra rows of the default run (VERDICT r1 "next round" 1b): the other BASELINE.json configs, each with its own
+# roofline / clocks / e2e, so that the driver's BENCH / SCALE files carry them at N = 1, 2, 4, 8
+ROWS = [
+    # C5 at 2^14 samples PER GPU (SURVEY.md 8d "C5 inputs"): weak scaling
+    dict(name="c5_d64_nb63", workload="c5_d64_nb63", log2_batch=14, weak=True, steps=3, warmup=3),
+    dict(name="c3_d10_nb9", workload="c3_d10_nb9", log2_batch=14, weak=True, steps=5, warmup=3),
+    # C2's penalised step on the C4 data: 2^22 global
+    dict(name="c4_2d_euler_5e-4", workload="c4_2d_2p24", log2_batch=22, weak=False, euler=5e-4, steps=3, warmup=3),
+]
+
+NOMINAL_FP32_TFLOPS = 148 * 128 * 2 * 1.965e9 / 1e12      # 74.5: 148 SMs x 128 FP32 lanes x 2 (FMA) x 1.965 GHz
+
+
+def _sm_mhz_now(dev):
+    """SM clock from the on-device probe (clock64 ticks over globaltimer ns), right now on the current stream."""
+    import ctypes
+    import torch
+    from gpflow_b200 import _lib
+    out = torch.zeros(2, dtype=torch.int64, device=dev)
+    _lib.load().gpflow_clock_probe(ctypes.c_void_p(out.data_ptr()), ctypes.c_void_p(torch.cuda.current_stream().cuda_stream))
+    o = out.cpu().double()
+    return round(float(1e3 * o[0] / max(float(o[1]), 1.0)), 1)
+
+
+def measure_peaks(dev):
+    """Roofline denominators, measured ONCE before any warm-up.
+    fp32: FFMA-saturating micro-kernel (gpflow_fp32_fma_burn) with the SM clock seen right after it; nominal 74.5 beside it.
+    tf32: dense TF32 GEMM rate as SURVEY.md 8(d) prescribes -- torch.matmul (cuBLAS) TF32 8192^3, best of 10 (burst) and
+    back to back for ~2 s (sustained, what a kernel inside a second-long step sees under the power cap).  A 3xTF32
+    contraction is judged against a THIRD of it (fp32-equivalent)."""
+    import torch
+    from gpflow_b200 import ops
+    fma = ops.fp32_fma_peak_tflops()
+    fma_mhz = _sm_mhz_now(dev)
+    old = torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cuda.matmul.allow_tf32 = True
+    n = 8192
+    a = torch.randn(n, n, device=dev)
+    b = torch.randn(n, n, device=dev)
+    c = torch.empty(n, n, device=dev)
+    fl = 2.0 * n ** 3
+    torch.matmul(a, b, out=c)
+    torch.cuda.synchronize()
+    best = 0.0
+    for _ in range(10):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(); torch.matmul(a, b, out=c); e1.record(); e1.synchronize()
+        best = max(best, fl / (e0.elapsed_time(e1) * 1e-3) / 1e12)
+    reps = max(8, int(2.0 * best * 1e12 / fl))
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(reps):
+        torch.matmul(a, b, out=c)
+    e1.record(); e1.synchronize()
+    sustained = reps * fl / (e0.elapsed_time(e1) * 1e-3) / 1e12
+    tf32_mhz = _sm_mhz_now(dev)
+    torch.backends.cuda.matmul.allow_tf32 = old
+    del a, b, c
+    torch.cuda.empty_cache()
+    measured = {}
+    try:
+        measured = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    return {"fp32_fma_tflops": fma, "fp32_fma_sm_mhz": fma_mhz, "fp32_nominal_tflops": NOMINAL_FP32_TFLOPS,
+            "tf32_dense_tflops_burst": best, "tf32_dense_tflops_sustained": sustained, "tf32_sm_mhz_after_sustained": tf32_mhz,
+            "how": "before warm-up: gpflow_fp32_fma_burn best of 5; torch.matmul TF32 8192^3 best of 10 (burst) and "
+                   "%d back to back (sustained)" % reps,
+            "hbm_gbs_measured": measured.get("hbm_gbs"), "bf16_tflops_measured": measured.get("bf16_tflops")}
+
+
+def measure_workload(args, name, wl, euler, rank, world, local_rank, dev, steps, warmup, peaks, weak, with_cpu_baseline):
+    """One row: W warm-up + K timed steps of the fused train step (+ all-reduce + fused Adam) on resident inputs, the same
+    through the public API with HOST buffers (e2e), roofline of the dominant kernel family.  weak: per-GPU batch fixed
+    at 2^log2_batch (global = world x that); else the global batch is fixed."""
+    import ctypes
+    import torch
+    import torch.distributed as dist
+    import gpflow_b200 as G
+    from gpflow_b200 import ops, _lib
+    from gpflow_b200.roofline import algorithmic_flops_per_sample, executed_flops_per_sample_tc
+
+    B = (1 << wl["log2_batch"]) if weak else (1 << wl["log2_batch"]) // world
+    B_global = B * world
+    d = wl["d"]
     flow = G.get_gp_flow(d, {"nb_neurons": list(wl["hidden"]), "nb_div_blocks": wl["nb"]}, wl["n_steps"],
-                         euler_dict={"use_euler": args.euler is not None, "case": "penalization",
-                                     "coef_penalization": args.euler}).to(dev)
+                         euler_dict={"use_euler": euler is not None, "case": "penalization",
+                                     "coef_penalization": euler}).to(dev)
     torch.manual_seed(0)
     with torch.no_grad():
         for p in flow.parameters():
-            p.normal_(0.0, wl["w_std"])           # N(0, 0.3^2) weights AND biases, seed 0
+            p.normal_(0.0, wl["w_std"])           # SURVEY 8(d): N(0, w_std^2) weights AND biases, seed 0
     net = G.GPFlowNetwork(flow, map_module=None)
     # network.py:307-320: Adam(lr, betas=(0.9, 0.999), weight_decay=1e-4) on the flat parameter buffer, one launch per step
     opt = net.configure_fused_optimizer(lr=2e-3, weight_decay=1e-4)
     cfg = flow.config()
+    lib = _lib.load()
 
     # inputs resident in HBM; rotate through enough distinct batches to exceed the 126 MB L2
     bytes_per_batch = 2 * B * d * 4
@@ -320,14 +426,10 @@ def main():
         n_buf = 1
     bufs = [synth_batch(B, d, 1234 + rank + 1000 * i, dev) for i in range(n_buf)]
 
-    def step(i):
+    for i in range(warmup):
         x_data, x_map = bufs[i % n_buf]
-        loss, reg = net.fused_training_step(x_data, x_map, global_batch=B_global)
+        net.fused_training_step(x_data, x_map, global_batch=B_global)
         opt.step()
-        return loss, reg
-
-    for i in range(args.warmup):
-        step(i)
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
@@ -336,16 +438,14 @@ def main():
         clocks.start()   # no sleep here: a delay on one rank after the barrier would be charged to every rank
     torch.cuda.synchronize()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    kev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
-    flat = flow.flat_parameters().detach()
-    probe = torch.zeros(args.steps, 2, dtype=torch.int64, device=dev)
-    import ctypes
-    lib = _lib.load()
+    kev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+    probe = torch.zeros(steps, 2, dtype=torch.int64, device=dev)
     stream_ptr = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+    tc_l0 = int(lib.gpflow_tc_launches_total())
     ev0.record()
-    for i in range(args.steps):
+    for i in range(steps):
         x_data, x_map = bufs[i % n_buf]
-        # the fused train-step kernel (+ finalize) bracketed by its own events: roofline numerator
+        # the fused train step (its kernels + finalize [+ all-reduce]) bracketed by its own events: roofline numerator
         kev[i][0].record()
         loss, reg = net.fused_training_step(x_data, x_map, global_batch=B_global)
         kev[i][1].record()
@@ -354,10 +454,11 @@ def main():
         lib.gpflow_clock_probe(ctypes.c_void_p(probe[i].data_ptr()), stream_ptr)   # ~20 us, SM clock right after the step
     ev1.record()
     torch.cuda.synchronize()
+    tc_launches = int(lib.gpflow_tc_launches_total()) - tc_l0
     if world > 1:
         dist.barrier()
     ms_total = ev0.elapsed_time(ev1)
-    ms_kernel = sum(a.elapsed_time(b) for a, b in kev) / args.steps
+    ms_kernel = sum(a.elapsed_time(b) for a, b in kev) / steps
     t = torch.tensor([ms_total, ms_kernel], device=dev, dtype=torch.float64)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -370,7 +471,7 @@ def main():
         clk["sm_mhz"] = round(mhz[len(mhz) // 2], 1)          # median of the on-device probes, one per timed step
         clk["sm_min_mhz"] = round(mhz[0], 1)
         clk["samples"] = len(mhz)
-    ms_per_step = ms_total / args.steps
+    ms_per_step = ms_total / steps
     value = B_global / (ms_per_step * 1e-3)
 
     # ---- e2e: public API with HOST buffers; H2D of the step's inputs and D2H of the loss inside the timed region
@@ -395,91 +496,94 @@ def main():
             dist.barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
-        h2d = e2e_run(args.steps)
+        h2d = e2e_run(steps)
         e1.record()
         torch.cuda.synchronize()
         te = torch.tensor([e0.elapsed_time(e1)], device=dev, dtype=torch.float64)
         if world > 1:
             dist.all_reduce(te, op=dist.ReduceOp.MAX)
-        e2e = {"value": B_global / (float(te[0]) / args.steps * 1e-3), "unit": "samples/s",
-               "h2d_bytes_per_step": h2d // args.steps * world, "d2h_bytes_per_step": 8 * world,
+        e2e = {"value": B_global / (float(te[0]) / steps * 1e-3), "unit": "samples/s",
+               "h2d_bytes_per_step": h2d // steps * world, "d2h_bytes_per_step": 8 * world,
                "api": "HostBatchStream -> GPFlowNetwork.fused_training_step -> FlatAdam.step -> float(loss)"}
-
     if rank != 0:
-        if world > 1:
-            dist.destroy_process_group()
-        return
+        return None
 
-    # ---- roofline of the dominant kernel: FP32 FMA pipe (compute-bound, K=15 widths -> CUDA cores)
-    from gpflow_b200.roofline import algorithmic_flops_per_sample
-    flops_per_sample = algorithmic_flops_per_sample(d, wl["nb"], wl["hidden"], wl["n_steps"], train=True,
-                                                    euler=args.euler is not None)
-    peak_tf = ops.fp32_fma_peak_tflops()
-    achieved_tf = flops_per_sample * B / (ms_kernel * 1e-3) / 1e12
-    peaks = {}
-    try:
-        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
-    except Exception:
-        pass
-    traffic = None
-    tp = os.path.join(ROOT, "profiles", "traffic_bytes_per_launch.json")
-    if os.path.exists(tp) and args.euler is None:
-        try:
-            traffic = json.load(open(tp))[args.workload]["dram_bytes_per_sample"] * B   # per launch, like `achieved`
-        except Exception:
-            traffic = None
-    roofline = {
-        "bound": "fp32_fma", "achieved": achieved_tf, "peak": peak_tf, "unit": "TFLOP/s",
-        "frac": achieved_tf / peak_tf if peak_tf else None, "traffic": traffic,
-        "kernel": G.kernel_variant(cfg, euler_coef=args.euler), "kernel_ms": ms_kernel,
-        "algorithmic_flops_per_sample": flops_per_sample, "samples_per_launch": B,
-        "peak_source": "FFMA burn micro-kernel measured live in this run (gpflow_fp32_fma_burn); MEASURED_PEAKS.json "
-                       "records no FP32 CUDA-core peak. Nominal 148 SM x 128 lanes x 2 x 1.965 GHz = 74.5 TFLOP/s",
-        "hbm": {"algorithmic_GBps": 12 * d * B / (ms_kernel * 1e-3) / 1e9,
-                "traffic_GBps": (traffic / (ms_kernel * 1e-3) / 1e9) if traffic else None,
-                "peak_GBps": peaks.get("hbm_gbs"), "peak_kind": "of measured (MEASURED_PEAKS.json copy bandwidth)",
-                "note": "algorithmic bytes = x_data + x_map + y (12 d B/sample)" + (
-                    "; the measured DRAM traffic is the activation stash the kernel streams out in the forward sweep "
-                    "and back in the reverse sweep by TMA instead of recomputing 60 velocity evaluations (DESIGN.md "
-                    "section 4)" if traffic else "")},
-    }
-    if "generic" in roofline["kernel"]:
-        # the wide shapes are judged against the tensor pipe at the precision actually used
-        # (3xTF32 => a third of the TF32 rate), measured live with the same mma.sync instruction
-        tf32 = ops.tf32_mma_peak_tflops()
-        roofline["tensor"] = {"bound": "tensor", "peak": tf32 / 3.0, "unit": "TFLOP/s fp32-equivalent (3xTF32)",
-                              "frac": achieved_tf / (tf32 / 3.0) if tf32 else None, "tf32_mma_sync_tflops": tf32,
-                              "peak_source": "mma.sync.m16n8k8 tf32 burn measured live in this run "
-                                             "(gpflow_tf32_mma_burn) / 3",
-                              "note": "hidden-layer contractions run on the tensor pipe (3xTF32 mma.sync), the "
-                                      "Jacobian-free last layer on the FP32 pipe; `achieved` counts the survey's "
-                                      "algorithmic flops, more than the kernel executes (DESIGN.md 4.3)"}
+    # ---- roofline of the dominant kernel family
+    kernel = G.kernel_variant(cfg, euler_coef=euler)
+    uses_tc = tc_launches > 0
+    flops_alg = algorithmic_flops_per_sample(d, wl["nb"], wl["hidden"], wl["n_steps"], train=True, euler=euler is not None)
+    achieved = flops_alg * B / (ms_kernel * 1e-3) / 1e12
+    if uses_tc:
+        # the wide shapes are judged against the tensor pipe at the precision actually used: 3xTF32 =>
+        # a third of the dense TF32 rate.  The step is seconds of back-to-back GEMMs => the SUSTAINED figure.
+        flops_exe = executed_flops_per_sample_tc(d, wl["nb"], wl["hidden"], wl["n_steps"], train=True)
+        achieved_exe = flops_exe * B / (ms_kernel * 1e-3) / 1e12
+        peak = peaks["tf32_dense_tflops_sustained"] / 3.0
+        desc = ops.make_desc(cfg, torch.float32, wrap=True)
+        roofline = {
+            "bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
+            "achieved_executed": achieved_exe, "frac_executed": achieved_exe / peak,
+            "frac_of_burst": achieved / (peaks["tf32_dense_tflops_burst"] / 3.0),
+            "traffic": None, "kernel": kernel, "kernel_ms": ms_kernel, "samples_per_launch": B,
+            "algorithmic_flops_per_sample": flops_alg, "executed_flops_per_sample": flops_exe,
+            "peak_source": "torch.matmul TF32 8192^3 sustained, measured before warm-up in this run, / 3 (3xTF32 split: "
+                           "fp32-equivalent).  `achieved` counts the survey's algorithmic flops (pruned Jacobian form), "
+                           "`achieved_executed` the flops the contracted-form GEMMs execute on the zero-padded widths "
+                           "(gpflow_b200/roofline.py) -- the tensor pipe does 3x that in TF32 products",
+            "slab_samples": int(lib.gpflow_tc_slab_samples(ctypes.byref(desc), B, _lib.OP_TRAIN_STEP)),
+        }
+        launches = tc_launches + steps        # + gpflow_adam_step
+    else:
+        peak = peaks["fp32_fma_tflops"]
+        peak_hot = ops.fp32_fma_peak_tflops()
+        traffic = None
+        tp = os.path.join(ROOT, "profiles", "traffic_bytes_per_launch.json")
+        if os.path.exists(tp) and euler is None:
+            try:
+                traffic = json.load(open(tp))[name]["dram_bytes_per_sample"] * B   # per launch, like `achieved`
+            except Exception:
+                traffic = None
+        roofline = {
+            "bound": "fp32_fma", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
+            "frac_nominal": achieved / NOMINAL_FP32_TFLOPS, "peak_nominal": NOMINAL_FP32_TFLOPS,
+            "peak_hot_after_run": peak_hot, "peak_sm_mhz": peaks["fp32_fma_sm_mhz"],
+            "achieved_executed": achieved, "traffic": traffic,
+            "kernel": kernel, "kernel_ms": ms_kernel, "algorithmic_flops_per_sample": flops_alg, "samples_per_launch": B,
+            "peak_source": "FFMA burn micro-kernel (gpflow_fp32_fma_burn) measured ONCE before warm-up in this run, SM clock "
+                           "beside it; MEASURED_PEAKS.json records no FP32 CUDA-core peak.  Nominal 148 SM x 128 lanes x "
+                           "2 x 1.965 GHz = 74.5 TFLOP/s; `peak_hot_after_run` is the same burn on the hot chip",
+            "hbm": {"algorithmic_GBps": 12 * d * B / (ms_kernel * 1e-3) / 1e9,
+                    "traffic_GBps": (traffic / (ms_kernel * 1e-3) / 1e9) if traffic else None,
+                    "peak_GBps": peaks.get("hbm_gbs_measured"), "peak_kind": "of measured (MEASURED_PEAKS.json copy bandwidth)",
+                    "note": "algorithmic bytes = x_data + x_map + y (12 d B/sample)"},
+        }
+        launches = steps * (ops.launch_count(cfg) + 1)   # + gpflow_adam_step
     cpu_baseline = None
-    if not args.no_cpu_baseline and world == 1:
+    if with_cpu_baseline and world == 1:
         threads = os.cpu_count() or 1
         rate, sec = cpu_oracle_rate(wl, args.cpu_baseline_sample, 2, 1, threads)
         cpu_baseline = {"value": rate, "unit": "samples/s", "cores": threads, "kind": "port",
                         "sample": "%d samples/step x 2 steps of the same synthetic workload (oracle port, torch CPU "
-                                  "autograd, all host threads)" % args.cpu_baseline_sample}
-    line = {
+                                  "autograd, all host threads; calibration against the unmodified reference: BASELINE.md "
+                                  "section 2)" % args.cpu_baseline_sample}
+    ws_mb = torch.cuda.max_memory_allocated(dev) >> 20
+    return {
         "metric": "gp_flow_train_step_samples_per_sec", "value": value, "unit": "samples/s", "n_gpus": world,
-        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
-        "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": args.workload + ": " + wl["desc"], "global_batch": B_global, "per_gpu_batch": B,
+        "steps": steps, "warmup": warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
+        "scaling": "weak" if weak else "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": name + ": " + wl["desc"], "global_batch": B_global, "per_gpu_batch": B,
                    "d": d, "nb_div_blocks": wl["nb"], "hidden": list(wl["hidden"]), "nb_layers_gp": wl["n_steps"],
-                   "euler_coef": args.euler, "parallelism": "dp%d (batch shards, one all-reduce of %d floats)" % (
+                   "euler_coef": euler, "parallelism": "dp%d (batch shards, one all-reduce of %d floats)" % (
                        world, cfg.n_params + 3),
-                   "l2": "inputs larger than L2: rotating through %d distinct resident batches of %.0f MB" % (
-                       n_buf, bytes_per_batch / 1e6),
-                   "step": "fused fwd+OT+bwd kernel, finalize, all-reduce, fused Adam (gpflow_adam_step)"},
-        "clocks": clk, "e2e": e2e, "gpu_launches": args.steps * (ops.launch_count(cfg) + 1),   # + gpflow_adam_step
+                   "l2": ("inputs larger than L2: rotating through %d distinct resident batches of %.0f MB" % (
+                       n_buf, bytes_per_batch / 1e6)) if bytes_per_batch * n_buf > 126e6 else
+                         ("the step's working set (slab activations; %d MB allocated) is larger than L2; %d input batches"
+                          % (ws_mb, n_buf)),
+                   "step": "fused fwd+OT+bwd (%s), finalize, all-reduce, fused Adam (gpflow_adam_step)" % kernel},
+        "clocks": clk, "e2e": e2e, "gpu_launches": launches,
         "roofline": roofline, "cpu_baseline": cpu_baseline,
         "loss": float(loss), "reg": float(reg),
     }
-    sys.stdout.flush()
-    os.write(json_fd, (json.dumps(line) + "\n").encode())
-    if world > 1:
-        dist.destroy_process_group()
 
 
 if __name__ == "__main__":

@@ -22,7 +22,7 @@ SCALAR_OT, SCALAR_REG, SCALAR_LAGR, NUM_SCALARS = 0, 1, 2, 3
 
 EXPORTS = [
     "gpflow_param_count", "gpflow_query_workspace", "gpflow_forward", "gpflow_train_step", "gpflow_backward",
-    "gpflow_velocity", "gpflow_kernel_variant", "gpflow_launch_count", "gpflow_fp32_fma_burn", "gpflow_tf32_mma_burn", "gpflow_clock_probe",
+    "gpflow_velocity", "gpflow_kernel_variant", "gpflow_launch_count", "gpflow_tc_launches_total", "gpflow_tc_slab_samples", "gpflow_fp32_fma_burn", "gpflow_tf32_mma_burn", "gpflow_clock_probe",
     "gpflow_adam_step", "gpflow_bnaf_param_count", "gpflow_bnaf_forward", "gpflow_ffjord_param_count",
     "gpflow_ffjord_integrate", "gpflow_error_string",
     "gpflow_abi_version",
@@ -100,6 +100,10 @@ def load():
     lib.gpflow_kernel_variant.argtypes = [D, ctypes.c_int, ctypes.c_char_p, ctypes.c_size_t]
     lib.gpflow_launch_count.restype = ctypes.c_int
     lib.gpflow_launch_count.argtypes = [D, ctypes.c_int]
+    lib.gpflow_tc_launches_total.restype = ctypes.c_int64
+    lib.gpflow_tc_launches_total.argtypes = []
+    lib.gpflow_tc_slab_samples.restype = ctypes.c_int
+    lib.gpflow_tc_slab_samples.argtypes = [D, ctypes.c_int64, ctypes.c_int]
     lib.gpflow_clock_probe.restype = ctypes.c_int
     lib.gpflow_clock_probe.argtypes = [P, P]
     BD = ctypes.POINTER(GpFlowBnafDesc)

@@ -87,14 +87,19 @@ bool sf2_match(const GpFlowDesc* d, int op) {
 
 // tc (chunked tensor-core path) takes the wide fp32 shapes without Euler penalization once the batch is large enough to
 // fill 128-row MMA tiles on every SM; GPFLOW_TC_MIN_BATCH overrides the threshold, GPFLOW_FLAG_FORCE_TC ignores it.
-int64_t tc_min_batch() {
-  static const int64_t v = [] { const char* e = getenv("GPFLOW_TC_MIN_BATCH"); return e ? (int64_t)atoll(e) : (int64_t)2048; }();
-  return v;
+// Measured crossovers (B200, train step, profiles/r2_tc_crossover.txt): d=10, H=[50,50,50] -- generic 29.6 ms vs tc 33.5 ms at
+// B = 4096, 58.4 vs 47.2 ms at 8192; d=64, H=[256,256] -- tc 8x faster already at B = 256.
+int64_t tc_min_batch(const GpFlowDesc* d) {
+  static const int64_t env = [] { const char* e = getenv("GPFLOW_TC_MIN_BATCH"); return e ? (int64_t)atoll(e) : (int64_t)-1; }();
+  if (env >= 0) return env;
+  int hmax = 0;
+  for (int i = 0; i < d->n_hidden; ++i) hmax = d->hidden[i] > hmax ? d->hidden[i] : hmax;
+  return hmax <= 64 ? 6144 : 128;
 }
 bool tc_selected(const GpFlowDesc* d, int64_t B) {
   if (d->flags & (GPFLOW_FLAG_FORCE_GENERIC | GPFLOW_FLAG_EULER_PEN)) return false;
   if (small_match(d, nullptr) || !tc_match(d)) return false;
-  return (d->flags & GPFLOW_FLAG_FORCE_TC) != 0 || B >= tc_min_batch();
+  return (d->flags & GPFLOW_FLAG_FORCE_TC) != 0 || B >= tc_min_batch(d);
 }
 
 template <typename T>
@@ -311,8 +316,8 @@ int gpflow_kernel_variant(const GpFlowDesc* d, int op, char* buf, size_t n) {
     snprintf(buf, n, "gpflow_sf2_kernel<f32,d=2,nb=1,H=[15,15],%s>", mode);
   else if (small_match(d, &s))
     snprintf(buf, n, "gpflow_small_kernel<%s,d=%d,nb=%d,H=[%d,%d],%s%s>", ty, s.d, s.nb, s.h1, s.h2, mode, eu);
-  else if (d->dtype == GPFLOW_F32 && tc_selected(d, (d->flags & GPFLOW_FLAG_FORCE_TC) ? 0 : tc_min_batch()))
-    snprintf(buf, n, "gpflow_tc<f32,tcgen05,%s> (batches >= %lld; generic below)", mode, (long long)tc_min_batch());
+  else if (d->dtype == GPFLOW_F32 && tc_selected(d, (d->flags & GPFLOW_FLAG_FORCE_TC) ? 0 : tc_min_batch(d)))
+    snprintf(buf, n, "gpflow_tc<f32,tcgen05,%s> (batches >= %lld; generic below)", mode, (long long)tc_min_batch(d));
   else
     snprintf(buf, n, "gpflow_generic_kernel<%s,%s%s>", ty, mode, eu);
   return GPFLOW_OK;
@@ -324,6 +329,13 @@ int gpflow_launch_count(const GpFlowDesc* d, int op) {
   SmallShape s;
   if (small_match(d, &s)) return 2;            // main kernel + deterministic finalize
   return generic_runs_padded(d) ? 4 : 3;       // [zero-padding scatter +] weight transpose + main kernel + finalize
+}
+
+int64_t gpflow_tc_launches_total(void) { return (int64_t)tc_launches_total(); }
+
+int gpflow_tc_slab_samples(const GpFlowDesc* d, int64_t B, int op) {
+  if (validate(d) != GPFLOW_OK || !tc_match(d)) return -1;
+  return tc_slab(d, B, op);
 }
 
 int gpflow_fp32_fma_burn(int64_t iters, void* sink, double* host_flops_out, void* stream) {

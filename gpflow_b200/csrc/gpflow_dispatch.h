@@ -53,6 +53,8 @@ GPF_DECL_GENERIC(generic_f64_euler, double);
 // chunked tensor-core path (gpflow_tc*.cuh): fp32, no Euler penalization, d <= 64, hidden widths <= 256
 bool tc_match(const GpFlowDesc* d);
 size_t tc_workspace(const GpFlowDesc* d, int64_t B, int op);
+unsigned long long tc_launches_total();
+int tc_slab(const GpFlowDesc* d, int64_t B, int op);
 int tc_f32(const GpFlowDesc* d, int op, const float* params, const float* x_in, const float* x_data, const float* grad_y,
            float* y_out, float* logdet_out, float* traj_out, float* grad_x_out, float* grads_out, float* scalars_out, int64_t B,
            void* ws, size_t wsb, cudaStream_t st, int sm_count, float* v_out, double t_eval);

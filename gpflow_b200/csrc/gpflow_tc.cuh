@@ -339,42 +339,31 @@ __global__ void tc_tb_mid_kernel(TcDims g, int l, const float* __restrict__ Tl, 
 // first layer, reverse (A.4, l = 1), part a.  In Ub: Tb_1 rows and hb_1 (row block d).
 //   ab_1 = hb sp + (sum_j Tb_1[j] W1x[:, j]) (-2 h sp)   -> written over hb_1 (row block d of Ub)
 //   xbar_j += W1x[:, j] . ab_1
-// Block = 4 samples x Hp1 units.
-constexpr int TC_L1B_SPB = 4;
+// Block = one sample x Hp1 units (W1x is read through L1: 64 KB shared by every block).
+constexpr int TC_L1B_SPB = 1;
 __global__ void tc_layer1_bwd_a_kernel(TcDims g, const float* __restrict__ W1T, const float* __restrict__ T1, const float* __restrict__ sp1,
                                        float* __restrict__ Ub, float* __restrict__ ybar) {
   __shared__ float xbs[8][TC_DMAX];   // per-warp partial dots, summed in a fixed order
   const int H = g.Hp[1], d = g.d, S = g.S;
   const int k = threadIdx.x, lane = k & 31, warp = k >> 5, nwarp = H >> 5;
-  float w[TC_DMAX];
-#pragma unroll
-  for (int j = 0; j < TC_DMAX; ++j) w[j] = j < d ? W1T[j * H + k] : 0.f;
-  for (int q = 0; q < TC_L1B_SPB; ++q) {
-    const int s = blockIdx.x * TC_L1B_SPB + q;
-    const float sp = sp1[(size_t)s * H + k];
-    const float h = T1[((size_t)d * S + s) * H + k];
-    float acc0 = 0.f, acc1 = 0.f;
-#pragma unroll
-    for (int j = 0; j < TC_DMAX; j += 2) {
-      if (j < d) acc0 = fmaf(Ub[((size_t)j * S + s) * H + k], w[j], acc0);
-      if (j + 1 < d) acc1 = fmaf(Ub[((size_t)(j + 1) * S + s) * H + k], w[j + 1], acc1);
-    }
-    const size_t o = ((size_t)d * S + s) * H + k;
-    const float ab = fmaf(Ub[o], sp, (acc0 + acc1) * (-2.f * h * sp));
-    Ub[o] = ab;
-#pragma unroll
-    for (int j = 0; j < TC_DMAX; ++j)
-      if (j < d) {
-        const float dot = warp_sum(w[j] * ab);
-        if (lane == 0) xbs[warp][j] = dot;
-      }
-    __syncthreads();
-    if (k < d) {
-      float tt = 0.f;
-      for (int r = 0; r < nwarp; ++r) tt += xbs[r][k];
-      ybar[(size_t)k * S + s] += tt;
-    }
-    __syncthreads();
+  const int s = blockIdx.x;
+  const float sp = sp1[(size_t)s * H + k];
+  const float h = T1[((size_t)d * S + s) * H + k];
+  float acc[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll 4
+  for (int j = 0; j < d; ++j) acc[j & 3] = fmaf(Ub[((size_t)j * S + s) * H + k], __ldg(W1T + j * H + k), acc[j & 3]);
+  const size_t o = ((size_t)d * S + s) * H + k;
+  const float ab = fmaf(Ub[o], sp, ((acc[0] + acc[1]) + (acc[2] + acc[3])) * (-2.f * h * sp));
+  Ub[o] = ab;
+  for (int j = 0; j < d; ++j) {
+    const float dot = warp_sum(__ldg(W1T + j * H + k) * ab);
+    if (lane == 0) xbs[warp][j] = dot;
+  }
+  __syncthreads();
+  if (k < d) {
+    float tt = 0.f;
+    for (int r = 0; r < nwarp; ++r) tt += xbs[r][k];
+    ybar[(size_t)k * S + s] += tt;
   }
 }
 // part b: dW1x[:, j] += sum_s (ab_1 x_j + sp Tb_1[j]),  dw1t += sum_s ab_1 t,  db1 += sum_s ab_1.
@@ -389,6 +378,7 @@ __global__ void __launch_bounds__(256) tc_layer1_bwd_b_kernel(TcDims g, const fl
   float acc[8], gt = 0.f, gb = 0.f;
 #pragma unroll
   for (int e = 0; e < 8; ++e) acc[e] = 0.f;
+#pragma unroll 4
   for (int s = s_lo + wy; s < s_hi; s += 8) {
     const float sp = sp1[(size_t)s * H + k];
     const float ab = Ub[((size_t)d * S + s) * H + k];

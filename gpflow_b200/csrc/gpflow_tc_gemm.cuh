@@ -34,6 +34,8 @@ constexpr int KC = 32;                 // fp32 elements per K chunk = one 128-by
 constexpr int MT = 128;                // rows of A per tile = TMEM lanes
 constexpr int kProdWarps = 8;
 constexpr int kProdThreads = kProdWarps * 32;
+constexpr int kGroupWarps = kProdWarps / 2;      // two producer groups work on alternate chunks (stages)
+constexpr int kGroupThreads = kGroupWarps * 32;   // threads that cooperate on one operand tile
 constexpr int kEpiWarps = 4;
 constexpr int kThreads = (2 + kEpiWarps + kProdWarps) * 32;   // warp 0: TMA, warp 1: MMA, 2..5: epilogue, 6..13: producers
 constexpr uint32_t kATileBytes = MT * 128;                     // 16 KB per hi / lo tile
@@ -185,14 +187,15 @@ GPF_DEV void store_chunk(char* t_hi, char* t_lo, int r, int c, float4 x) {
 // the producers wait for the shared-memory stage of chunk i+1 to be released: fetch_* fills a register fragment
 // (R / 8 floats per thread), commit_* splits it into tf32 hi / lo and writes the swizzled K-major tiles.
 //
-// ROWS mapping (operand rows are K-contiguous in memory): q = ptid + 256 it, row r = q >> 3, 16-byte chunk c = q & 7;
+// ptid below is the thread index inside its producer GROUP (0 .. kGroupThreads - 1).
+// ROWS mapping (operand rows are K-contiguous in memory): q = ptid + 128 it, row r = q >> 3, 16-byte chunk c = q & 7;
 // 8 consecutive threads read one 128-byte row segment.
 template <int R>
 GPF_DEV void fetch_rows(float* frag, int ptid, const float* __restrict__ X, long long ld, long long row0, long long rows_valid,
                         int k0, int k_valid) {
 #pragma unroll
-  for (int it = 0; it < R * 8 / kProdThreads; ++it) {
-    const int q = ptid + it * kProdThreads;
+  for (int it = 0; it < R * 8 / kGroupThreads; ++it) {
+    const int q = ptid + it * kGroupThreads;
     const int r = q >> 3, c = q & 7;
     float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
     if (row0 + r < rows_valid && c * 4 < k_valid) x = __ldg(reinterpret_cast<const float4*>(X + (row0 + r) * ld + k0 + c * 4));
@@ -202,19 +205,19 @@ GPF_DEV void fetch_rows(float* frag, int ptid, const float* __restrict__ X, long
 template <int R>
 GPF_DEV void commit_rows(const float* frag, int ptid, char* t_hi, char* t_lo) {
 #pragma unroll
-  for (int it = 0; it < R * 8 / kProdThreads; ++it) {
-    const int q = ptid + it * kProdThreads;
+  for (int it = 0; it < R * 8 / kGroupThreads; ++it) {
+    const int q = ptid + it * kGroupThreads;
     store_chunk(t_hi, t_lo, q >> 3, q & 7, make_float4(frag[4 * it], frag[4 * it + 1], frag[4 * it + 2], frag[4 * it + 3]));
   }
 }
 // UNITS mapping (consecutive operand rows are contiguous in memory: transposed operands, per-sample column vectors):
-// unit u = warp + 8 it covers rows (u >> 2) * 32 + lane and k = 8 (u & 3) .. + 7; f(m, kq, v) fills v[0..7] = tile[m][8 kq + i].
+// unit u = warp + 4 it covers rows (u >> 2) * 32 + lane and k = 8 (u & 3) .. + 7; f(m, kq, v) fills v[0..7] = tile[m][8 kq + i].
 template <int R, class F>
 GPF_DEV void fetch_units(float* frag, int ptid, F f) {
   const int warp = ptid >> 5, lane = ptid & 31;
 #pragma unroll
-  for (int it = 0; it < R / 64; ++it) {
-    const int u = warp + it * kProdWarps;
+  for (int it = 0; it < R / 32; ++it) {
+    const int u = warp + it * kGroupWarps;
     float v[8];
     f((u >> 2) * 32 + lane, u & 3, v);
 #pragma unroll
@@ -225,8 +228,8 @@ template <int R>
 GPF_DEV void commit_units(const float* frag, int ptid, char* t_hi, char* t_lo) {
   const int warp = ptid >> 5, lane = ptid & 31;
 #pragma unroll
-  for (int it = 0; it < R / 64; ++it) {
-    const int u = warp + it * kProdWarps;
+  for (int it = 0; it < R / 32; ++it) {
+    const int u = warp + it * kGroupWarps;
     const int m = (u >> 2) * 32 + lane, kq = u & 3;
     store_chunk(t_hi, t_lo, m, 2 * kq, make_float4(frag[8 * it], frag[8 * it + 1], frag[8 * it + 2], frag[8 * it + 3]));
     store_chunk(t_hi, t_lo, m, 2 * kq + 1, make_float4(frag[8 * it + 4], frag[8 * it + 5], frag[8 * it + 6], frag[8 * it + 7]));
@@ -276,8 +279,8 @@ struct EpiCtx {
 //   NT (N tile, multiple of 16, <= 256), STAGES, B_TMA, A_MODE, B_MODE (MODE_ROWS / MODE_UNITS of the fragments),
 //   Params (POD, passed by value), Tile {int nk (K chunks, may be 0 = empty tile); int n (MMA N, multiple of 16); ...},
 //   num_tiles(p), decode(p, t, tile),
-//   fetch_a(p, tile, kc, ptid, float* frag)          frag: MT / 8 floats in A_MODE order
-//   fetch_b(p, tile, kc, ptid, float* frag)          when !B_TMA (NT / 8 floats, B_MODE order)
+//   fetch_a(p, tile, kc, ptid, float* frag)          frag: MT / 4 floats in A_MODE order; ptid = thread in its group
+//   fetch_b(p, tile, kc, ptid, float* frag)          when !B_TMA (NT / 4 floats, B_MODE order)
 //   tmap(p, tile), tma_coords(p, tile, kc, c0, r_hi, r_lo) when B_TMA
 //   epilogue(p, tile, ctx, row, col0, ncols, v)      v[i] = D[row][col0 + i]
 // ---------------------------------------------------------------------------------------------------------------
@@ -309,7 +312,7 @@ __global__ void __launch_bounds__(kThreads, 1) tc_gemm_kernel(const __grid_const
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < Op::STAGES; ++s) {
-      mbar_init(&full_bar[s], kProdWarps + (Op::B_TMA ? 1 : 0));
+      mbar_init(&full_bar[s], kGroupWarps + (Op::B_TMA ? 1 : 0));
       mbar_init(&empty_bar[s], 1);
     }
     for (int b = 0; b < 2; ++b) {
@@ -429,50 +432,55 @@ __global__ void __launch_bounds__(kThreads, 1) tc_gemm_kernel(const __grid_const
     }
     if (threadIdx.x == 64) GPF_TC_PROF_STORE(2);
   } else {
-    // ===== operand producers: the loads of chunk i+1 are issued before waiting for its shared-memory stage =====
+    // ===== operand producers: two groups of 4 warps work on alternate chunks (group g: chunks g, g + 2, ...), so that
+    // one group's fence / arrive / wait-for-empty overlaps the other group's loads and stores; inside a group the
+    // global loads of its next chunk are in flight while the current one is split and written =====
     const int ptid = threadIdx.x - (2 + kEpiWarps) * 32;
+    const int grp = ptid >> 7, gtid = ptid & (kGroupThreads - 1);
     GPF_TC_PROF_DECL
-    uint32_t stage = 0, phase = 0;
-    float fa[MT / 8];
-    float fb[Op::B_TMA ? 1 : Op::NT / 8];
-    int t = blockIdx.x, kc = 0;
-    typename Op::Tile tile;
-    tile.nk = 0;
-    // advance (t, kc, tile) to the first / next chunk; returns false when the CTA's tiles are exhausted
-    auto first = [&]() -> bool {
-      while (t < ntiles) {
-        Op::decode(p, t, tile);
-        if (tile.nk > 0) { kc = 0; return true; }
-        t += gridDim.x;
+    constexpr int kFB = Op::B_TMA ? 1 : Op::NT / 4;
+    float fa[MT / 4], fb[kFB];
+    struct Pos { int t, kc; typename Op::Tile tile; bool ok; };
+    auto seek = [&](Pos& q) {        // first chunk of the first non-empty tile at or after q.t
+      while (q.t < ntiles) {
+        Op::decode(p, q.t, q.tile);
+        if (q.tile.nk > 0) { q.kc = 0; q.ok = true; return; }
+        q.t += gridDim.x;
       }
-      return false;
+      q.ok = false;
     };
-    auto next = [&]() -> bool {
-      if (++kc < tile.nk) return true;
-      t += gridDim.x;
-      return first();
+    auto advance = [&](Pos& q) {
+      if (!q.ok) return;
+      if (++q.kc < q.tile.nk) return;
+      q.t += gridDim.x;
+      seek(q);
     };
-    bool have = first();
-    if (have) {
-      Op::fetch_a(p, tile, kc, ptid, fa);
-      if constexpr (!Op::B_TMA) Op::fetch_b(p, tile, kc, ptid, fb);
-    }
-    while (have) {
+    auto fetch = [&](const Pos& q) {
+      if (!q.ok) return;
+      Op::fetch_a(p, q.tile, q.kc, gtid, fa);
+      if constexpr (!Op::B_TMA) Op::fetch_b(p, q.tile, q.kc, gtid, fb);
+    };
+    Pos q;
+    q.t = blockIdx.x; q.kc = 0; q.ok = false;
+    seek(q);
+    if (grp == 1) advance(q);
+    fetch(q);
+    uint32_t c = grp;                // sequence number of the chunk in this CTA's stream
+    while (q.ok) {
+      const uint32_t stage = c % Op::STAGES, phase = (c / Op::STAGES) & 1;
       GPF_TC_WAIT(&empty_bar[stage], phase ^ 1);
       unsigned char* st = smem + stage * SM::kStageBytes;
-      commit_frag<MT, Op::A_MODE>(fa, ptid, reinterpret_cast<char*>(st), reinterpret_cast<char*>(st + kATileBytes));
+      commit_frag<MT, Op::A_MODE>(fa, gtid, reinterpret_cast<char*>(st), reinterpret_cast<char*>(st + kATileBytes));
       if constexpr (!Op::B_TMA)
-        commit_frag<Op::NT, Op::B_MODE>(fb, ptid, reinterpret_cast<char*>(st + 2 * kATileBytes),
+        commit_frag<Op::NT, Op::B_MODE>(fb, gtid, reinterpret_cast<char*>(st + 2 * kATileBytes),
                                         reinterpret_cast<char*>(st + 2 * kATileBytes + SM::kBTileBytes));
       fence_proxy_async();     // generic-proxy stores -> visible to the tensor core's async proxy
       __syncwarp();
       if (lane == 0) mbar_arrive(&full_bar[stage]);
-      if (++stage == Op::STAGES) { stage = 0; phase ^= 1; }
-      have = next();
-      if (have) {
-        Op::fetch_a(p, tile, kc, ptid, fa);
-        if constexpr (!Op::B_TMA) Op::fetch_b(p, tile, kc, ptid, fb);
-      }
+      c += 2;
+      advance(q);
+      advance(q);
+      fetch(q);
     }
     if (ptid == 0) GPF_TC_PROF_STORE(3);
   }

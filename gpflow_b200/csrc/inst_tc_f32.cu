@@ -5,6 +5,8 @@ namespace gpflow {
 
 bool tc_match(const GpFlowDesc* d) { return tc::tc_shape_ok(d); }
 size_t tc_workspace(const GpFlowDesc* d, int64_t B, int op) { return tc::tc_workspace_bytes(d, B, op); }
+unsigned long long tc_launches_total() { return tc::tc_launch_counter(); }
+int tc_slab(const GpFlowDesc* d, int64_t B, int op) { return tc::tc_slab_size(d, B, op); }
 
 int tc_f32(const GpFlowDesc* d, int op, const float* params, const float* x_in, const float* x_data, const float* grad_y,
            float* y_out, float* logdet_out, float* traj_out, float* grad_x_out, float* grads_out, float* scalars_out, int64_t B,

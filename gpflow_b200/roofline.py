@@ -28,3 +28,17 @@ def flops_per_eval(d, nb, hidden):
 def algorithmic_flops_per_sample(d, nb, hidden, n_steps, train=True, euler=False):
     fwd = (4 + (10 if euler else 0)) * n_steps * flops_per_eval(d, nb, hidden)
     return 3.0 * fwd if train else fwd
+
+
+def executed_flops_per_sample_tc(d, nb, hidden, n_steps, train=True):
+    """Flops the chunked tensor-core path (gpflow_tc*.cuh) EXECUTES per sample, fp32-equivalent (each 3xTF32 product
+    counted once), on the zero-padded widths.  Per velocity evaluation, forward: first layer 2 d H_1, hidden layers
+    2 (d + 1) H_{l-1} H_l (value row + d tangent rows), last layer in contracted form: F for all d nb rows, D and G for
+    the R kept rows, 2 H_L each.  The reverse sweep of an evaluation runs a data GEMM and a weight-gradient GEMM of the
+    same size for every forward GEMM (2x), and the train step recomputes the forward evaluation before reversing it:
+    train = 4 N (forward + recompute + 2 forward) = 4 x forward."""
+    H = [(h + 63) // 64 * 64 for h in hidden]
+    R = sum(d - k for k in range(nb))
+    f = 2.0 * d * H[0] + sum(2.0 * (d + 1) * H[l - 1] * H[l] for l in range(1, len(H))) + 2.0 * H[-1] * (d * nb + 2 * R)
+    fwd = 4 * n_steps * f
+    return 4.0 * fwd if train else fwd

@@ -57,7 +57,8 @@ typedef enum GpFlowOp { GPFLOW_OP_FORWARD = 0, GPFLOW_OP_TRAIN_STEP = 1, GPFLOW_
 #define GPFLOW_FLAG_FORCE_V1 0x20u      /* testing aid: use the register-resident v1 small-d kernel instead of sf2     */
 #define GPFLOW_FLAG_FORCE_TC 0x40u      /* testing aid: use the chunked tensor-core (tcgen05) path whatever the batch size;
                                            GPFLOW_ERR_UNSUPPORTED if the shape is outside it (fp32, no Euler, d <= 64,
-                                           hidden widths <= 256).  Without it the path is taken for batches >= 2048.   */
+                                           hidden widths <= 256).  Without it the path is taken above a measured
+                                           batch threshold (128 for wide nets, 6144 for widths <= 64).           */
 
 /*
  * One GP flow = get_gp_flow(dim, velocity_dict, nb_layers_gp, T_final, ...) with nb_blocks == 1
@@ -153,6 +154,13 @@ int gpflow_kernel_variant(const GpFlowDesc* desc, int op, char* buf, size_t buf_
 
 /* Number of kernel launches one call of `op` enqueues (for launch accounting in benchmarks). */
 int gpflow_launch_count(const GpFlowDesc* desc, int op);
+
+/* Launch accounting of the chunked tensor-core path (whose launch count depends on the batch: slabs x evaluations x
+ * kernels per evaluation): cumulative number of kernels the path has enqueued in this process (host counter; take the
+ * difference around the region of interest).  gpflow_tc_slab_samples: samples per slab for a batch of B (-1 if the
+ * shape is outside the path). */
+int64_t gpflow_tc_launches_total(void);
+int gpflow_tc_slab_samples(const GpFlowDesc* desc, int64_t B, int op);
 
 /* FP32 FMA micro-benchmark (roofline denominator): every thread of a grid that fills all SMs runs
  * `iters` x 128 independent-chain FFMAs.  `sink` is a device float[1] (never written in practice).  The number of

@@ -111,10 +111,10 @@ def test_tc_is_the_default_for_large_wide_batches():
     assert "generic" in G.kernel_variant(cfg, euler_coef=5e-5)        # Euler penalization stays on the generic kernel
     assert "generic" in G.kernel_variant(cfg, torch.float64)
     assert "sf2" in G.kernel_variant(G.FlowConfig(d=2, nb=1, hidden=(15, 15)))
-    spec, params, x_data, x_map = _inputs(10, 9, (50, 50, 50), 2048, 2, 0.03)
+    spec, params, x_data, x_map = _inputs(10, 9, (50, 50, 50), 6144, 2, 0.03)
     flat = O.flatten_params(params).float().cuda()
     cfg2 = G.FlowConfig(d=10, nb=9, hidden=(50, 50, 50), n_steps=2)
-    a = G.fused_train_step(cfg2, flat, x_data.float().cuda(), x_map.float().cuda())                      # default: tc at B >= 2048
+    a = G.fused_train_step(cfg2, flat, x_data.float().cuda(), x_map.float().cuda())                      # default: tc from B = 6144 for this shape
     b = G.fused_train_step(cfg2, flat, x_data.float().cuda(), x_map.float().cuda(), force_tc=True)
     c = G.fused_train_step(cfg2, flat, x_data.float().cuda(), x_map.float().cuda(), force_generic=True)
     assert torch.equal(a["buf"], b["buf"]) and rel(a["grads"], c["grads"]) < 5e-6
