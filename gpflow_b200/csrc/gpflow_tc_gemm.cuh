@@ -284,6 +284,11 @@ struct EpiCtx {
 //   tmap(p, tile), tma_coords(p, tile, kc, c0, r_hi, r_lo) when B_TMA
 //   epilogue(p, tile, ctx, row, col0, ncols, v)      v[i] = D[row][col0 + i]
 // ---------------------------------------------------------------------------------------------------------------
+// Op::A_TMA (optional, default false): the A operand (128 rows, pre-split weights) also arrives by TMA; the op then supplies
+// tmap_a(p, tile) and tma_coords_a(p, tile, kc, c0, r_hi, r_lo) and no fetch_a.
+template <class Op, class = void> struct OpATma { static constexpr bool value = false; };
+template <class Op> struct OpATma<Op, decltype((void)Op::A_TMA)> { static constexpr bool value = Op::A_TMA; };
+
 template <class Op>
 struct GemmSmem {
   static constexpr uint32_t kBTileBytes = Op::NT * 128;
@@ -312,7 +317,7 @@ __global__ void __launch_bounds__(kThreads, 1) tc_gemm_kernel(const __grid_const
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < Op::STAGES; ++s) {
-      mbar_init(&full_bar[s], kGroupWarps + (Op::B_TMA ? 1 : 0));
+      mbar_init(&full_bar[s], ((!OpATma<Op>::value || !Op::B_TMA) ? kGroupWarps : 0) + ((OpATma<Op>::value || Op::B_TMA) ? 1 : 0));
       mbar_init(&empty_bar[s], 1);
     }
     for (int b = 0; b < 2; ++b) {
@@ -328,8 +333,8 @@ __global__ void __launch_bounds__(kThreads, 1) tc_gemm_kernel(const __grid_const
   const uint32_t tmem_base = *tmem_holder;
 
   if (warp == 0) {
-    // ===== TMA producer of the weight operand =====
-    if constexpr (Op::B_TMA) {
+    // ===== TMA producer of the weight operand(s) =====
+    if constexpr (Op::B_TMA || OpATma<Op>::value) {
       if (lane == 0) {
         GPF_TC_PROF_DECL
         uint32_t stage = 0, phase = 0;
@@ -346,11 +351,18 @@ __global__ void __launch_bounds__(kThreads, 1) tc_gemm_kernel(const __grid_const
               continue;
             }
 #endif
-            mbar_expect_tx(&full_bar[stage], 2 * SM::kBTileBytes);
+            mbar_expect_tx(&full_bar[stage], (Op::B_TMA ? 2 * SM::kBTileBytes : 0) + (OpATma<Op>::value ? 2 * kATileBytes : 0));
             int c0, r_hi, r_lo;
-            Op::tma_coords(p, tile, kc, c0, r_hi, r_lo);
-            tma_load_2d(st + 2 * kATileBytes, Op::tmap(p, tile), c0, r_hi, &full_bar[stage]);
-            tma_load_2d(st + 2 * kATileBytes + SM::kBTileBytes, Op::tmap(p, tile), c0, r_lo, &full_bar[stage]);
+            if constexpr (OpATma<Op>::value) {
+              Op::tma_coords_a(p, tile, kc, c0, r_hi, r_lo);
+              tma_load_2d(st, Op::tmap_a(p, tile), c0, r_hi, &full_bar[stage]);
+              tma_load_2d(st + kATileBytes, Op::tmap_a(p, tile), c0, r_lo, &full_bar[stage]);
+            }
+            if constexpr (Op::B_TMA) {
+              Op::tma_coords(p, tile, kc, c0, r_hi, r_lo);
+              tma_load_2d(st + 2 * kATileBytes, Op::tmap(p, tile), c0, r_hi, &full_bar[stage]);
+              tma_load_2d(st + 2 * kATileBytes + SM::kBTileBytes, Op::tmap(p, tile), c0, r_lo, &full_bar[stage]);
+            }
             if (++stage == Op::STAGES) { stage = 0; phase ^= 1; }
           }
         }
@@ -439,7 +451,7 @@ __global__ void __launch_bounds__(kThreads, 1) tc_gemm_kernel(const __grid_const
     const int grp = ptid >> 7, gtid = ptid & (kGroupThreads - 1);
     GPF_TC_PROF_DECL
     constexpr int kFB = Op::B_TMA ? 1 : Op::NT / 4;
-    float fa[MT / 4], fb[kFB];
+    float fa[OpATma<Op>::value ? 1 : MT / 4], fb[kFB];
     struct Pos { int t, kc; typename Op::Tile tile; bool ok; };
     auto seek = [&](Pos& q) {        // first chunk of the first non-empty tile at or after q.t
       while (q.t < ntiles) {
@@ -457,12 +469,12 @@ __global__ void __launch_bounds__(kThreads, 1) tc_gemm_kernel(const __grid_const
     };
     auto fetch = [&](const Pos& q) {
       if (!q.ok) return;
-      Op::fetch_a(p, q.tile, q.kc, gtid, fa);
+      if constexpr (!OpATma<Op>::value) Op::fetch_a(p, q.tile, q.kc, gtid, fa);
       if constexpr (!Op::B_TMA) Op::fetch_b(p, q.tile, q.kc, gtid, fb);
     };
     Pos q;
     q.t = blockIdx.x; q.kc = 0; q.ok = false;
-    seek(q);
+    if constexpr (!(OpATma<Op>::value && Op::B_TMA)) seek(q);     // both operands by TMA: nothing to produce
     if (grp == 1) advance(q);
     fetch(q);
     uint32_t c = grp;                // sequence number of the chunk in this CTA's stream
@@ -470,7 +482,8 @@ __global__ void __launch_bounds__(kThreads, 1) tc_gemm_kernel(const __grid_const
       const uint32_t stage = c % Op::STAGES, phase = (c / Op::STAGES) & 1;
       GPF_TC_WAIT(&empty_bar[stage], phase ^ 1);
       unsigned char* st = smem + stage * SM::kStageBytes;
-      commit_frag<MT, Op::A_MODE>(fa, gtid, reinterpret_cast<char*>(st), reinterpret_cast<char*>(st + kATileBytes));
+      if constexpr (!OpATma<Op>::value)
+        commit_frag<MT, Op::A_MODE>(fa, gtid, reinterpret_cast<char*>(st), reinterpret_cast<char*>(st + kATileBytes));
       if constexpr (!Op::B_TMA)
         commit_frag<Op::NT, Op::B_MODE>(fb, gtid, reinterpret_cast<char*>(st + 2 * kATileBytes),
                                         reinterpret_cast<char*>(st + 2 * kATileBytes + SM::kBTileBytes));

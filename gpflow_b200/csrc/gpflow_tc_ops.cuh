@@ -86,61 +86,56 @@ struct OpLayer {
 };
 
 // ---------------------------------------------------------------------------------------------------------------
-// last layer, forward, contracted form (header of Generic<T>): grouped GEMMs with M = samples
-//   F_(i,n) = W[(i,n)] . h_L + b      D_(i,n) = W[(i,n)] . T_L[i]       (groups i: rows n <= min(i, nb-1), contiguous)
-//   G_(i,n) = W[(i,n)] . R_n                                            (groups n: rows i >= n, contiguous in W3Gs)
-// outputs in column layout [p = i nb + n][s]
+// last layer, forward, contracted form (header of Generic<T>): grouped GEMMs
+//   D_(i,n) = W[(i,n)] . T_L[i]      groups i: rows n <= min(i, nb-1), contiguous in W3s
+//   G_(i,n) = W[(i,n)] . R_n         groups n: rows i >= n, contiguous in W3Gs
+// (F_(i,n) = W[(i,n)] . h_L + b for all rows is one dense GEMM: OpLayer mode 3.)
+// Orientation: a tcgen05.mma costs ~100-130 cycles whatever its N (measured; the A tile is re-read from shared memory
+// for every instruction), so the SAMPLES go on the 256-wide N side and the group's weight rows -- at most d <= 64 of
+// the 128 M rows are used -- on the M side: out[q][s], A = weight rows by TMA, B = activation rows by the producers.
+// Outputs in column layout [p = i nb + n][s]: an output row is contiguous.
 // ---------------------------------------------------------------------------------------------------------------
 template <int ST_>
 struct OpLast {
-  static constexpr int NT = 64, STAGES = ST_;
-  static constexpr bool B_TMA = true;
+  static constexpr int NT = 256, STAGES = ST_;
+  static constexpr bool A_TMA = true, B_TMA = false;
   static constexpr int A_MODE = MODE_ROWS, B_MODE = MODE_ROWS;
   struct Params {
-    CUtensorMap map3, mapG;
-    const float *TL, *R, *b3;   // TL: [(d+1) S][K] (row block d = h_L)
-    float *F, *G, *D;
-    int d, nb, S, K, mt, lo3, loG;
+    CUtensorMap map3, mapG;     // boxes of 128 weight rows
+    const float *TL, *R;        // TL: [(d+1) S][K]
+    float *G, *D;
+    int d, nb, S, K, nt, lo3, loG;
   };
-  struct Tile { int nk, n, fam, idx, cnt, m0; };
-  GPF_DEV static int num_tiles(const Params& p) { return (p.d + p.nb) * p.mt; }
-  GPF_DEV static void decode(const Params& p, int t, Tile& tl) {   // F (fam 0) is a dense GEMM now: OpLayer mode 3
-    const int grp = t / p.mt;
-    tl.m0 = (t % p.mt) * MT;
+  struct Tile { int nk, n, fam, idx, cnt, s0; };
+  GPF_DEV static int num_tiles(const Params& p) { return (p.d + p.nb) * p.nt; }
+  GPF_DEV static void decode(const Params& p, int t, Tile& tl) {
+    const int grp = t / p.nt;
+    tl.s0 = (t % p.nt) * NT;
     tl.nk = p.K / KC;
+    tl.n = NT;
     if (grp < p.d) {
-      tl.fam = 1;
-      tl.idx = grp;
+      tl.fam = 1; tl.idx = grp;
       tl.cnt = (tl.idx < p.nb - 1 ? tl.idx : p.nb - 1) + 1;
     } else {
-      tl.fam = 2;
-      tl.idx = grp - p.d;
+      tl.fam = 2; tl.idx = grp - p.d;
       tl.cnt = p.d - tl.idx;
     }
-    tl.n = (tl.cnt + 15) / 16 * 16;
   }
-  GPF_DEV static const CUtensorMap* tmap(const Params& p, const Tile& tl) { return tl.fam == 2 ? &p.mapG : &p.map3; }
-  GPF_DEV static void tma_coords(const Params& p, const Tile& tl, int kc, int& c0, int& r_hi, int& r_lo) {
+  GPF_DEV static const CUtensorMap* tmap_a(const Params& p, const Tile& tl) { return tl.fam == 2 ? &p.mapG : &p.map3; }
+  GPF_DEV static void tma_coords_a(const Params& p, const Tile& tl, int kc, int& c0, int& r_hi, int& r_lo) {
     c0 = kc * KC;
     if (tl.fam == 2) { r_hi = tl.idx * p.d + tl.idx; r_lo = p.loG + r_hi; }
     else { r_hi = tl.idx * p.nb; r_lo = p.lo3 + r_hi; }
   }
-  GPF_DEV static void fetch_a(const Params& p, const Tile& tl, int kc, int ptid, float* frag) {
-    const float* base = tl.fam == 0 ? p.TL + (size_t)p.d * p.S * p.K
-                                    : (tl.fam == 1 ? p.TL + (size_t)tl.idx * p.S * p.K : p.R + (size_t)tl.idx * p.S * p.K);
-    fetch_rows<MT>(frag, ptid, base, p.K, tl.m0, p.S, kc * KC, p.K - kc * KC);
+  GPF_DEV static void fetch_b(const Params& p, const Tile& tl, int kc, int ptid, float* frag) {
+    const float* base = tl.fam == 1 ? p.TL + (size_t)tl.idx * p.S * p.K : p.R + (size_t)tl.idx * p.S * p.K;
+    fetch_rows<NT>(frag, ptid, base, p.K, tl.s0, p.S, kc * KC, p.K - kc * KC);
   }
-  GPF_DEV static void epilogue(const Params& p, const Tile& tl, const EpiCtx&, int row, int c0, int nc, float (&v)[32]) {
-    const int s = tl.m0 + row;
-#pragma unroll
-    for (int i = 0; i < 32; ++i) {
-      const int c = c0 + i;
-      if (i < nc && c < tl.cnt) {
-        if (tl.fam == 0) { const int q = tl.idx * p.nb + c; p.F[(size_t)q * p.S + s] = v[i] + p.b3[q]; }
-        else if (tl.fam == 1) p.D[(size_t)(tl.idx * p.nb + c) * p.S + s] = v[i];
-        else p.G[(size_t)((tl.idx + c) * p.nb + tl.idx) * p.S + s] = v[i];
-      }
-    }
+  GPF_DEV static void epilogue(const Params& p, const Tile& tl, const EpiCtx& ctx, int, int c0, int nc, float (&v)[32]) {
+    ctx.store_rows(v, nc, c0, [&p, &tl](int q) -> float* {
+      if (q >= tl.cnt) return nullptr;
+      return tl.fam == 1 ? p.D + (size_t)(tl.idx * p.nb + q) * p.S + tl.s0
+                         : p.G + (size_t)((tl.idx + q) * p.nb + tl.idx) * p.S + tl.s0; }, false);
   }
 };
 
@@ -234,103 +229,87 @@ struct OpLB {
 };
 
 // ---------------------------------------------------------------------------------------------------------------
-// last layer, weight gradient: out[k][q] (M = hidden units k, N = rows q of one group), K = samples of the slab
-//   groups i:  dW[(i,n)] += sum_s fb_(i,n) h_L + Db_(i,n) T_L[i]     (K = 2 S: the two products back to back)
-//   groups n:  dW[(i,n)] += sum_s Qb_i R_n
-// K is cut into segments of 8 chunks (256 samples); every output tile belongs to ONE CTA which adds its segments in
-// order with red.global.add (round-to-nearest fp32) => deterministic.
+// last layer, weight gradient: out[q][k] = sum_s coef_q[s] X[s][k]  (M = output rows q, N = hidden units k, K = samples)
+//   F tiles (128 rows each, all rows):  dW[(i,n)] += sum_s fb_(i,n) h_L       fb = 2 (Qb_i SX_n - x_i SQ_n) on kept rows
+//   D groups i:                         dW[(i,n)] += sum_s Db_(i,n) T_L[i]    Db = -s_i SQ_n
+//   G groups n:                         dW[(i,n)] += sum_s Qb_i R_n
+// Same orientation argument as OpLast: the 256-wide side is N.  K is cut into segments of 8 chunks (256 samples); a
+// work item = (output tile, K split) belongs to ONE CTA which adds its segments in order into the split's partial with
+// red.global.add (round-to-nearest fp32) => deterministic; the partials are summed by tc_finalize_kernel.
 // ---------------------------------------------------------------------------------------------------------------
-template <int ST_>
+template <int NT_, int ST_>
 struct OpW3 {
-  static constexpr int NT = 64, STAGES = ST_;
+  static constexpr int NT = NT_, STAGES = ST_;
   static constexpr bool B_TMA = false;
-  static constexpr int A_MODE = MODE_UNITS, B_MODE = MODE_ROWS;
+  static constexpr int A_MODE = MODE_ROWS, B_MODE = MODE_UNITS;
   struct Params {
     const float *TL, *R;
     const float *Qb, *SX, *SQ, *x, *sj;
     float* gW3;        // [nsplit][nout][K] partial accumulators
-    int d, nb, S, K, mtk, nseg, n_out, G, rounds, nsplit, nout;
+    int d, nb, nout, S, K, nF, n_out, nseg, nsplit, items, G, segs_per_item, rounds;
   };
-  struct Tile { int nk, n, fam, idx, cnt, km, chunk0, sp; };
+  struct Tile { int nk, n, fam, idx, cnt, chunk0, sp; };
   GPF_DEV static int num_tiles(const Params& p) { return p.rounds * p.G; }
   GPF_DEV static void decode(const Params& p, int t, Tile& tl) {
     const int r = t / p.G, b = t % p.G;
-    int o, seg;
-    if (p.nsplit == 1) { o = (r / p.nseg) * p.G + b; seg = r % p.nseg; tl.sp = 0; }
-    else { o = b / p.nsplit; tl.sp = b % p.nsplit; seg = r * p.nsplit + tl.sp; }   // G = n_out * nsplit: one output tile per CTA
-    tl.nk = 0; tl.n = 16; tl.fam = 0; tl.idx = 0; tl.cnt = 0; tl.km = 0; tl.chunk0 = seg * TC_SEG;
-    if (o >= p.n_out || seg >= p.nseg) return;
-    const int grp = o / p.mtk;
-    tl.km = o % p.mtk;
-    if (grp < p.d) {
-      tl.fam = 0; tl.idx = grp;
-      tl.cnt = (grp < p.nb - 1 ? grp : p.nb - 1) + 1;
-      tl.nk = TC_SEG;                                  // 2 S / 32 chunks = nseg segments of 8 (S % 256 == 0)
-    } else {
-      tl.fam = 1; tl.idx = grp - p.d;
-      tl.cnt = p.d - tl.idx;
-      tl.nk = tl.chunk0 < p.S / KC ? TC_SEG : 0;
-    }
-    tl.n = (tl.cnt + 15) / 16 * 16;
+    const int item = b + (r / p.segs_per_item) * p.G;
+    tl.nk = 0; tl.n = p.K; tl.fam = 0; tl.idx = 0; tl.cnt = 0; tl.chunk0 = 0; tl.sp = 0;
+    if (item >= p.items) return;
+    const int o = item / p.nsplit;
+    tl.sp = item % p.nsplit;
+    const int seg = tl.sp + (r % p.segs_per_item) * p.nsplit;
+    if (seg >= p.nseg) return;
+    tl.chunk0 = seg * TC_SEG;
+    tl.nk = TC_SEG;
+    if (o < p.nF) { tl.fam = 0; tl.idx = o; tl.cnt = p.nout - o * MT < MT ? p.nout - o * MT : MT; }
+    else if (o < p.nF + p.d) { tl.fam = 1; tl.idx = o - p.nF; tl.cnt = (tl.idx < p.nb - 1 ? tl.idx : p.nb - 1) + 1; }
+    else { tl.fam = 2; tl.idx = o - p.nF - p.d; tl.cnt = p.d - tl.idx; }
   }
   GPF_DEV static void fetch_a(const Params& p, const Tile& tl, int kc, int ptid, float* frag) {
-    const int S = p.S, K = p.K;
-    fetch_units<MT>(frag, ptid, [&](int m, int kq, float (&v)[8]) {
-      const int k = tl.km * MT + m;
-      int sg = (tl.chunk0 + kc) * KC + kq * 8;
-      const float* X;
-      if (tl.fam == 0) {
-        if (sg < S) X = p.TL + (size_t)p.d * S * K;
-        else { X = p.TL + (size_t)tl.idx * S * K; sg -= S; }
-      } else {
-        X = p.R + (size_t)tl.idx * S * K;
-      }
-#pragma unroll
-      for (int e = 0; e < 8; ++e) v[e] = k < K ? __ldg(X + (size_t)(sg + e) * K + k) : 0.f;
-    });
-  }
-  GPF_DEV static void fetch_b(const Params& p, const Tile& tl, int kc, int ptid, float* frag) {
     const int S = p.S;
 #pragma unroll
-    for (int it = 0; it < NT * 8 / kGroupThreads; ++it) {
+    for (int it = 0; it < MT * 8 / kGroupThreads; ++it) {
       const int idx = ptid + it * kGroupThreads;
       const int q = idx >> 3, c = idx & 7;
-      int sg = (tl.chunk0 + kc) * KC + c * 4;
+      const int sg = (tl.chunk0 + kc) * KC + c * 4;
       float4 o = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (tl.fam == 0) {
-        if (q < tl.cnt) {
-          const int i = tl.idx;
-          if (sg < S) {
+      if (q < tl.cnt) {
+        if (tl.fam == 0) {
+          const int prow = tl.idx * MT + q, i = prow / p.nb, n = prow - i * p.nb;
+          if (n <= i) {
             const float4 qb = __ldg(reinterpret_cast<const float4*>(p.Qb + (size_t)i * S + sg));
-            const float4 sx = __ldg(reinterpret_cast<const float4*>(p.SX + (size_t)q * S + sg));
+            const float4 sx = __ldg(reinterpret_cast<const float4*>(p.SX + (size_t)n * S + sg));
             const float4 xx = __ldg(reinterpret_cast<const float4*>(p.x + (size_t)i * S + sg));
-            const float4 sq = __ldg(reinterpret_cast<const float4*>(p.SQ + (size_t)q * S + sg));
+            const float4 sq = __ldg(reinterpret_cast<const float4*>(p.SQ + (size_t)n * S + sg));
             o.x = 2.f * (qb.x * sx.x - xx.x * sq.x); o.y = 2.f * (qb.y * sx.y - xx.y * sq.y);
             o.z = 2.f * (qb.z * sx.z - xx.z * sq.z); o.w = 2.f * (qb.w * sx.w - xx.w * sq.w);
-          } else {
-            sg -= S;
-            const float4 sv = __ldg(reinterpret_cast<const float4*>(p.sj + (size_t)i * S + sg));
-            const float4 sq = __ldg(reinterpret_cast<const float4*>(p.SQ + (size_t)q * S + sg));
-            o.x = -sv.x * sq.x; o.y = -sv.y * sq.y; o.z = -sv.z * sq.z; o.w = -sv.w * sq.w;
           }
+        } else if (tl.fam == 1) {
+          const float4 sv = __ldg(reinterpret_cast<const float4*>(p.sj + (size_t)tl.idx * S + sg));
+          const float4 sq = __ldg(reinterpret_cast<const float4*>(p.SQ + (size_t)q * S + sg));
+          o.x = -sv.x * sq.x; o.y = -sv.y * sq.y; o.z = -sv.z * sq.z; o.w = -sv.w * sq.w;
+        } else {
+          o = __ldg(reinterpret_cast<const float4*>(p.Qb + (size_t)(tl.idx + q) * S + sg));
         }
-      } else if (tl.idx + q < p.d && q < tl.cnt) {
-        o = __ldg(reinterpret_cast<const float4*>(p.Qb + (size_t)(tl.idx + q) * S + sg));
       }
       frag[4 * it] = o.x; frag[4 * it + 1] = o.y; frag[4 * it + 2] = o.z; frag[4 * it + 3] = o.w;
     }
   }
-  GPF_DEV static void epilogue(const Params& p, const Tile& tl, const EpiCtx&, int row, int c0, int nc, float (&v)[32]) {
-    const int k = tl.km * MT + row;
-    if (k >= p.K) return;
+  GPF_DEV static void fetch_b(const Params& p, const Tile& tl, int kc, int ptid, float* frag) {
+    const int S = p.S, K = p.K;
+    const float* X = tl.fam == 0 ? p.TL + (size_t)p.d * S * K : (tl.fam == 1 ? p.TL + (size_t)tl.idx * S * K : p.R + (size_t)tl.idx * S * K);
+    fetch_units<NT>(frag, ptid, [&](int k, int kq, float (&v)[8]) {
+      const size_t s0 = (size_t)(tl.chunk0 + kc) * KC + kq * 8;
 #pragma unroll
-    for (int i = 0; i < 32; ++i) {
-      const int q = c0 + i;
-      if (i < nc && q < tl.cnt) {
-        const int prow = tl.fam == 0 ? tl.idx * p.nb + q : (tl.idx + q) * p.nb + tl.idx;
-        atomicAdd(p.gW3 + ((size_t)tl.sp * p.nout + prow) * p.K + k, v[i]);
-      }
-    }
+      for (int e = 0; e < 8; ++e) v[e] = k < K ? __ldg(X + (s0 + e) * K + k) : 0.f;
+    });
+  }
+  GPF_DEV static void epilogue(const Params& p, const Tile& tl, const EpiCtx& ctx, int, int c0, int nc, float (&v)[32]) {
+    float* base = p.gW3 + (size_t)tl.sp * p.nout * p.K;
+    ctx.store_rows(v, nc, c0, [&p, &tl, base](int q) -> float* {
+      if (q >= tl.cnt) return nullptr;
+      const int prow = tl.fam == 0 ? tl.idx * MT + q : (tl.fam == 1 ? tl.idx * p.nb + q : (tl.idx + q) * p.nb + tl.idx);
+      return base + (size_t)prow * p.K; }, true);
   }
 };
 
@@ -496,11 +475,12 @@ inline void tc_carve(const TcDims& g, int n_steps, bool train, int sm_count, TcB
       b.gWp[l] = take((size_t)b.wsplit_G[l] * MT * g.Hp[l - 1]);
       b.gb[l] = take(g.Hp[l]);
     }
-    {   // last-layer weight gradient: split-K partials when there are fewer output tiles than SMs
-      const int n_out = (d + g.nb) * ((HL + MT - 1) / MT);
-      b.w3_nsplit = sm_count / n_out < 1 ? 1 : sm_count / n_out;
-      const int nseg = 2 * S / (KC * TC_SEG);
+    {   // last-layer weight gradient: (output tile, K split) work items, one partial per split
+      const int n_out = (g.nout + MT - 1) / MT + d + g.nb;
+      const int nseg = S / (KC * TC_SEG);
+      b.w3_nsplit = 2 * n_out > sm_count ? 8 : sm_count / n_out;   // many tiles: 8 splits even out the rounds
       if (b.w3_nsplit > nseg) b.w3_nsplit = nseg;
+      if (b.w3_nsplit < 1) b.w3_nsplit = 1;
     }
     b.gW3 = take((size_t)b.w3_nsplit * g.nout * HL);
     b.gb3 = take(g.nout);
@@ -611,22 +591,22 @@ int tc_run(const GpFlowDesc* d, int op, const float* params, const float* x_in, 
     tc_prep_last_kernel<<<(g.nout * HL + 255) / 256, 256, 0, st>>>(g, params, w);
     TC_KCK();
   }
-  CUtensorMap mapW[TC_MAXL + 1], mapWT[TC_MAXL + 1], map3, map3F, mapG, mapT, mapGT, mapJT;
+  CUtensorMap mapW[TC_MAXL + 1], mapWT[TC_MAXL + 1], map3A, map3F, mapGA, mapT, mapGT, mapJT;
   for (int l = 2; l <= L; ++l) {
     if (!make_tmap_2d(&mapW[l], w.Ws[l], (uint64_t)2 * b.npad[l], g.Hp[l - 1], g.Hp[l - 1], HT)) return GPFLOW_ERR_CUDA;
     if (!make_tmap_2d(&mapWT[l], w.WTs[l], (uint64_t)2 * b.npadT[l], g.Hp[l], g.Hp[l], HT)) return GPFLOW_ERR_CUDA;
   }
-  if (!make_tmap_2d(&map3, w.W3s, (uint64_t)2 * g.rows3, HL, HL, 64)) return GPFLOW_ERR_CUDA;
+  if (!make_tmap_2d(&map3A, w.W3s, (uint64_t)2 * g.rows3, HL, HL, MT)) return GPFLOW_ERR_CUDA;
   if (!make_tmap_2d(&map3F, w.W3s, (uint64_t)2 * g.rows3, HL, HL, HT)) return GPFLOW_ERR_CUDA;
-  if (!make_tmap_2d(&mapG, w.W3Gs, (uint64_t)2 * g.rowsG, HL, HL, 64)) return GPFLOW_ERR_CUDA;
+  if (!make_tmap_2d(&mapGA, w.W3Gs, (uint64_t)2 * g.rowsG, HL, HL, MT)) return GPFLOW_ERR_CUDA;
   if (!make_tmap_2d(&mapT, w.W3Ts, (uint64_t)2 * g.HTp, g.ldT, g.ldT, HT)) return GPFLOW_ERR_CUDA;
   if (!make_tmap_2d(&mapGT, w.W3GTs, (uint64_t)nb * 2 * g.HTp, g.dpad, g.dpad, HT)) return GPFLOW_ERR_CUDA;
   if (!make_tmap_2d(&mapJT, w.W3JTs, (uint64_t)dd * 2 * g.HTp, g.nbpad, g.nbpad, HT)) return GPFLOW_ERR_CUDA;
 
   using LayerOp = OpLayer<HT, ST>;
-  using LastOp = OpLast<4>;
+  using LastOp = OpLast<2>;
   using LBOp = OpLB<HT, ST>;
-  using W3Op = OpW3<4>;
+  using W3Op = OpW3<HT, ST>;
   using WOp = OpW<HT, ST>;
   const int mt = S / MT;
   const int eb = 256;   // block of the element-wise kernels
@@ -658,10 +638,10 @@ int tc_run(const GpFlowDesc* d, int op, const float* params, const float* x_in, 
     }
     {
       typename LastOp::Params p;
-      p.map3 = map3; p.mapG = mapG;
-      p.TL = P(b.T[L]); p.R = P(b.R); p.b3 = w.b3; p.F = P(b.F); p.G = P(b.G); p.D = P(b.D);
-      p.d = dd; p.nb = nb; p.S = S; p.K = HL; p.mt = mt; p.lo3 = g.rows3; p.loG = g.rowsG;
-      TC_CK(launch_gemm<LastOp>(p, (dd + nb) * mt, sm_count, st));
+      p.map3 = map3A; p.mapG = mapGA;
+      p.TL = P(b.T[L]); p.R = P(b.R); p.G = P(b.G); p.D = P(b.D);
+      p.d = dd; p.nb = nb; p.S = S; p.K = HL; p.nt = S / 256; p.lo3 = g.rows3; p.loG = g.rowsG;
+      TC_CK(launch_gemm<LastOp>(p, (dd + nb) * p.nt, sm_count, st));
     }
     tc_vel1_kernel<<<g_nS, eb, 0, st>>>(g, xpt, P(b.sj), P(b.F), P(b.D), P(b.SX), P(b.FX), P(b.SD));
     TC_KCK();
@@ -693,13 +673,16 @@ int tc_run(const GpFlowDesc* d, int op, const float* params, const float* x_in, 
       typename W3Op::Params p;
       p.TL = P(b.T[L]); p.R = P(b.R); p.Qb = P(b.Qb); p.SX = P(b.SX); p.SQ = P(b.SQ); p.x = xpt; p.sj = P(b.sj);
       p.gW3 = P(b.gW3);
-      p.d = dd; p.nb = nb; p.S = S; p.K = HL; p.mtk = (HL + MT - 1) / MT; p.nseg = 2 * S / (KC * TC_SEG);
-      p.n_out = (dd + nb) * p.mtk;
-      p.nout = g.nout;
+      p.d = dd; p.nb = nb; p.nout = g.nout; p.S = S; p.K = HL;
+      p.nF = (g.nout + MT - 1) / MT;
+      p.n_out = p.nF + dd + nb;
+      p.nseg = S / (KC * TC_SEG);
       p.nsplit = b.w3_nsplit;
-      if (p.nsplit > 1) { p.G = p.n_out * p.nsplit; p.rounds = (p.nseg + p.nsplit - 1) / p.nsplit; }
-      else { p.G = p.n_out < sm_count ? p.n_out : sm_count; p.rounds = (p.n_out + p.G - 1) / p.G * p.nseg; }
-      // the grid must be exactly G so that every output tile stays with one CTA
+      p.items = p.n_out * p.nsplit;
+      p.G = p.items < sm_count ? p.items : sm_count;
+      p.segs_per_item = (p.nseg + p.nsplit - 1) / p.nsplit;
+      p.rounds = (p.items + p.G - 1) / p.G * p.segs_per_item;
+      // the grid must be exactly G so that every work item stays with one CTA
       using SMW = GemmSmem<W3Op>;
       static bool attr = false;
       if (!attr) { TC_CK(cudaFuncSetAttribute(tc_gemm_kernel<W3Op>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMW::kBytes)); attr = true; }

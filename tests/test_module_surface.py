@@ -209,3 +209,52 @@ def test_velocity_is_divergence_free(nb):
     xw = x.clone()
     xw[:, 2] = float(np.sqrt(flow.v.bound))
     assert float(flow.v(xw, t)[:, 2].abs().max()) < 1e-12 * max(vmag, 1.0)
+
+
+def test_compute_ot_costs_matches_reference_report():
+    """`compute_ot_costs` (src/plots/outputs.py:7-248) on the pretrained C1 map (BNAF mirror) + a seeded GP flow: the numbers
+    of the report the unmodified reference printed (tests/golden/ot_costs_c1_f32.npz, oracle/make_golden_ot_costs.py) --
+    NLL of the map and of the OT map, both OT costs, the Lagrangian on the 100 x 100 mesh -- and the report text itself."""
+    import gpflow_b200 as G
+    from gpflow_b200.ot_costs import compute_ot_costs
+    z = np.load(os.path.join(GOLDEN_DIR, "ot_costs_c1_f32.npz"))
+    b = np.load(os.path.join(GOLDEN_DIR, "bnaf_eight_gaussians_f32.npz"))
+    bmap = G.BNAFMap(int(b["dim"]), int(b["n_neurons"]), int(b["n_layers"]), torch.from_numpy(b["params"])).cuda()
+    flow = G.get_gp_flow(2, {"nb_neurons": [15, 15]}, 15).cuda()
+    flat, off = torch.from_numpy(z["flow_params"]), 0
+    with torch.no_grad():
+        for p in flow.parameters():
+            p.copy_(flat[off:off + p.numel()].view_as(p)); off += p.numel()
+    net = G.GPFlowNetwork(flow, map_module=bmap)
+    x_test = torch.from_numpy(z["x_test"]).cuda()
+    res, text = compute_ot_costs(net, x_test, batch_size=1024)
+    for k in ("nll_map", "cost_map", "nll_ot", "cost_gp_map", "lagrangian"):
+        assert abs(res[k] - float(z[k])) < 2e-5 * abs(float(z[k])), (k, res[k], float(z[k]))
+    # Gaussian-preserving: the OT map has the same likelihood as the map it composes with (to fp32 accuracy)
+    assert abs(res["nll_ot"] - res["nll_map"]) < 1e-4
+    assert text.strip() == str(z["report"]).strip()
+    y_ot, ld = net.ot_map(x_test, return_log_det=True)
+    assert rel(y_ot.cpu(), z["y_ot"]) < 1e-5 and rel(ld.cpu(), z["log_det_ot"]) < 1e-4
+
+
+def test_compute_ot_costs_inverse_consistency_with_ffjord_map():
+    """The block the reference runs when the map has a `backward` (outputs.py:101-137): finv_f errors and backward OT
+    costs, here with the FFJORD mirror of the pretrained dsprites map (d = 10: Lagrangian on uniform cube samples)."""
+    import gpflow_b200 as G
+    from gpflow_b200.ot_costs import compute_ot_costs
+    z = np.load(os.path.join(GOLDEN_DIR, "ffjord_dsprites_f32.npz"))
+    m = G.FFJORDMap(int(z["d"]), [int(h) for h in z["hidden"]], int(z["n_blocks"]), torch.from_numpy(z["params"]),
+                    [float(t) for t in z["t_end"]], 64).cuda()
+    torch.manual_seed(3)
+    flow = G.get_gp_flow(10, {"nb_neurons": [50, 50, 50], "nb_div_blocks": 9}, 15).cuda()
+    with torch.no_grad():
+        for p in flow.parameters():
+            p.normal_(0.0, 0.03)
+    net = G.GPFlowNetwork(flow, map_module=m)
+    x_gauss = torch.randn(600, 10, generator=torch.Generator().manual_seed(4)).cuda()
+    x_test = m.backward(torch.randn(600, 10, generator=torch.Generator().manual_seed(5)).cuda())
+    res, text = compute_ot_costs(net, x_test, batch_size=256, x_gauss=x_gauss)
+    assert res["finv_f_err"] < 1e-4 and res["finv_f_gp_err"] < 2e-3        # RK4 round trips (64 / 15 steps)
+    assert res["cost_back"] > 0 and res["cost_gp_back"] > 0 and res["lagrangian"] > 0
+    assert abs(res["nll_ot"] - res["nll_map"]) < 5e-3
+    assert "finv_f error GP map" in text and "OT cost GP backward random data" in text
