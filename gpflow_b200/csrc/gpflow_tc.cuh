@@ -152,7 +152,8 @@ __global__ void tc_prep_last_kernel(TcDims g, const float* __restrict__ p, TcWei
 // T1[j] = sp (.) W1x[:, j] (U_1 = W1x is the same for every sample), s_j = x_j^2 - (1 - eps).  Block = 8 samples x Hp1 units.
 __global__ void tc_layer1_kernel(TcDims g, const float* __restrict__ W1T, const float* __restrict__ b1,
                                  const float* __restrict__ x /*CL [d][S]*/, float t, float bnd, float* __restrict__ T1 /*[(d+1) S][Hp1]*/,
-                                 float* __restrict__ sp1 /*[S][Hp1]*/, float* __restrict__ sj /*CL [d][S]*/) {
+                                 float* __restrict__ sp1 /*[S][Hp1]*/, float* __restrict__ sj /*CL [d][S]*/,
+                                 int write_tangents /* 0: the consumers regenerate T1[j] = sp1 (.) W1x[:, j] on the fly */) {
   __shared__ float xs[TC_DMAX][TC_L1_SPB];
   const int H = g.Hp[1], d = g.d, S = g.S;
   const int s0 = blockIdx.x * TC_L1_SPB, k = threadIdx.x;
@@ -177,9 +178,11 @@ __global__ void tc_layer1_kernel(TcDims g, const float* __restrict__ W1T, const 
     const float sp = 1.f - h * h;
     sp1[(size_t)s * H + k] = sp;
     T1[((size_t)d * S + s) * H + k] = h;
+    if (write_tangents) {
 #pragma unroll
-    for (int j = 0; j < TC_DMAX; ++j)
-      if (j < d) T1[((size_t)j * S + s) * H + k] = sp * w[j];
+      for (int j = 0; j < TC_DMAX; ++j)
+        if (j < d) T1[((size_t)j * S + s) * H + k] = sp * w[j];
+    }
   }
 }
 

@@ -29,6 +29,8 @@ struct OpLayer {
     const float* bias;
     long long M;
     int K, N, lo_row, mode, S, ntn;   // ntn: number of N tiles (1 for the hidden layers)
+    const float* gen_sp;              // non-null (layer 2 tangent rows): A is not read but generated on the fly,
+    const float* gen_w;               //   A[(j, s)][k] = gen_sp[s][k] * gen_w[j][k]   (T_1[j] = sp_1 (.) W1x[:, j])
   };
   struct Tile { int nk, n, n0; long long m0; };
   GPF_DEV static int num_tiles(const Params& p) { return (int)((p.M + MT - 1) / MT) * p.ntn; }
@@ -44,6 +46,18 @@ struct OpLayer {
     c0 = kc * KC; r_hi = tl.n0; r_lo = p.lo_row + tl.n0;
   }
   GPF_DEV static void fetch_a(const Params& p, const Tile& tl, int kc, int ptid, float* frag) {
+    if (p.gen_sp != nullptr) {   // a tile never straddles two tangent directions (S is a multiple of 128)
+      const int j = (int)(tl.m0 / p.S), s0 = (int)(tl.m0 % p.S);
+#pragma unroll
+      for (int it = 0; it < MT * 8 / kGroupThreads; ++it) {
+        const int q = ptid + it * kGroupThreads;
+        const int r = q >> 3, c = q & 7;
+        const float4 a = __ldg(reinterpret_cast<const float4*>(p.gen_sp + (size_t)(s0 + r) * p.K + kc * KC + c * 4));
+        const float4 w = __ldg(reinterpret_cast<const float4*>(p.gen_w + (size_t)j * p.K + kc * KC + c * 4));
+        frag[4 * it] = a.x * w.x; frag[4 * it + 1] = a.y * w.y; frag[4 * it + 2] = a.z * w.z; frag[4 * it + 3] = a.w * w.w;
+      }
+      return;
+    }
     fetch_rows<MT>(frag, ptid, p.A, p.K, tl.m0, p.M, kc * KC, p.K - kc * KC);
   }
   GPF_DEV static void epilogue(const Params& p, const Tile& tl, const EpiCtx& ctx, int row, int c0, int nc, float (&v)[32]) {
@@ -245,7 +259,7 @@ struct OpW3 {
   struct Params {
     const float *TL, *R;
     const float *Qb, *SX, *SQ, *x, *sj;
-    float* gW3;        // [nsplit][nout][K] partial accumulators
+    float* gW3;        // [3 families][nsplit][nout][K] partial accumulators (the families write the same rows)
     int d, nb, nout, S, K, nF, n_out, nseg, nsplit, items, G, segs_per_item, rounds;
   };
   struct Tile { int nk, n, fam, idx, cnt, chunk0, sp; };
@@ -305,7 +319,7 @@ struct OpW3 {
     });
   }
   GPF_DEV static void epilogue(const Params& p, const Tile& tl, const EpiCtx& ctx, int, int c0, int nc, float (&v)[32]) {
-    float* base = p.gW3 + (size_t)tl.sp * p.nout * p.K;
+    float* base = p.gW3 + (size_t)(tl.fam * p.nsplit + tl.sp) * p.nout * p.K;
     ctx.store_rows(v, nc, c0, [&p, &tl, base](int q) -> float* {
       if (q >= tl.cnt) return nullptr;
       const int prow = tl.fam == 0 ? tl.idx * MT + q : (tl.fam == 1 ? tl.idx * p.nb + q : (tl.idx + q) * p.nb + tl.idx);
@@ -328,6 +342,9 @@ struct OpW {
     const float* Tm;   // [(d+1) S][Nl]
     float* gWp;        // [G][128][Nl]
     int Ml, Nl, nsplit, G, cps, nchunks, nseg;
+    const float* gen_sp;   // non-null (l = 2): the tangent rows of T_1 are generated, T_1[(j, s)][n] = gen_sp[s][n] * gen_w[j][n];
+    const float* gen_w;    //   only row block d of Tm (h_1) is read
+    int S, d;
   };
   struct Tile { int nk, n, km, b, chunk0; };
   GPF_DEV static int num_tiles(const Params& p) { return p.G * p.nseg; }
@@ -354,6 +371,13 @@ struct OpW {
   GPF_DEV static void fetch_b(const Params& p, const Tile& tl, int kc, int ptid, float* frag) {
     fetch_units<NT>(frag, ptid, [&](int n, int kq, float (&v)[8]) {
       const size_t r0 = (size_t)(tl.chunk0 + kc) * KC + kq * 8;
+      if (p.gen_sp != nullptr && r0 < (size_t)p.d * p.S) {   // 8 consecutive rows share their tangent direction (S % 8 == 0)
+        const int j = (int)(r0 / p.S), s0 = (int)(r0 % p.S);
+        const float w = n < p.Nl ? __ldg(p.gen_w + (size_t)j * p.Nl + n) : 0.f;
+#pragma unroll
+        for (int e = 0; e < 8; ++e) v[e] = n < p.Nl ? w * __ldg(p.gen_sp + (size_t)(s0 + e) * p.Nl + n) : 0.f;
+        return;
+      }
 #pragma unroll
       for (int e = 0; e < 8; ++e) v[e] = n < p.Nl ? __ldg(p.Tm + (r0 + e) * p.Nl + n) : 0.f;
     });
@@ -478,11 +502,11 @@ inline void tc_carve(const TcDims& g, int n_steps, bool train, int sm_count, TcB
     {   // last-layer weight gradient: (output tile, K split) work items, one partial per split
       const int n_out = (g.nout + MT - 1) / MT + d + g.nb;
       const int nseg = S / (KC * TC_SEG);
-      b.w3_nsplit = 2 * n_out > sm_count ? 8 : sm_count / n_out;   // many tiles: 8 splits even out the rounds
+      b.w3_nsplit = 2 * n_out > sm_count ? 4 : sm_count / n_out;   // many tiles: 4 splits even out the rounds
       if (b.w3_nsplit > nseg) b.w3_nsplit = nseg;
       if (b.w3_nsplit < 1) b.w3_nsplit = 1;
     }
-    b.gW3 = take((size_t)b.w3_nsplit * g.nout * HL);
+    b.gW3 = take((size_t)3 * b.w3_nsplit * g.nout * HL);
     b.gb3 = take(g.nout);
   }
   b.scal = take(4);
@@ -603,6 +627,9 @@ int tc_run(const GpFlowDesc* d, int op, const float* params, const float* x_in, 
   if (!make_tmap_2d(&mapGT, w.W3GTs, (uint64_t)nb * 2 * g.HTp, g.dpad, g.dpad, HT)) return GPFLOW_ERR_CUDA;
   if (!make_tmap_2d(&mapJT, w.W3JTs, (uint64_t)dd * 2 * g.HTp, g.nbpad, g.nbpad, HT)) return GPFLOW_ERR_CUDA;
 
+  // GPFLOW_TC_GEN_T1=1: regenerate T_1[j] = sp_1 (.) W1x[:, j] inside the GEMM producers instead of materialising it.
+  // Measured at C5 (2^14 samples): 990 ms per step against 948 ms with the materialised rows -- off by default.
+  static const bool gen_t1 = [] { const char* e = getenv("GPFLOW_TC_GEN_T1"); return e != nullptr && e[0] == '1'; }();
   using LayerOp = OpLayer<HT, ST>;
   using LastOp = OpLast<2>;
   using LBOp = OpLB<HT, ST>;
@@ -614,16 +641,18 @@ int tc_run(const GpFlowDesc* d, int op, const float* params, const float* x_in, 
 
   // ---- one velocity evaluation, forward: activations of the slab at the stage point xpt, time t (up to SX / FX / SD) ----
   auto eval_forward = [&](const float* xpt, float t) -> int {
-    tc_layer1_kernel<<<S / TC_L1_SPB, g.Hp[1], 0, st>>>(g, w.W1T, w.bp[1], xpt, t, bnd, P(b.T[1]), P(b.sp[1]), P(b.sj));
+    tc_layer1_kernel<<<S / TC_L1_SPB, g.Hp[1], 0, st>>>(g, w.W1T, w.bp[1], xpt, t, bnd, P(b.T[1]), P(b.sp[1]), P(b.sj), (L == 1 || !gen_t1) ? 1 : 0);
     TC_KCK();
     for (int l = 2; l <= L; ++l) {
       typename LayerOp::Params p;
       p.map = mapW[l];
       p.K = g.Hp[l - 1]; p.N = g.Hp[l]; p.lo_row = b.npad[l]; p.S = S; p.ntn = 1;
       p.bias = w.bp[l]; p.aux = P(b.sp[l]); p.out2 = P(b.sp[l]);
+      p.gen_sp = nullptr; p.gen_w = nullptr;
       p.A = P(b.T[l - 1]) + (size_t)dd * S * p.K; p.M = S; p.mode = 0; p.out = P(b.T[l]) + (size_t)dd * S * p.N;
       TC_CK(launch_gemm<LayerOp>(p, mt, sm_count, st));
       p.A = P(b.T[l - 1]); p.M = (long long)dd * S; p.mode = 1; p.out = P(b.T[l]);
+      if (l == 2 && gen_t1) { p.gen_sp = P(b.sp[1]); p.gen_w = w.W1T; }   // T_1 is not materialised
       TC_CK(launch_gemm<LayerOp>(p, dd * mt, sm_count, st));
     }
     tc_rsum_kernel<<<S, HL, 0, st>>>(g, P(b.T[L]), P(b.sj), P(b.R));
@@ -632,7 +661,7 @@ int tc_run(const GpFlowDesc* d, int op, const float* params, const float* x_in, 
       typename LayerOp::Params p;
       p.map = map3F;
       p.K = HL; p.N = g.nout; p.lo_row = g.rows3; p.S = S; p.ntn = (g.nout + HT - 1) / HT;
-      p.bias = w.b3; p.aux = nullptr; p.out2 = nullptr;
+      p.bias = w.b3; p.aux = nullptr; p.out2 = nullptr; p.gen_sp = nullptr; p.gen_w = nullptr;
       p.A = P(b.T[L]) + (size_t)dd * S * HL; p.M = S; p.mode = 3; p.out = P(b.F);
       TC_CK(launch_gemm<LayerOp>(p, mt * p.ntn, sm_count, st));
     }
@@ -700,6 +729,7 @@ int tc_run(const GpFlowDesc* d, int op, const float* params, const float* x_in, 
       {
         typename WOp::Params p;
         p.Ub = P(b.Ub[l]); p.Tm = P(b.T[l - 1]); p.gWp = P(b.gWp[l]);
+        p.gen_sp = (l == 2 && gen_t1) ? P(b.sp[1]) : nullptr; p.gen_w = w.W1T; p.S = S; p.d = dd;
         p.Ml = g.Hp[l]; p.Nl = g.Hp[l - 1];
         const int mtl = (p.Ml + MT - 1) / MT;
         p.nchunks = (dd + 1) * S / KC;
@@ -724,7 +754,7 @@ int tc_run(const GpFlowDesc* d, int op, const float* params, const float* x_in, 
         typename LayerOp::Params p;
         p.map = mapWT[l];
         p.K = g.Hp[l]; p.N = g.Hp[l - 1]; p.lo_row = b.npadT[l]; p.S = S; p.ntn = 1;
-        p.bias = nullptr; p.aux = nullptr; p.out2 = nullptr;
+        p.bias = nullptr; p.aux = nullptr; p.out2 = nullptr; p.gen_sp = nullptr; p.gen_w = nullptr;
         p.A = P(b.Ub[l]); p.M = (long long)(dd + 1) * S; p.mode = 2; p.out = P(b.Ub[l - 1]);
         TC_CK(launch_gemm<LayerOp>(p, (dd + 1) * mt, sm_count, st));
       }
@@ -820,7 +850,7 @@ int tc_run(const GpFlowDesc* d, int op, const float* params, const float* x_in, 
     if (train)
     {
       for (int l = 2; l <= L; ++l) { tabs.gWp[l] = P(b.gWp[l]); tabs.gb[l] = P(b.gb[l]); tabs.ns[l] = wsplit_ns[l]; }
-      tabs.ns3 = b.w3_nsplit;
+      tabs.ns3 = 3 * b.w3_nsplit;
     }
     const int count = (train && grads_out != nullptr) ? g.P : 3;
     tc_finalize_kernel<<<(count + 255) / 256, 256, 0, st>>>(

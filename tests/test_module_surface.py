@@ -233,7 +233,8 @@ def test_compute_ot_costs_matches_reference_report():
     # Gaussian-preserving: the OT map has the same likelihood as the map it composes with (to fp32 accuracy)
     assert abs(res["nll_ot"] - res["nll_map"]) < 1e-4
     assert text.strip() == str(z["report"]).strip()
-    y_ot, ld = net.ot_map(x_test, return_log_det=True)
+    with torch.no_grad():
+        y_ot, ld = net.ot_map(x_test, return_log_det=True)
     assert rel(y_ot.cpu(), z["y_ot"]) < 1e-5 and rel(ld.cpu(), z["log_det_ot"]) < 1e-4
 
 
