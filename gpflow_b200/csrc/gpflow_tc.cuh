@@ -203,15 +203,20 @@ __global__ void tc_vel1_kernel(TcDims g, const float* __restrict__ x, const floa
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= g.nb * S) return;
   const int n = idx / S, s = idx % S;
-  float sx = 0.f, fx = 0.f, sd = 0.f;
+  // the loads of several j are independent: 4 partial sums keep them in flight (the sums are short: <= d terms)
+  float sx[4] = {0.f, 0.f, 0.f, 0.f}, fx[4] = {0.f, 0.f, 0.f, 0.f}, sd[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll 4
   for (int j = n; j < g.d; ++j) {
+    const int a = (j - n) & 3;
     const float xj = x[(size_t)j * S + s];
     const size_t p = (size_t)(j * g.nb + n) * S + s;
-    sx += xj;
-    fx = fmaf(F[p], xj, fx);
-    sd = fmaf(sj[(size_t)j * S + s], D[p], sd);
+    sx[a] += xj;
+    fx[a] = fmaf(F[p], xj, fx[a]);
+    sd[a] = fmaf(sj[(size_t)j * S + s], D[p], sd[a]);
   }
-  SX[idx] = sx; FX[idx] = fx; SD[idx] = sd;
+  SX[idx] = (sx[0] + sx[1]) + (sx[2] + sx[3]);
+  FX[idx] = (fx[0] + fx[1]) + (fx[2] + fx[3]);
+  SD[idx] = (sd[0] + sd[1]) + (sd[2] + sd[3]);
 }
 // part 2: Q_i = sum_{n <= min(i, nb-1)} [2 f_(i,n) SX_n - 2 FX_n + g_(i,n) - SD_n], v_i = s_i Q_i, followed by the RK4
 // bookkeeping of the stage (ode_order_method.py:66-71).  Thread = (i, s).
@@ -226,12 +231,14 @@ __global__ void tc_vel2_kernel(TcDims g, const float* __restrict__ sj, const flo
   if (idx >= g.d * S) return;
   const int i = idx / S, s = idx % S;
   const int nmax = i < g.nb - 1 ? i : g.nb - 1;
-  float q = 0.f;
+  float qa[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll 4
   for (int n = 0; n <= nmax; ++n) {
     const size_t p = (size_t)(i * g.nb + n) * S + s;
     const size_t ns = (size_t)n * S + s;
-    q += 2.f * F[p] * SX[ns] - 2.f * FX[ns] + G[p] - SD[ns];
+    qa[n & 3] += 2.f * F[p] * SX[ns] - 2.f * FX[ns] + G[p] - SD[ns];
   }
+  const float q = (qa[0] + qa[1]) + (qa[2] + qa[3]);
   const float vi = sj[idx] * q;
   Q[idx] = q;
   v[idx] = vi;
@@ -262,13 +269,16 @@ __global__ void tc_vb1_kernel(TcDims g, const float* __restrict__ Qb, const floa
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= g.nb * S) return;
   const int n = idx / S, s = idx % S;
-  float sq = 0.f, sxb = 0.f;
+  float sq[4] = {0.f, 0.f, 0.f, 0.f}, sxb[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll 4
   for (int i = n; i < g.d; ++i) {
+    const int a = (i - n) & 3;
     const float qb = Qb[(size_t)i * S + s];
-    sq += qb;
-    sxb = fmaf(2.f * F[(size_t)(i * g.nb + n) * S + s], qb, sxb);
+    sq[a] += qb;
+    sxb[a] = fmaf(2.f * F[(size_t)(i * g.nb + n) * S + s], qb, sxb[a]);
   }
-  SQ[idx] = sq; SXb[idx] = sxb;
+  SQ[idx] = (sq[0] + sq[1]) + (sq[2] + sq[3]);
+  SXb[idx] = (sxb[0] + sxb[1]) + (sxb[2] + sxb[3]);
 }
 // xbar_j (first part) = sum_{n <= min(j, nb-1)} [SXb_n - 2 SQ_n f_(j,n)] + 2 x_j (vbar_j Q_j - sum_n SQ_n D_(j,n));
 // the CR . T_L[j] term of sb_j and the first-layer term are added by tc_tb_last_kernel / tc_layer1_bwd_kernel.
@@ -280,15 +290,16 @@ __global__ void tc_vb2_kernel(TcDims g, const float* __restrict__ x, const float
   if (idx >= g.d * S) return;
   const int j = idx / S, s = idx % S;
   const int nmax = j < g.nb - 1 ? j : g.nb - 1;
-  float xb = 0.f, sd = 0.f;
+  float xb[4] = {0.f, 0.f, 0.f, 0.f}, sd[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll 4
   for (int n = 0; n <= nmax; ++n) {
     const size_t p = (size_t)(j * g.nb + n) * S + s;
     const float sq = SQ[(size_t)n * S + s];
-    xb += SXb[(size_t)n * S + s] - 2.f * sq * F[p];
-    sd = fmaf(sq, D[p], sd);
+    xb[n & 3] += SXb[(size_t)n * S + s] - 2.f * sq * F[p];
+    sd[n & 3] = fmaf(sq, D[p], sd[n & 3]);
   }
-  const float sb = vbar[idx] * Q[idx] - sd;
-  ybar[idx] = fmaf(2.f * x[idx], sb, xb);
+  const float sb = vbar[idx] * Q[idx] - ((sd[0] + sd[1]) + (sd[2] + sd[3]));
+  ybar[idx] = fmaf(2.f * x[idx], sb, (xb[0] + xb[1]) + (xb[2] + xb[3]));
 }
 // last hidden layer, reverse: Tb_L[j] = s_j CR_{min(j, nb-1)} + TbD[j] (TbD already carries -s_j sum_n SQ_n W[(j,n)]),
 // CR_n = sum_{n' <= n} Rb_n';  sb_j += CR . T_L[j];  Ub_L[j] = sp (.) Tb_L[j];

@@ -455,7 +455,12 @@ inline size_t tc_per_sample_floats(const TcDims& g, int n_steps, bool train) {
 inline int tc_slab_size(const GpFlowDesc* d, int64_t B, int op) {
   const TcDims g = tc_make_dims(d, 256);
   const size_t per = tc_per_sample_floats(g, d->n_steps, op != GPFLOW_OP_FORWARD) * 4;
-  long long smax = (long long)(((size_t)880 << 20) / per) / 256 * 256;
+  size_t budget_mb = 880;
+  if (const char* e = getenv("GPFLOW_TC_SLAB_MB")) {   // experiment knob: per-slab buffer budget
+    const long long v = atoll(e);
+    if (v >= 64 && v <= 65536) budget_mb = (size_t)v;
+  }
+  long long smax = (long long)((budget_mb << 20) / per) / 256 * 256;
   if (smax < 256) smax = 256;
   if (smax > 32768) smax = 32768;
   if (const char* e = getenv("GPFLOW_TC_SLAB")) {   // testing aid: force small slabs (multi-slab accumulation paths)
