@@ -23,8 +23,28 @@ def _deps():
     return d
 
 
+def source_hash():
+    """sha256 over the CUDA sources and the public header: ties a built library to the committed sources."""
+    import hashlib
+    h = hashlib.sha256()
+    for p in sorted(_deps()):
+        h.update(os.path.basename(p).encode())
+        h.update(open(p, "rb").read())
+    return h.hexdigest()
+
+
+HASH_FILE = os.path.join(LIBDIR, "libgpflow_b200.sources.sha256")
+
+
+def built_hash():
+    try:
+        return open(HASH_FILE).read().strip()
+    except OSError:
+        return None
+
+
 def up_to_date():
-    if not os.path.exists(LIB):
+    if not os.path.exists(LIB) or built_hash() != source_hash():
         return False
     t = os.path.getmtime(LIB)
     return all(os.path.getmtime(p) <= t for p in _deps())
@@ -60,6 +80,8 @@ def build(force=False, verbose=False):
                        capture_output=True, text=True)
     if r.returncode != 0:
         raise RuntimeError("link failed:\n" + r.stderr[-4000:])
+    with open(HASH_FILE, "w") as f:
+        f.write(source_hash() + "\n")
     return LIB
 
 
