@@ -8,7 +8,10 @@ Workload (BASELINE.json configs[3], SURVEY.md 8d "C4"): synthetic 2-D Gaussian-n
 2^24 samples sharded over the ranks (strong scaling), d=2, nb_div_blocks=1, velocity MLP [15,15], 15 RK4 steps,
 fp32.  One step = fused forward + OT cost + backward (one CUDA launch + deterministic finalize) -> ONE all-reduce of
 the [grads | scalars] buffer (N > 1) -> fused Adam update (gpflow_adam_step) of the flat parameter buffer.
-Prints ONE JSON line (see the repo's task contract for the keys).
+Prints ONE JSON line (see the repo's task contract for the keys).  The default run appends `rows` to that line: the other
+BASELINE.json configurations -- C5 (d=64, nb=63, H=[256,256]) at 2^14 samples PER GPU and C3 (d=10, nb=9, H=[50,50,50]) on
+the chunked tcgen05 path (weak scaling), C4 with the Euler penalization -- each with its own roofline / clocks / e2e, and
+`peaks`: the roofline denominators measured once, before any warm-up (FFMA burn + SM clock, torch.matmul TF32 8192^3).
 """
 import argparse
 import json
