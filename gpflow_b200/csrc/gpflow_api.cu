@@ -473,6 +473,9 @@ const char* gpflow_error_string(int status) {
     case GPFLOW_ERR_WORKSPACE: return "workspace too small (see gpflow_query_workspace)";
     case GPFLOW_ERR_MISALIGNED: return "buffer not aligned";
     case GPFLOW_ERR_CUDA: return "CUDA launch failed";
+    case GPFLOW_ERR_STATIC_SCRATCH:
+      return "gpflow_velocity_static: batch / shape needs more than GPFLOW_STATIC_SCRATCH_BYTES of scratch "
+             "(use gpflow_velocity with a caller-provided workspace)";
     default: return "unknown status";
   }
 }

@@ -21,6 +21,23 @@ def velocity(vf, x: torch.Tensor, t, force_tc=False) -> torch.Tensor:
     return out
 
 
+def velocity_static(cfg, flat_params: torch.Tensor, x: torch.Tensor, t, out: torch.Tensor) -> torch.Tensor:
+    """`gpflow_velocity_static` (include/gpflow_b200.h; no counterpart in the reference): v(x, t) into the caller's `out`
+    with the library's built-in 32 MiB scratch instead of a workspace -- this wrapper and the call allocate nothing
+    (all tensors must already be contiguous CUDA tensors of one dtype).  Calls that overlap on the GPU race on the scratch.
+    Raises (GPFLOW_ERR_STATIC_SCRATCH) when the shape / batch needs more than the scratch holds."""
+    for name, ten in (("flat_params", flat_params), ("x", x), ("out", out)):
+        if not ten.is_cuda or not ten.is_contiguous() or ten.dtype != x.dtype:
+            raise RuntimeError("gpflow_b200: `%s` must be a contiguous CUDA tensor of x's dtype" % name)
+    if out.shape != x.shape:
+        raise ValueError("gpflow_b200: `out` must have x's shape")
+    desc = ops.make_desc(cfg, x.dtype, force_generic=True)
+    with torch.cuda.device(x.device):
+        _lib.check(_lib.load().gpflow_velocity_static(ctypes.byref(desc), x.shape[0], ops._ptr(flat_params), ops._ptr(x),
+                                                     ctypes.c_double(float(t)), ops._ptr(out), ops._stream()))
+    return out
+
+
 def potentials(vfield, x):
     raise NotImplementedError(
         "gpflow_b200: VectorField.eval/.jacobian are evaluated inside the fused velocity kernels; a standalone "

@@ -39,7 +39,9 @@ typedef enum GpFlowStatus {
   GPFLOW_ERR_NULL_POINTER = 3,   /* a required pointer is NULL                               */
   GPFLOW_ERR_WORKSPACE = 4,      /* workspace smaller than gpflow_query_workspace() reports  */
   GPFLOW_ERR_MISALIGNED = 5,     /* a buffer is not aligned to its element size              */
-  GPFLOW_ERR_CUDA = 6            /* cudaGetLastError() after a launch was not cudaSuccess    */
+  GPFLOW_ERR_CUDA = 6,           /* cudaGetLastError() after a launch was not cudaSuccess    */
+  GPFLOW_ERR_STATIC_SCRATCH = 7  /* gpflow_velocity_static(): the call needs more scratch than
+                                    GPFLOW_STATIC_SCRATCH_BYTES; use gpflow_velocity() with a workspace */
 } GpFlowStatus;
 
 typedef enum GpFlowDType { GPFLOW_F32 = 0, GPFLOW_F64 = 1 } GpFlowDType;
@@ -148,6 +150,24 @@ int gpflow_backward(const GpFlowDesc* desc, int64_t B, const void* params, const
  */
 int gpflow_velocity(const GpFlowDesc* desc, int64_t B, const void* params, const void* x, double t, void* v_out,
                     void* workspace, size_t workspace_bytes, void* cuda_stream);
+
+/*
+ * gpflow_velocity() for callers that cannot allocate or pass a workspace (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * Same inputs, outputs and results as gpflow_velocity() on the generic kernel family; the scratch is a
+ * file-scope device array of GPFLOW_STATIC_SCRATCH_BYTES inside the library (every GPU that loads the library holds
+ * it until the process exits).  The call allocates nothing: no cudaMalloc / cudaFree, no allocating library routine.
+ *   - limit: GPFLOW_ERR_STATIC_SCRATCH when gpflow_query_workspace(desc | GPFLOW_FLAG_FORCE_GENERIC, B, OP_FORWARD)
+ *     exceeds GPFLOW_STATIC_SCRATCH_BYTES (d=2 H=[15,15] and d=5 H=[5,5,5]: any B; d=10 nb=9 H=[50,50,50] fp32:
+ *     B <= 256); nothing is launched in that case;
+ *   - every call shares the one array: calls that OVERLAP on the GPU (other streams, other threads) race on it; calls
+ *     enqueued on one stream are safe.  It keeps the previous call's contents; the evaluation does not depend on them;
+ *   - the first call on each device looks the array's device address up (cudaGetSymbolAddress, may load the module):
+ *     make one call per device before starting a graph capture.
+ */
+#define GPFLOW_STATIC_SCRATCH_BYTES (32u << 20)
+int gpflow_velocity_static(const GpFlowDesc* desc, int64_t B, const void* params, const void* x, double t, void* v_out,
+                           void* cuda_stream);
 
 /* Name of the kernel family an op on this descriptor dispatches to ("small<f32,2,1,15,15>", "generic<f64>", ...). */
 int gpflow_kernel_variant(const GpFlowDesc* desc, int op, char* buf, size_t buf_len);
