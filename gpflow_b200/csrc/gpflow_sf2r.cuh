@@ -1,0 +1,188 @@
+// gpflow_b200 -- "sf2r": second formulation of the 2-D stream-function train-step kernel (sm_100a, fp32, d = 2,
+// nb_div_blocks = 1, two hidden layers of width <= 15).  Same reference call sites, same results and the same thread
+// mapping as gpflow_sf2.cuh (one thread = one sample, one warp = a tile of 32 samples, TMA-streamed stash); what changes
+// is HOW the gradient of the stream function is obtained.
+//
+// sf2 follows the reference literally: forward-mode tangents through the network (vector_field.py:92-128), i.e. per
+// evaluation three 15x15 contractions forward (a2, U2[:,0], U2[:,1]), three back through W2 and a rank-3 update of dW2.
+// For d = 2, nb = 1 the velocity only needs the scalar psi = f_0 - f_1 and its gradient (gpflow_sf2.cuh header), and the
+// gradient of ONE scalar is cheaper in reverse mode:
+//     a1 = W1 [x; t] + b1, h1 = tanh a1, sp1 = 1 - h1^2;   a2 = W2 h1 + b2, h2 = tanh a2, sp2 = 1 - h2^2
+//     psi = w3 . h2 + b3;   ws = w3 (.) sp2;   z = W2^T ws;   q = sp1 (.) z;   d_j psi = sum_m W1[m][j] q[m]
+// -- two contractions instead of three.  Its own reverse sweep (cotangents psib, gb_j of psi, d_j psi) is
+//     c  = sp1 (.) (W1x gb)            tb = W2 c                 e  = psib h2 + sp2 (.) tb           -> dw3
+//     ab2 = ws (.) (psib - 2 h2 (.) tb)                          hb = W2^T ab2,   z = W2^T ws (recomputed, same rows)
+//     dW2 += ab2 h1^T + ws c^T   (rank 2 per sample)             db2 += ab2
+//     ab1 = sp1 (.) hb - 2 h1 (.) z (.) c                        dW1 += ab1 [x; t]^T + q gb^T,   db1 += ab1
+//     xbar = W1x^T ab1 + (closed-form part)
+// -- three contractions that share ONE pass over the rows of W2, and a rank-2 update: 7 contraction-equivalents per
+// evaluation instead of 9, and the stash shrinks from 72 to 32 floats per sample and evaluation (x, h1, h2: 128 B, i.e.
+// 15.4 KB per sample and train step instead of 33.8 KB).  The arithmetic is plain fp32 FMA as before; only the order of
+// the sums differs from sf2 / the reference (both agree with the fp64 oracle to ~1e-6).
+//
+// Shared-memory layout per warp:
+//   stash buffers  2 x [32 samples][32 floats], 128-byte rows whose 16-byte chunks are XOR-swizzled with (sample & 7):
+//                  chunks 0-3 = (x0, h1[0..14]), chunks 4-7 = (x1, h2[0..14]).  A row is exactly what goes to HBM (one
+//                  4 KB bulk copy per evaluation); the swizzle makes the per-lane 128-bit accesses conflict free
+//                  without padding bytes in the stash.
+//   work rows      [32 samples][68 floats] (reverse sweep only): ab2 | ws | c | e | (x0 x1 gb0 gb1), later ab1 | q over
+//                  ab2 | ws.  Left/right factors of the two rank updates, read by the other lanes of the warp.
+// "Position" p = unit + 1 indexes the 16-wide rows (position 0 is the x slot of the stash row): it doubles as the bias
+// column of layer 2 in the forward contraction and in the dW2 tile.
+#pragma once
+#include "gpflow_sf2.cuh"
+
+namespace gpflow {
+
+template <int H1_, int H2_, int NW_>
+struct SF2R {
+  static constexpr int H1 = H1_, H2 = H2_, NW = NW_;
+  static_assert(H1 >= 1 && H1 <= 15 && H2 >= 1 && H2 <= 15, "position 0 of the 16-wide rows is the x / bias slot");
+  typedef SF2<H1_, H2_, NW_> Flat;  // flat parameter offsets
+  static constexpr int NPARAM = Flat::NPARAM;
+  // packed weights (floats)
+  static constexpr int W1P = 0;          // [16][4]  unit m: {W1[m][0], W1[m][1], W1[m][2] (time), b1[m]}; rows >= H1 zero
+  static constexpr int W2F = W1P + 64;   // [16][16] forward rows by POSITION p of h1: W2F[0][k] = b2[k], W2F[m+1][k] = W2[k][m]
+  static constexpr int W2B = W2F + 256;  // [16][16] backward rows AND columns by position: W2B[k+1][m+1] = W2[k][m], row 0 =
+                                         //          column 0 = 0 (register pairs line up with the position-indexed rows)
+  static constexpr int W3P = W2B + 256;  // [16]     by position: W3P[0] = 0, W3P[k+1] = W3[0][k] - W3[1][k]
+  static constexpr int B3C = W3P + 16;   // [4]      b3[0] - b3[1], 0, 0, 0
+  static constexpr int WEND = B3C + 4;
+  // per-warp buffers (floats)
+  static constexpr int SROW = 32, S_FL = 32 * SROW, STASH_BYTES = S_FL * 4;   // one evaluation of one tile: 4 KB
+  static constexpr int WS = 68;                                               // work row, 17 x 16 B (odd: conflict free)
+  static constexpr int O_AB = 0, O_WS = 16, O_C = 32, O_E = 48, O_XG = 64;
+  static constexpr int WK_FL = 32 * WS;
+  static constexpr int WARP_FL = 2 * S_FL + WK_FL;
+  // second-level accumulators: 16 dW2 tile | 4 dw3 | db3 | 16 dW1 tile | ot
+  static constexpr int G_W2 = 0, G_W3 = 16, G_B3 = 20, G_W1 = 21, G_OT = 37, NACC = 38;
+  static constexpr int SCT = 16;
+
+  static size_t smem_bytes(int n_steps) {
+    return (size_t)(WEND + SCT + round_up(n_steps + 1, 4) + round_up(NPARAM, 4) + NW * WARP_FL) * sizeof(float) + 128;
+  }
+};
+
+// packed weight i from the flat nn.Linear parameters (vector_field.py:56-61)
+template <class K>
+GPF_DEV float sf2r_pack_value(const float* __restrict__ raw, int i) {
+  typedef typename K::Flat F;
+  constexpr int H1 = K::H1, H2 = K::H2;
+  float v = 0.0f;
+  if (i < K::W2F) {
+    const int m = i >> 2, c = i & 3;
+    if (m < H1) v = c < 3 ? raw[F::OFF_W1 + 3 * m + c] : raw[F::OFF_B1 + m];
+  } else if (i < K::W2B) {
+    const int p = (i - K::W2F) >> 4, k = (i - K::W2F) & 15;
+    if (k < H2) v = p == 0 ? raw[F::OFF_B2 + k] : (p - 1 < H1 ? raw[F::OFF_W2 + k * H1 + (p - 1)] : 0.0f);
+  } else if (i < K::W3P) {
+    const int p = (i - K::W2B) >> 4, pm = (i - K::W2B) & 15;
+    if (p >= 1 && p - 1 < H2 && pm >= 1 && pm - 1 < H1) v = raw[F::OFF_W2 + (p - 1) * H1 + (pm - 1)];
+  } else if (i < K::B3C) {
+    const int p = i - K::W3P;
+    if (p >= 1 && p - 1 < H2) v = raw[F::OFF_W3 + (p - 1)] - raw[F::OFF_W3 + H2 + (p - 1)];
+  } else if (i == K::B3C) {
+    v = raw[F::OFF_B3] - raw[F::OFF_B3 + 1];
+  }
+  return v;
+}
+
+// chunk c (0..7) of a swizzled stash row; l7 = sample & 7
+GPF_DEV int sw_chunk(int c, int l7) { return (c ^ l7) << 2; }
+
+GPF_DEV void load_w16(const float* W, int off, float2 (&wp)[8]) {
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    const float4 t = ldw4(W, off + 4 * q);
+    wp[2 * q] = make_float2(t.x, t.y);
+    wp[2 * q + 1] = make_float2(t.z, t.w);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// forward: v(x, ts).  Writes the stash row (x0, h1 | x1, h2) of this lane's sample.
+// ---------------------------------------------------------------------------------------------------------
+template <class K>
+GPF_DEV void sf2r_forward_eval(const float* __restrict__ W, float* __restrict__ Srow, int l7, float x0, float x1, float ts,
+                               float bnd, float& v0, float& v1) {
+  constexpr int H1 = K::H1, H2 = K::H2;
+  // ---- layer 1 (unit m unrolled): h1 = tanh(W1 [x; t] + b1)   (vector_field.py:75-90)
+  float hp[16];  // by position: hp[0] = x0, hp[m + 1] = h1[m]
+  hp[0] = x0;
+#pragma unroll
+  for (int m = 0; m < 15; ++m) {
+    if (m < H1) {
+      const float4 w = ldw4(W, K::W1P + 4 * m);
+      hp[m + 1] = tanh_real(fmaf(w.x, x0, fmaf(w.y, x1, fmaf(w.z, ts, w.w))));
+    } else {
+      hp[m + 1] = 0.0f;
+    }
+  }
+#pragma unroll
+  for (int c = 0; c < 4; ++c) sts4(Srow + sw_chunk(c, l7), hp[4 * c], hp[4 * c + 1], hp[4 * c + 2], hp[4 * c + 3]);
+  // ---- layer 2 (position p unrolled): a2 = b2 + W2 h1 as packed fp32x2 FMAs, two output units per instruction
+  float2 a2p[8];
+  load_w16(W, K::W2F, a2p);  // position 0: the bias row times 1
+#pragma unroll
+  for (int p = 1; p <= H1; ++p) {
+    float2 wp[8];
+    load_w16(W, K::W2F + 16 * p, wp);
+    const float2 hd = make_float2(hp[p], hp[p]);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) a2p[j] = __ffma2_rn(wp[j], hd, a2p[j]);
+  }
+  // ---- activation 2, collapsed output row: psi = w3 . h2 + b3, ws = w3 (.) sp2
+  float h2p[16], ws[16];  // by position
+  h2p[0] = x1;
+  ws[0] = 0.0f;
+  float psi = ldw4(W, K::B3C).x;
+#pragma unroll
+  for (int c = 0; c < 4; ++c) {
+    const float4 w3v = ldw4(W, K::W3P + 4 * c);
+    const float w3[4] = {w3v.x, w3v.y, w3v.z, w3v.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int p = 4 * c + i, k = p - 1;
+      if (p >= 1 && k < H2) {
+        const float a = (k & 1) ? a2p[k >> 1].y : a2p[k >> 1].x;
+        const float h = tanh_real(a);
+        psi = fmaf(w3[i], h, psi);
+        ws[p] = w3[i] * fmaf(-h, h, 1.0f);
+        h2p[p] = h;
+      } else if (p >= 1) {
+        h2p[p] = ws[p] = 0.0f;
+      }
+    }
+    sts4(Srow + sw_chunk(4 + c, l7), h2p[4 * c], h2p[4 * c + 1], h2p[4 * c + 2], h2p[4 * c + 3]);
+  }
+  // ---- z = W2^T ws (position p of h2 unrolled); zp by position of h1
+  float2 zp[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) zp[j] = make_float2(0.0f, 0.0f);
+#pragma unroll
+  for (int p = 1; p <= H2; ++p) {
+    float2 wp[8];
+    load_w16(W, K::W2B + 16 * p, wp);
+    const float2 wd = make_float2(ws[p], ws[p]);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) zp[j] = __ffma2_rn(wp[j], wd, zp[j]);
+  }
+  // ---- grad psi = W1x^T (sp1 (.) z)
+  float g0 = 0.0f, g1 = 0.0f;
+#pragma unroll
+  for (int m = 0; m < H1; ++m) {
+    const float4 w = ldw4(W, K::W1P + 4 * m);
+    const float h = hp[m + 1], z = ((m + 1) & 1) ? zp[(m + 1) >> 1].y : zp[(m + 1) >> 1].x;
+    const float q = fmaf(-h, h, 1.0f) * z;
+    g0 = fmaf(w.x, q, g0);
+    g1 = fmaf(w.y, q, g1);
+  }
+  // ---- closed form A.2 for d = 2, nb = 1 (velocity_field.py:20-79)
+  const float s0 = fmaf(x0, x0, -bnd), s1 = fmaf(x1, x1, -bnd);
+  const float q0 = fmaf(2.0f * psi, x1, s1 * g1);
+  const float q1 = -fmaf(2.0f * psi, x0, s0 * g0);
+  v0 = s0 * q0;
+  v1 = s1 * q1;
+}
+
+}  // namespace gpflow

@@ -1,0 +1,200 @@
+// gpflow_b200 -- sf2r kernel, reverse sweep of one velocity evaluation for one warp tile (formulas: gpflow_sf2r.cuh).
+#pragma once
+#include "gpflow_sf2r.cuh"
+
+namespace gpflow {
+
+// Given the stash rows of one evaluation and the cotangent (vb0, vb1) of v, returns xbar = J_v^T vbar and accumulates
+// every parameter gradient:
+//   acc[16]   lane-owned 4x4 tile (positions 4ti.., 4tj..) of dW2 (+ db2 in column 0); rank-64 update over the tile
+//   accw[16]  lane-owned 4x4 tile {dW1[m][0], dW1[m][1], dW1[m][2] (time), db1[m]}, m = 4 (lane & 3) + r
+//   acc3[4]   dw3 of the collapsed output row at positions 4 (lane & 3) + r (dW3[0] = +, dW3[1] = -);  b3b lane-private
+template <class K>
+GPF_DEV void sf2r_reverse_eval(const float* __restrict__ W, const float* __restrict__ Sbuf, float* __restrict__ Wk, int lane,
+                               float ts, float bnd, float vb0, float vb1, float& xbar0, float& xbar1, float (&acc)[16],
+                               float (&accw)[16], float (&acc3)[4], float& b3b) {
+  constexpr int H1 = K::H1;
+  const int l7 = lane & 7;
+  const float* Srow = Sbuf + lane * K::SROW;
+  float* Wrow = Wk + lane * K::WS;
+  float hp[16];  // by position: x0, h1[0..14]
+#pragma unroll
+  for (int c = 0; c < 4; ++c) {
+    const float4 t = lds4(Srow + sw_chunk(c, l7));
+    hp[4 * c] = t.x; hp[4 * c + 1] = t.y; hp[4 * c + 2] = t.z; hp[4 * c + 3] = t.w;
+  }
+  const float x0 = hp[0], x1 = Srow[sw_chunk(4, l7)];
+  // ---- A.3, the part that does not need psi / grad psi
+  const float s0 = fmaf(x0, x0, -bnd), s1 = fmaf(x1, x1, -bnd);
+  const float qb0 = vb0 * s0, qb1 = vb1 * s1;
+  const float psib = 2.0f * (x1 * qb0 - x0 * qb1);
+  const float gb1 = s1 * qb0, gb0 = -s0 * qb1;
+  b3b += psib;
+  // ---- c = sp1 (.) (W1x gb), by POSITION (c[0] = 0) so that its register pairs are those of the 128-bit stores and of
+  //      the position-indexed weight rows; the work row also gets (x0 x1 gb0 gb1).  Position 0 of this sample's stash row
+  //      (x0, already read) becomes 1.0: the bias column of the dW2 update below
+  float cq[16];
+  cq[0] = 0.0f;
+#pragma unroll
+  for (int m = 0; m < 15; ++m) {
+    if (m < H1) {
+      const float4 w = ldw4(W, K::W1P + 4 * m);
+      const float h = hp[m + 1];
+      cq[m + 1] = fmaf(-h, h, 1.0f) * fmaf(w.x, gb0, w.y * gb1);
+    } else {
+      cq[m + 1] = 0.0f;
+    }
+  }
+#pragma unroll
+  for (int c = 0; c < 4; ++c) sts4(Wrow + K::O_C + 4 * c, cq[4 * c], cq[4 * c + 1], cq[4 * c + 2], cq[4 * c + 3]);
+  sts4(Wrow + K::O_XG, x0, x1, gb0, gb1);
+  const_cast<float*>(Srow)[sw_chunk(0, l7)] = 1.0f;
+  float2 cp[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) cp[j] = make_float2(cq[2 * j], cq[2 * j + 1]);
+  // ---- one pass over the rows of W2 (position p of h2, rolled by chunk): tb = W2 c (dot), then hb += W2[k,:] ab2[k],
+  //      z += W2[k,:] ws[k].  Position 0 (the x1 slot) has a zero weight row and w3 = 0: it contributes nothing.
+  float2 hbp[8], zp[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) hbp[j] = zp[j] = make_float2(0.0f, 0.0f);
+  float psi = ldw4(W, K::B3C).x;
+  GPF_SF2_LOOP
+  for (int c = 0; c < 4; ++c) {
+    const float4 hc = lds4(Srow + sw_chunk(4 + c, l7));
+    const float4 w3v = ldw4(W, K::W3P + 4 * c);
+    const float hh[4] = {hc.x, hc.y, hc.z, hc.w}, w3[4] = {w3v.x, w3v.y, w3v.z, w3v.w};
+    float ab[4], wsv[4], ev[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      float2 wp[8];
+      load_w16(W, K::W2B + 16 * (4 * c + i), wp);
+      float2 ta = __fmul2_rn(wp[0], cp[0]), tc = __fmul2_rn(wp[1], cp[1]);
+#pragma unroll
+      for (int j = 1; j < 4; ++j) {
+        ta = __ffma2_rn(wp[2 * j], cp[2 * j], ta);
+        tc = __ffma2_rn(wp[2 * j + 1], cp[2 * j + 1], tc);
+      }
+      const float tb = (ta.x + tc.x) + (ta.y + tc.y);
+      const float h = hh[i], sp = fmaf(-h, h, 1.0f);
+      ev[i] = fmaf(psib, h, sp * tb);                    // dw3 contribution: psib h2 + sp2 tb
+      const float wsi = w3[i] * sp;
+      const float abi = wsi * fmaf(-2.0f * h, tb, psib);   // ab2 = sp2 (psib w3 - 2 h2 w3 tb)
+      psi = fmaf(w3[i], h, psi);
+      const float2 abd = make_float2(abi, abi), wsd = make_float2(wsi, wsi);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        hbp[j] = __ffma2_rn(wp[j], abd, hbp[j]);
+        zp[j] = __ffma2_rn(wp[j], wsd, zp[j]);
+      }
+      ab[i] = abi;
+      wsv[i] = wsi;
+    }
+    sts4(Wrow + K::O_AB + 4 * c, ab[0], ab[1], ab[2], ab[3]);
+    sts4(Wrow + K::O_WS + 4 * c, wsv[0], wsv[1], wsv[2], wsv[3]);
+    sts4(Wrow + K::O_E + 4 * c, ev[0], ev[1], ev[2], ev[3]);
+  }
+  // ---- activation 1 + layer 1 (unit m unrolled): q = sp1 z, grad psi, ab1, xbar
+  float g0 = 0.0f, g1 = 0.0f, xb0 = 0.0f, xb1 = 0.0f;
+  float ab1[16], qv[16];
+#pragma unroll
+  for (int m = 0; m < 16; ++m) {
+    if (m < H1) {
+      const float4 w = ldw4(W, K::W1P + 4 * m);
+      const float h = hp[m + 1], sp = fmaf(-h, h, 1.0f);
+      const float z = ((m + 1) & 1) ? zp[(m + 1) >> 1].y : zp[(m + 1) >> 1].x;
+      const float hb = ((m + 1) & 1) ? hbp[(m + 1) >> 1].y : hbp[(m + 1) >> 1].x;
+      const float q = sp * z;
+      g0 = fmaf(w.x, q, g0);
+      g1 = fmaf(w.y, q, g1);
+      const float a = fmaf(-2.0f * h * z, cq[m + 1], sp * hb);   // ab1 = sp1 (hb - 2 h1 z qbar), c = sp1 qbar
+      xb0 = fmaf(w.x, a, xb0);
+      xb1 = fmaf(w.y, a, xb1);
+      ab1[m] = a;
+      qv[m] = q;
+    } else {
+      ab1[m] = qv[m] = 0.0f;
+    }
+  }
+  // ---- rest of A.3
+  {
+    const float q0 = fmaf(2.0f * psi, x1, s1 * g1);
+    const float q1 = -fmaf(2.0f * psi, x0, s0 * g0);
+    const float sb0 = fmaf(vb0, q0, -g0 * qb1), sb1 = fmaf(vb1, q1, g1 * qb0);
+    xb0 += fmaf(2.0f * x0, sb0, -2.0f * psi * qb1);
+    xb1 += fmaf(2.0f * x1, sb1, 2.0f * psi * qb0);
+  }
+  __syncwarp();
+  // ---- dW2[pk][pm] += sum_s ab2_s[pk] h1_s[pm] + ws_s[pk] c_s[pm]  (h1 position 0 == 1 -> db2): lane (slice, ti, tj)
+  //      owns the 4x4 tile (4ti.., 4tj..) over the 16 samples with bit 2 == slice (conflict-free with the swizzle)
+  {
+    const int tj = lane & 3, ti = (lane >> 2) & 3, slice = lane >> 4;
+    const float* wl = Wk + 4 * slice * K::WS + 4 * ti;                 // left factors:  + O_AB / O_WS
+    const float* wr = Wk + 4 * slice * K::WS + K::O_C + 4 * tj;        // right factor c
+    const float* sr[4];                                                // right factor h1: sample 4 slice + ql (+ 8 qh)
+#pragma unroll
+    for (int ql = 0; ql < 4; ++ql) sr[ql] = Sbuf + (4 * slice + ql) * K::SROW + sw_chunk(tj, 4 * slice + ql);
+    float2 accp[4][2];
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+      accp[r][0] = make_float2(acc[4 * r], acc[4 * r + 1]);
+      accp[r][1] = make_float2(acc[4 * r + 2], acc[4 * r + 3]);
+    }
+#pragma unroll
+    for (int qh = 0; qh < 4; ++qh) {
+#pragma unroll
+      for (int ql = 0; ql < 4; ++ql) {
+        const int so = ql + 8 * qh;
+        const float4 rh = lds4(sr[ql] + 8 * qh * K::SROW), rc = lds4(wr + so * K::WS);
+        const float4 la = lds4(wl + so * K::WS + K::O_AB), lw = lds4(wl + so * K::WS + K::O_WS);
+        const float2 r0[2] = {make_float2(rh.x, rh.y), make_float2(rh.z, rh.w)};
+        const float2 r1[2] = {make_float2(rc.x, rc.y), make_float2(rc.z, rc.w)};
+        const float a4[4] = {la.x, la.y, la.z, la.w}, w4[4] = {lw.x, lw.y, lw.z, lw.w};
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+          const float2 ad = make_float2(a4[r], a4[r]), wd = make_float2(w4[r], w4[r]);
+#pragma unroll
+          for (int i = 0; i < 2; ++i) accp[r][i] = __ffma2_rn(ad, r0[i], __ffma2_rn(wd, r1[i], accp[r][i]));
+        }
+      }
+    }
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+      acc[4 * r] = accp[r][0].x; acc[4 * r + 1] = accp[r][0].y;
+      acc[4 * r + 2] = accp[r][1].x; acc[4 * r + 3] = accp[r][1].y;
+    }
+  }
+  __syncwarp();  // every lane is done with the other lanes' [ab2 | ws] rows
+  sts4(Wrow + K::O_AB, ab1[0], ab1[1], ab1[2], ab1[3]);
+  sts4(Wrow + K::O_AB + 4, ab1[4], ab1[5], ab1[6], ab1[7]);
+  sts4(Wrow + K::O_AB + 8, ab1[8], ab1[9], ab1[10], ab1[11]);
+  sts4(Wrow + K::O_AB + 12, ab1[12], ab1[13], ab1[14], ab1[15]);
+  sts4(Wrow + K::O_WS, qv[0], qv[1], qv[2], qv[3]);
+  sts4(Wrow + K::O_WS + 4, qv[4], qv[5], qv[6], qv[7]);
+  sts4(Wrow + K::O_WS + 8, qv[8], qv[9], qv[10], qv[11]);
+  sts4(Wrow + K::O_WS + 12, qv[12], qv[13], qv[14], qv[15]);
+  __syncwarp();
+  // ---- dW1[m][:] += sum_s ab1_s[m] [x0, x1, t, 1]_s + q_s[m] [gb0, gb1, 0, 0]_s;  dw3[p] += sum_s e_s[p]:
+  //      lane (slice, ti) owns units / positions 4ti.. over the samples s = slice (mod 8)
+  {
+    const int ti = lane & 3, slice = lane >> 2;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const float* wr = Wk + (slice + 8 * q) * K::WS;
+      const float4 xg = lds4(wr + K::O_XG);
+      const float4 l0 = lds4(wr + K::O_AB + 4 * ti), l1 = lds4(wr + K::O_WS + 4 * ti), l2 = lds4(wr + K::O_E + 4 * ti);
+      const float la[4] = {l0.x, l0.y, l0.z, l0.w}, lq[4] = {l1.x, l1.y, l1.z, l1.w}, le[4] = {l2.x, l2.y, l2.z, l2.w};
+#pragma unroll
+      for (int r = 0; r < 4; ++r) {
+        accw[4 * r + 0] = fmaf(la[r], xg.x, fmaf(lq[r], xg.z, accw[4 * r + 0]));
+        accw[4 * r + 1] = fmaf(la[r], xg.y, fmaf(lq[r], xg.w, accw[4 * r + 1]));
+        accw[4 * r + 2] = fmaf(la[r], ts, accw[4 * r + 2]);
+        accw[4 * r + 3] += la[r];
+        acc3[r] += le[r];
+      }
+    }
+  }
+  xbar0 = xb0;
+  xbar1 = xb1;
+}
+
+}  // namespace gpflow

@@ -1,12 +1,21 @@
 // translation unit: sf2 (2-D stream-function) kernels, float: train step / backward (TMA-stashed) and forward-only
 #include "gpflow_sf2_fwd.cuh"
+#include "gpflow_sf2r_kernel.cuh"
 namespace gpflow {
+// GPFLOW_SF2_FORM=0 selects the first formulation (forward-mode tangents, 72-float stash: gpflow_sf2_kernel) for A/B
+// measurements and as an independent cross-check; the default is the reverse-mode-gradient kernel gpflow_sf2r_kernel.
+static int sf2_form() {
+  static const int f = [] { const char* e = getenv("GPFLOW_SF2_FORM"); return (e != nullptr && e[0] == '0') ? 0 : 1; }();
+  return f;
+}
 GPF_DECL_SMALL(sf2_15_15_f32) {
   const Ptrs<float>& p = *reinterpret_cast<const Ptrs<float>*>(ptrs);
   if (op == GPFLOW_OP_FORWARD) return launch_sf2_fwd<15, 15>(d, p, B, ws, wsb, st, sm_count);
-  return launch_sf2<15, 15>(d, op, p, B, ws, wsb, st, sm_count);
+  if (sf2_form() == 0) return launch_sf2<15, 15>(d, op, p, B, ws, wsb, st, sm_count);
+  return launch_sf2r<15, 15>(d, p, B, ws, wsb, st, sm_count);
 }
 size_t sf2_15_15_workspace(const GpFlowDesc* d, int64_t B, int op) {
-  return op == GPFLOW_OP_FORWARD ? sf2_fwd_workspace<15, 15>(B) : sf2_workspace<15, 15>(d, B);
+  if (op == GPFLOW_OP_FORWARD) return sf2_fwd_workspace<15, 15>(B);
+  return sf2_form() == 0 ? sf2_workspace<15, 15>(d, B) : sf2r_workspace<15, 15>(d, B);
 }
 }  // namespace gpflow
