@@ -546,11 +546,17 @@ def measure_workload(args, name, wl, euler, rank, world, local_rank, dev, steps,
                 traffic = json.load(open(tp))[name]["dram_bytes_per_sample"] * B   # per launch, like `achieved`
             except Exception:
                 traffic = None
+        achieved_exe, flops_exe = achieved, flops_alg
+        if "sf2r" in kernel:   # reverse-mode grad psi: fewer flops than the forward-mode count of the survey
+            from gpflow_b200.roofline import executed_flops_per_sample_sf2r
+            flops_exe = executed_flops_per_sample_sf2r(wl["hidden"][0], wl["hidden"][1], wl["n_steps"])
+            achieved_exe = achieved * flops_exe / flops_alg
         roofline = {
             "bound": "fp32_fma", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
             "frac_nominal": achieved / NOMINAL_FP32_TFLOPS, "peak_nominal": NOMINAL_FP32_TFLOPS,
             "peak_hot_after_run": peak_hot, "peak_sm_mhz": peaks["fp32_fma_sm_mhz"],
-            "achieved_executed": achieved, "traffic": traffic,
+            "achieved_executed": achieved_exe, "frac_executed": achieved_exe / peak,
+            "executed_flops_per_sample": flops_exe, "traffic": traffic,
             "kernel": kernel, "kernel_ms": ms_kernel, "algorithmic_flops_per_sample": flops_alg, "samples_per_launch": B,
             "peak_source": "FFMA burn micro-kernel (gpflow_fp32_fma_burn) measured ONCE before warm-up in this run, SM clock "
                            "beside it; MEASURED_PEAKS.json records no FP32 CUDA-core peak.  Nominal 148 SM x 128 lanes x "

@@ -65,7 +65,8 @@ def build(force=False, verbose=False):
         s, o = so
         if not force and os.path.exists(o) and os.path.getmtime(o) >= max(os.path.getmtime(s), newest_hdr):
             return
-        cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-c", s, "-o", o]
+        extra = os.environ.get("GPFLOW_NVCC_EXTRA", "").split()   # experiments only (e.g. -DGPF_SF2_CONST=1); use with --force
+        cmd = [nvcc] + NVCC_FLAGS + extra + (["-Xptxas", "-v"] if verbose else []) + ["-c", s, "-o", o]
         r = subprocess.run(cmd, capture_output=True, text=True)
         if verbose:
             sys.stderr.write(r.stderr)

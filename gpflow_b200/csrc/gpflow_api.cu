@@ -313,7 +313,7 @@ int gpflow_kernel_variant(const GpFlowDesc* d, int op, char* buf, size_t n) {
   const char* eu = (d->flags & GPFLOW_FLAG_EULER_PEN) ? ",euler" : "";
   SmallShape s;
   if (sf2_match(d, op))
-    snprintf(buf, n, "gpflow_sf2_kernel<f32,d=2,nb=1,H=[15,15],%s>", mode);
+    snprintf(buf, n, "%s<f32,d=2,nb=1,H=[15,15],%s>", sf2_15_15_kernel_name(op), mode);
   else if (small_match(d, &s))
     snprintf(buf, n, "gpflow_small_kernel<%s,d=%d,nb=%d,H=[%d,%d],%s%s>", ty, s.d, s.nb, s.h1, s.h2, mode, eu);
   else if (d->dtype == GPFLOW_F32 && tc_selected(d, (d->flags & GPFLOW_FLAG_FORCE_TC) ? 0 : tc_min_batch(d)))
@@ -327,6 +327,7 @@ int gpflow_launch_count(const GpFlowDesc* d, int op) {
   if (validate(d) != GPFLOW_OK) return -1;
   (void)op;
   SmallShape s;
+  if (sf2_match(d, op)) return sf2_15_15_launches(op);   // [weight pack +] main kernel + deterministic finalize
   if (small_match(d, &s)) return 2;            // main kernel + deterministic finalize
   return generic_runs_padded(d) ? 4 : 3;       // [zero-padding scatter +] weight transpose + main kernel + finalize
 }

@@ -87,13 +87,29 @@ GPF_DEV float sf2r_pack_value(const float* __restrict__ raw, int i) {
   return v;
 }
 
+// Where the (warp-uniform) packed weights are read from.  A warp-uniform LDS.128 costs 2 shared-memory wavefronts for 16
+// useful bytes (measured, profiles/r2_sf2r_*), and with 7 instead of 9 contractions per evaluation the shared-memory pipe
+// became the limiter (84 % busy); the constant bank serves the same loads through the uniform datapath (LDCU / LDC).
+// GPF_SF2R_CONST is a bit mask: 1 = forward evaluation, 2 = the rolled W2 pass of the reverse sweep, 4 = the other
+// weight loads of the reverse sweep.  The constant copy is per device and shared by all calls: see launch_sf2r.
+#ifndef GPF_SF2R_CONST
+#define GPF_SF2R_CONST 1   // measured at C4 (tools/sf2r_const_ab.sh): 0: 1.34e8, 1: 1.48e8, 3: 1.47e8, 7: 1.40e8 samples/s
+#endif
+__constant__ float sf2r_cw[640];
+template <int BIT>
+GPF_DEV float4 ldwr4(const float* W, int off) {
+  if (GPF_SF2R_CONST & BIT) return *reinterpret_cast<const float4*>(&sf2r_cw[off]);
+  return ldsw4(W + off);
+}
+
 // chunk c (0..7) of a swizzled stash row; l7 = sample & 7
 GPF_DEV int sw_chunk(int c, int l7) { return (c ^ l7) << 2; }
 
+template <int BIT>
 GPF_DEV void load_w16(const float* W, int off, float2 (&wp)[8]) {
 #pragma unroll
   for (int q = 0; q < 4; ++q) {
-    const float4 t = ldw4(W, off + 4 * q);
+    const float4 t = ldwr4<BIT>(W, off + 4 * q);
     wp[2 * q] = make_float2(t.x, t.y);
     wp[2 * q + 1] = make_float2(t.z, t.w);
   }
@@ -112,7 +128,7 @@ GPF_DEV void sf2r_forward_eval(const float* __restrict__ W, float* __restrict__ 
 #pragma unroll
   for (int m = 0; m < 15; ++m) {
     if (m < H1) {
-      const float4 w = ldw4(W, K::W1P + 4 * m);
+      const float4 w = ldwr4<1>(W, K::W1P + 4 * m);
       hp[m + 1] = tanh_real(fmaf(w.x, x0, fmaf(w.y, x1, fmaf(w.z, ts, w.w))));
     } else {
       hp[m + 1] = 0.0f;
@@ -122,11 +138,11 @@ GPF_DEV void sf2r_forward_eval(const float* __restrict__ W, float* __restrict__ 
   for (int c = 0; c < 4; ++c) sts4(Srow + sw_chunk(c, l7), hp[4 * c], hp[4 * c + 1], hp[4 * c + 2], hp[4 * c + 3]);
   // ---- layer 2 (position p unrolled): a2 = b2 + W2 h1 as packed fp32x2 FMAs, two output units per instruction
   float2 a2p[8];
-  load_w16(W, K::W2F, a2p);  // position 0: the bias row times 1
+  load_w16<1>(W, K::W2F, a2p);  // position 0: the bias row times 1
 #pragma unroll
   for (int p = 1; p <= H1; ++p) {
     float2 wp[8];
-    load_w16(W, K::W2F + 16 * p, wp);
+    load_w16<1>(W, K::W2F + 16 * p, wp);
     const float2 hd = make_float2(hp[p], hp[p]);
 #pragma unroll
     for (int j = 0; j < 8; ++j) a2p[j] = __ffma2_rn(wp[j], hd, a2p[j]);
@@ -135,10 +151,10 @@ GPF_DEV void sf2r_forward_eval(const float* __restrict__ W, float* __restrict__ 
   float h2p[16], ws[16];  // by position
   h2p[0] = x1;
   ws[0] = 0.0f;
-  float psi = ldw4(W, K::B3C).x;
+  float psi = ldwr4<1>(W, K::B3C).x;
 #pragma unroll
   for (int c = 0; c < 4; ++c) {
-    const float4 w3v = ldw4(W, K::W3P + 4 * c);
+    const float4 w3v = ldwr4<1>(W, K::W3P + 4 * c);
     const float w3[4] = {w3v.x, w3v.y, w3v.z, w3v.w};
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
@@ -162,7 +178,7 @@ GPF_DEV void sf2r_forward_eval(const float* __restrict__ W, float* __restrict__ 
 #pragma unroll
   for (int p = 1; p <= H2; ++p) {
     float2 wp[8];
-    load_w16(W, K::W2B + 16 * p, wp);
+    load_w16<1>(W, K::W2B + 16 * p, wp);
     const float2 wd = make_float2(ws[p], ws[p]);
 #pragma unroll
     for (int j = 0; j < 8; ++j) zp[j] = __ffma2_rn(wp[j], wd, zp[j]);
@@ -171,7 +187,7 @@ GPF_DEV void sf2r_forward_eval(const float* __restrict__ W, float* __restrict__ 
   float g0 = 0.0f, g1 = 0.0f;
 #pragma unroll
   for (int m = 0; m < H1; ++m) {
-    const float4 w = ldw4(W, K::W1P + 4 * m);
+    const float4 w = ldwr4<1>(W, K::W1P + 4 * m);
     const float h = hp[m + 1], z = ((m + 1) & 1) ? zp[(m + 1) >> 1].y : zp[(m + 1) >> 1].x;
     const float q = fmaf(-h, h, 1.0f) * z;
     g0 = fmaf(w.x, q, g0);

@@ -4,11 +4,19 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <mutex>
+
 #include "gpflow_dispatch.h"
 #include "gpflow_sf2_kernel.cuh"  // SF2Args, kSF2MaxWarps, the first formulation (kept: GPFLOW_SF2_FORM=0)
 #include "gpflow_sf2r_rev.cuh"
 
 namespace gpflow {
+
+template <class K>
+__global__ void sf2r_pack_kernel(const float* __restrict__ params, float* __restrict__ packed) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < 640) packed[i] = i < K::WEND ? sf2r_pack_value<K>(params, i) : 0.0f;
+}
 
 template <int H1, int H2, int NW>
 __global__ void __launch_bounds__(NW * 32, 1) gpflow_sf2r_kernel(const SF2Args a) {
@@ -253,11 +261,28 @@ size_t sf2r_workspace(const GpFlowDesc* d, int64_t B) {
   const int64_t ctas = tiles < kMaxSMs ? (tiles < 1 ? 1 : tiles) : kMaxSMs;
   const int64_t slots = ctas * kSF2MaxWarps;
   const int64_t stash_slots = tiles < slots ? tiles : slots;
-  size_t bytes = 0;
+  size_t bytes = 640 * 4;  // packed weights (staging for the constant bank)
   bytes += align_up((size_t)slots * (3 + K::NPARAM) * 4, 256);
   bytes += align_up((size_t)slots * K::NACC * 32 * 4, 256);
   bytes += (size_t)stash_slots * 4 * d->n_steps * K::STASH_BYTES;
   return bytes;
+}
+
+// The constant-bank copy of the packed weights (sf2r_cw) is ONE array per device, rewritten by every call.  Calls on one
+// stream are ordered by the stream; a call on another stream must not overwrite the array while the previous call's
+// kernel is still reading it, so every call waits (on the device, cudaStreamWaitEvent) for the event recorded behind the
+// previous call's kernel on this device.  The mutex keeps two host threads from interleaving their [wait, copy, launch,
+// record] sequences.  The event is created on the first call per device (not device memory).  While the stream is being
+// captured into a CUDA graph the wait / record are skipped: the captured nodes are ordered by the capture itself, and
+// replays of such a graph must not overlap other calls of this kernel on the same device.
+struct SF2RConstGuard {
+  std::mutex mu;
+  cudaEvent_t ev[64];
+  bool have[64];
+};
+inline SF2RConstGuard& sf2r_const_guard() {
+  static SF2RConstGuard g = {};
+  return g;
 }
 
 template <int H1, int H2>
@@ -286,6 +311,8 @@ int launch_sf2r(const GpFlowDesc* d, const Ptrs<float>& p, int64_t B, void* ws, 
   a.params = p.params; a.x_in = p.x_in; a.x_data = p.x_data; a.grad_y = p.grad_y;
   a.y_out = p.y_out; a.grad_x_out = p.grad_x_out;
   char* wsp = reinterpret_cast<char*>(ws);
+  float* packed = reinterpret_cast<float*>(wsp);
+  wsp += 640 * 4;
   a.partials = reinterpret_cast<float*>(wsp);
   wsp += align_up((size_t)slots * npart * 4, 256);
   a.g2 = reinterpret_cast<float*>(wsp);
@@ -297,8 +324,51 @@ int launch_sf2r(const GpFlowDesc* d, const Ptrs<float>& p, int64_t B, void* ws, 
   a.t0 = rev ? (float)(d->dt * (double)d->n_steps_nominal) : 0.0f;  // res_net.py:217-219
   a.sigma = (float)d->sigma;
   a.loss_scale = (float)d->loss_scale;
+#if GPF_SF2R_CONST
+  {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) {
+      cudaGetLastError();
+      return GPFLOW_ERR_CUDA;
+    }
+    SF2RConstGuard& g = sf2r_const_guard();
+    std::lock_guard<std::mutex> lk(g.mu);
+    cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+    if (cudaStreamIsCapturing(st, &cs) != cudaSuccess) {
+      cudaGetLastError();
+      cs = cudaStreamCaptureStatusNone;
+    }
+    const bool guard = cs == cudaStreamCaptureStatusNone;
+    if (guard) {
+      if (!g.have[dev]) {
+        if (cudaEventCreateWithFlags(&g.ev[dev], cudaEventDisableTiming) != cudaSuccess) {
+          cudaGetLastError();
+          return GPFLOW_ERR_CUDA;
+        }
+        g.have[dev] = true;
+      } else if (cudaStreamWaitEvent(st, g.ev[dev], 0) != cudaSuccess) {
+        cudaGetLastError();
+        return GPFLOW_ERR_CUDA;
+      }
+    }
+    sf2r_pack_kernel<K><<<5, 128, 0, st>>>(p.params, packed);
+    if (cudaGetLastError() != cudaSuccess) return GPFLOW_ERR_CUDA;
+    if (cudaMemcpyToSymbolAsync(sf2r_cw, packed, 640 * 4, 0, cudaMemcpyDeviceToDevice, st) != cudaSuccess) {
+      cudaGetLastError();
+      return GPFLOW_ERR_CUDA;
+    }
+    kern<<<(unsigned)grid, NW * 32, smem, st>>>(a);
+    if (cudaGetLastError() != cudaSuccess) return GPFLOW_ERR_CUDA;
+    if (guard && cudaEventRecord(g.ev[dev], st) != cudaSuccess) {
+      cudaGetLastError();
+      return GPFLOW_ERR_CUDA;
+    }
+  }
+#else
+  (void)packed;
   kern<<<(unsigned)grid, NW * 32, smem, st>>>(a);
   if (cudaGetLastError() != cudaSuccess) return GPFLOW_ERR_CUDA;
+#endif
   gpflow_finalize_kernel<float><<<(npart + 127) / 128, 128, 0, st>>>(a.partials, (int)slots, npart, npart, p.scalars_out,
                                                                      p.grads_out);
   if (cudaGetLastError() != cudaSuccess) return GPFLOW_ERR_CUDA;

@@ -38,7 +38,7 @@ GPF_DEV void sf2r_reverse_eval(const float* __restrict__ W, const float* __restr
 #pragma unroll
   for (int m = 0; m < 15; ++m) {
     if (m < H1) {
-      const float4 w = ldw4(W, K::W1P + 4 * m);
+      const float4 w = ldwr4<4>(W, K::W1P + 4 * m);
       const float h = hp[m + 1];
       cq[m + 1] = fmaf(-h, h, 1.0f) * fmaf(w.x, gb0, w.y * gb1);
     } else {
@@ -57,17 +57,17 @@ GPF_DEV void sf2r_reverse_eval(const float* __restrict__ W, const float* __restr
   float2 hbp[8], zp[8];
 #pragma unroll
   for (int j = 0; j < 8; ++j) hbp[j] = zp[j] = make_float2(0.0f, 0.0f);
-  float psi = ldw4(W, K::B3C).x;
+  float psi = ldwr4<4>(W, K::B3C).x;
   GPF_SF2_LOOP
   for (int c = 0; c < 4; ++c) {
     const float4 hc = lds4(Srow + sw_chunk(4 + c, l7));
-    const float4 w3v = ldw4(W, K::W3P + 4 * c);
+    const float4 w3v = ldwr4<4>(W, K::W3P + 4 * c);
     const float hh[4] = {hc.x, hc.y, hc.z, hc.w}, w3[4] = {w3v.x, w3v.y, w3v.z, w3v.w};
     float ab[4], wsv[4], ev[4];
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
       float2 wp[8];
-      load_w16(W, K::W2B + 16 * (4 * c + i), wp);
+      load_w16<2>(W, K::W2B + 16 * (4 * c + i), wp);
       float2 ta = __fmul2_rn(wp[0], cp[0]), tc = __fmul2_rn(wp[1], cp[1]);
 #pragma unroll
       for (int j = 1; j < 4; ++j) {
@@ -99,7 +99,7 @@ GPF_DEV void sf2r_reverse_eval(const float* __restrict__ W, const float* __restr
 #pragma unroll
   for (int m = 0; m < 16; ++m) {
     if (m < H1) {
-      const float4 w = ldw4(W, K::W1P + 4 * m);
+      const float4 w = ldwr4<4>(W, K::W1P + 4 * m);
       const float h = hp[m + 1], sp = fmaf(-h, h, 1.0f);
       const float z = ((m + 1) & 1) ? zp[(m + 1) >> 1].y : zp[(m + 1) >> 1].x;
       const float hb = ((m + 1) & 1) ? hbp[(m + 1) >> 1].y : hbp[(m + 1) >> 1].x;

@@ -14,6 +14,11 @@ GPF_DECL_SMALL(sf2_15_15_f32) {
   if (sf2_form() == 0) return launch_sf2<15, 15>(d, op, p, B, ws, wsb, st, sm_count);
   return launch_sf2r<15, 15>(d, p, B, ws, wsb, st, sm_count);
 }
+// kernels per call (launch accounting) and the name of the main kernel
+int sf2_15_15_launches(int op) { return (op != GPFLOW_OP_FORWARD && sf2_form() != 0 && GPF_SF2R_CONST) ? 3 : 2; }
+const char* sf2_15_15_kernel_name(int op) {
+  return (op != GPFLOW_OP_FORWARD && sf2_form() != 0) ? "gpflow_sf2r_kernel" : "gpflow_sf2_kernel";
+}
 size_t sf2_15_15_workspace(const GpFlowDesc* d, int64_t B, int op) {
   if (op == GPFLOW_OP_FORWARD) return sf2_fwd_workspace<15, 15>(B);
   return sf2_form() == 0 ? sf2_workspace<15, 15>(d, B) : sf2r_workspace<15, 15>(d, B);

@@ -42,3 +42,18 @@ def executed_flops_per_sample_tc(d, nb, hidden, n_steps, train=True):
     f = 2.0 * d * H[0] + sum(2.0 * (d + 1) * H[l - 1] * H[l] for l in range(1, len(H))) + 2.0 * H[-1] * (d * nb + 2 * R)
     fwd = 4 * n_steps * f
     return 4.0 * fwd if train else fwd
+
+
+def executed_flops_per_sample_sf2r(h1, h2, n_steps):
+    """Flops the 2-D stream-function kernel `gpflow_sf2r_kernel` (gpflow_sf2r*.cuh) EXECUTES per sample and train step
+    (FMA = 2, tanh / erf not counted, like the algorithmic count).  It obtains grad psi in reverse mode, so a forward
+    evaluation has two H1 x H2 contractions (a2, z = W2^T ws) instead of the three the forward-mode count assumes, and
+    its reverse sweep three (tb, hb, z again) plus a rank-2 update of dW2 instead of three plus a rank-3 update:
+        F_fwd = 6 H1 + 2 H1 H2 + H2 + 2 H1 H2 + 2 H2 + 3 H2 + 2 H1 + 4 H1 + 12
+        F_rev = 5 H1 + 3 (2 H1 H2) + 10 H2 + 14 H1 + 4 H2 (H1 + 1) + 11 H1 + 40
+    (layer 1, a2 + bias, z, psi, sp2 / ws, sp1 / q, grad psi, closed form | c, the three contractions, per-unit adjoints of
+    layer 2 and layer 1, dW2 with its bias column, dW1 / db1, closed-form adjoint).  H = [15, 15]: 4 132 per evaluation
+    against the algorithmic 5 112 (0.81)."""
+    f_fwd = 6 * h1 + 2 * h1 * h2 + h2 + 2 * h1 * h2 + 2 * h2 + 3 * h2 + 2 * h1 + 4 * h1 + 12
+    f_rev = 5 * h1 + 3 * (2 * h1 * h2) + 10 * h2 + 14 * h1 + 4 * h2 * (h1 + 1) + 11 * h1 + 40
+    return 4.0 * n_steps * (f_fwd + f_rev)

@@ -55,7 +55,7 @@ def test_param_count_and_validation(lib):
 def test_workspace_query_and_variant_names(lib):
     from gpflow_b200 import ops, FlowConfig, kernel_variant, _lib
     c4 = FlowConfig(2, 1, (15, 15), 15)
-    assert "gpflow_sf2_kernel<f32,d=2,nb=1,H=[15,15],train>" == kernel_variant(c4)
+    assert "gpflow_sf2r_kernel<f32,d=2,nb=1,H=[15,15],train>" == kernel_variant(c4)
     assert "gpflow_small_kernel<f32,d=2,nb=1,H=[15,15],train>" == kernel_variant(c4, force_v1=True)
     assert "gpflow_sf2_kernel<f32,d=2,nb=1,H=[15,15],fwd>" == kernel_variant(c4, op=_lib.OP_FORWARD, lagrangian=True)
     assert "gpflow_small_kernel<f32,d=2,nb=1,H=[15,15],fwd>" == kernel_variant(c4, op=_lib.OP_FORWARD, force_v1=True)
