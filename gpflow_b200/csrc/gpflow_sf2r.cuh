@@ -96,6 +96,14 @@ GPF_DEV float sf2r_pack_value(const float* __restrict__ raw, int i) {
 #define GPF_SF2R_CONST 1   // measured at C4 (tools/sf2r_const_ab.sh): 0: 1.34e8, 1: 1.48e8, 3: 1.47e8, 7: 1.40e8 samples/s
 #endif
 __constant__ float sf2r_cw[640];
+// GPF_SF2R_TANH: 0 = tanh_real (<= 2 ulp relative, default), 1 = tanh_exp2 (absolute accuracy ~3e-7).  Measured at C4
+// (tools/sf2r_tanh_ab.sh): 1.46e8 vs 1.60e8 samples/s and the same errors against the fp64 oracle at weights N(0, 0.1..0.6^2),
+// but at the reference's own initialisation (weights N(0, 1e-3^2): |a| ~ 1e-3, where tanh x ~ x needs RELATIVE accuracy)
+// the 12-step training replays of the unmodified reference fail their 1e-5 bar -- so the faster variant is not used.
+#ifndef GPF_SF2R_TANH
+#define GPF_SF2R_TANH 0
+#endif
+GPF_DEV float sf2r_tanh(float x) { return GPF_SF2R_TANH ? tanh_exp2(x) : tanh_real(x); }
 template <int BIT>
 GPF_DEV float4 ldwr4(const float* W, int off) {
   if (GPF_SF2R_CONST & BIT) return *reinterpret_cast<const float4*>(&sf2r_cw[off]);
@@ -129,7 +137,7 @@ GPF_DEV void sf2r_forward_eval(const float* __restrict__ W, float* __restrict__ 
   for (int m = 0; m < 15; ++m) {
     if (m < H1) {
       const float4 w = ldwr4<1>(W, K::W1P + 4 * m);
-      hp[m + 1] = tanh_real(fmaf(w.x, x0, fmaf(w.y, x1, fmaf(w.z, ts, w.w))));
+      hp[m + 1] = sf2r_tanh(fmaf(w.x, x0, fmaf(w.y, x1, fmaf(w.z, ts, w.w))));
     } else {
       hp[m + 1] = 0.0f;
     }
@@ -161,7 +169,7 @@ GPF_DEV void sf2r_forward_eval(const float* __restrict__ W, float* __restrict__ 
       const int p = 4 * c + i, k = p - 1;
       if (p >= 1 && k < H2) {
         const float a = (k & 1) ? a2p[k >> 1].y : a2p[k >> 1].x;
-        const float h = tanh_real(a);
+        const float h = sf2r_tanh(a);
         psi = fmaf(w3[i], h, psi);
         ws[p] = w3[i] * fmaf(-h, h, 1.0f);
         h2p[p] = h;

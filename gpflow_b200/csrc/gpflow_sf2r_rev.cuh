@@ -66,6 +66,10 @@ GPF_DEV void sf2r_reverse_eval(const float* __restrict__ W, const float* __restr
     float ab[4], wsv[4], ev[4];
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
+      if (i == 0 && c == 0) {   // position 0 is the x1 slot (zero weight row, w3 = 0): skip it (warp-uniform branch)
+        ab[0] = wsv[0] = ev[0] = 0.0f;
+        continue;
+      }
       float2 wp[8];
       load_w16<2>(W, K::W2B + 16 * (4 * c + i), wp);
       float2 ta = __fmul2_rn(wp[0], cp[0]), tc = __fmul2_rn(wp[1], cp[1]);
