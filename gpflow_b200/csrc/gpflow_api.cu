@@ -85,6 +85,14 @@ bool sf2_match(const GpFlowDesc* d, int op) {
   return d->n_steps <= 1024;
 }
 
+// sf2e: the same shape WITH the Euler penalization, train step / backward op (forward op, Lagrangian: v1 kernel)
+bool sf2e_match(const GpFlowDesc* d, int op) {
+  SmallShape s;
+  if (!small_match(d, &s) || d->dtype != GPFLOW_F32 || !sf2e_15_15_enabled()) return false;
+  if (!(d->flags & GPFLOW_FLAG_EULER_PEN) || (d->flags & (GPFLOW_FLAG_FORCE_V1 | GPFLOW_FLAG_LAGRANGIAN))) return false;
+  return op != GPFLOW_OP_FORWARD && d->n_steps <= 1024;
+}
+
 // tc (chunked tensor-core path) takes the wide fp32 shapes without Euler penalization once the batch is large enough to
 // fill 128-row MMA tiles on every SM; GPFLOW_TC_MIN_BATCH overrides the threshold, GPFLOW_FLAG_FORCE_TC ignores it.
 // Measured crossovers (B200, train step, profiles/r2_tc_crossover.txt): d=10, H=[50,50,50] -- generic 29.6 ms vs tc 33.5 ms at
@@ -111,6 +119,7 @@ int dispatch<float>(const GpFlowDesc* d, int op, const Ptrs<float>& p, int64_t B
   const bool euler = (d->flags & GPFLOW_FLAG_EULER_PEN) != 0;
   SmallShape s;
   if (sf2_match(d, op)) return sf2_15_15_f32(d, op, &p, B, ws, wsb, st, sm);
+  if (sf2e_match(d, op)) return sf2e_15_15_f32(d, op, &p, B, ws, wsb, st, sm);
   if (small_match(d, &s)) return euler ? small_2_1_15_15_f32_euler(d, op, &p, B, ws, wsb, st, sm) : small_2_1_15_15_f32(d, op, &p, B, ws, wsb, st, sm);
   if (tc_selected(d, B))
     return tc_f32(d, op, p.params, p.x_in, p.x_data, p.grad_y, p.y_out, p.logdet_out, p.traj_out, p.grad_x_out, p.grads_out,
@@ -246,6 +255,10 @@ int gpflow_query_workspace(const GpFlowDesc* d, int64_t B, int op, size_t* bytes
     *bytes = sf2_15_15_workspace(d, B, op);
     return GPFLOW_OK;
   }
+  if (sf2e_match(d, op)) {
+    *bytes = sf2e_15_15_workspace(d, B);
+    return GPFLOW_OK;
+  }
   if (small_match(d, &s)) {
     *bytes = small_workspace(d, B, op, (int)np);
     return GPFLOW_OK;
@@ -314,6 +327,8 @@ int gpflow_kernel_variant(const GpFlowDesc* d, int op, char* buf, size_t n) {
   SmallShape s;
   if (sf2_match(d, op))
     snprintf(buf, n, "%s<f32,d=2,nb=1,H=[15,15],%s>", sf2_15_15_kernel_name(op), mode);
+  else if (sf2e_match(d, op))
+    snprintf(buf, n, "gpflow_sf2e_kernel<f32,d=2,nb=1,H=[15,15],%s,euler>", mode);
   else if (small_match(d, &s))
     snprintf(buf, n, "gpflow_small_kernel<%s,d=%d,nb=%d,H=[%d,%d],%s%s>", ty, s.d, s.nb, s.h1, s.h2, mode, eu);
   else if (d->dtype == GPFLOW_F32 && tc_selected(d, (d->flags & GPFLOW_FLAG_FORCE_TC) ? 0 : tc_min_batch(d)))
@@ -328,6 +343,7 @@ int gpflow_launch_count(const GpFlowDesc* d, int op) {
   (void)op;
   SmallShape s;
   if (sf2_match(d, op)) return sf2_15_15_launches(op);   // [weight pack +] main kernel + deterministic finalize
+  if (sf2e_match(d, op)) return 3;
   if (small_match(d, &s)) return 2;            // main kernel + deterministic finalize
   return generic_runs_padded(d) ? 4 : 3;       // [zero-padding scatter +] weight transpose + main kernel + finalize
 }

@@ -39,6 +39,9 @@ GPF_DECL_SMALL(small_2_1_15_15_f32_euler);
 GPF_DECL_SMALL(small_2_1_15_15_f64);
 GPF_DECL_SMALL(small_2_1_15_15_f64_euler);
 GPF_DECL_SMALL(sf2_15_15_f32);  // stream-function kernels v2 (fp32, no Euler): train step / backward, forward-only
+GPF_DECL_SMALL(sf2e_15_15_f32);  // sf2r + Euler penalization (train step / backward)
+bool sf2e_15_15_enabled();
+size_t sf2e_15_15_workspace(const GpFlowDesc* d, int64_t B);
 size_t sf2_15_15_workspace(const GpFlowDesc* d, int64_t B, int op);
 int sf2_15_15_launches(int op);              // [pack +] main kernel + finalize
 const char* sf2_15_15_kernel_name(int op);   // gpflow_sf2r_kernel (train / backward, default) or gpflow_sf2_kernel

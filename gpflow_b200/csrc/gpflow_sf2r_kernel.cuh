@@ -18,10 +18,34 @@ __global__ void sf2r_pack_kernel(const float* __restrict__ params, float* __rest
   if (i < 640) packed[i] = i < K::WEND ? sf2r_pack_value<K>(params, i) : 0.0f;
 }
 
+// gradient entry e of the flat parameter vector from a warp's second-level accumulators G[NACC][32]
+template <class K>
+GPF_DEV float sf2r_partial_entry(const float* G, int e) {
+  typedef typename K::Flat F;
+  constexpr int H1 = K::H1, H2 = K::H2;
+  float s = 0.0f;
+  if (e < F::OFF_W2) {  // W1 [H1][3] then b1 [H1]  ->  tile entry (m & 3, c) of the lanes (slice, ti = m >> 2)
+    const int m = e < F::OFF_B1 ? e / 3 : e - F::OFF_B1, c = e < F::OFF_B1 ? e % 3 : 3;
+    for (int sl = 0; sl < 8; ++sl) s += G[(K::G_W1 + (m & 3) * 4 + c) * 32 + sl * 4 + (m >> 2)];
+  } else if (e < F::OFF_W3) {  // W2 [H2][H1] then b2 [H2]  ->  tile entry (position k + 1, position m + 1 | 0 = bias)
+    const int pk = (e < F::OFF_B2 ? (e - F::OFF_W2) / H1 : e - F::OFF_B2) + 1;
+    const int pm = e < F::OFF_B2 ? (e - F::OFF_W2) % H1 + 1 : 0;
+    const int ln = (pk >> 2) * 4 + (pm >> 2), el = (pk & 3) * 4 + (pm & 3);
+    s = G[(K::G_W2 + el) * 32 + ln] + G[(K::G_W2 + el) * 32 + ln + 16];
+  } else if (e < F::OFF_B3) {  // W3 [2][H2]: row 0 = +, row 1 = - of the collapsed row, position k + 1
+    const int r = (e - F::OFF_W3) / H2, p = (e - F::OFF_W3) % H2 + 1;
+    for (int sl = 0; sl < 8; ++sl) s += G[(K::G_W3 + (p & 3)) * 32 + sl * 4 + (p >> 2)];
+    if (r == 1) s = -s;
+  } else {  // b3 [2]
+    for (int l = 0; l < 32; ++l) s += G[K::G_B3 * 32 + l];
+    if (e - F::OFF_B3 == 1) s = -s;
+  }
+  return s;
+}
+
 template <int H1, int H2, int NW>
 __global__ void __launch_bounds__(NW * 32, 1) gpflow_sf2r_kernel(const SF2Args a) {
   typedef SF2R<H1, H2, NW> K;
-  typedef typename K::Flat F;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   __shared__ uint64_t bar_stage;
   __shared__ uint64_t bars[NW][2];
@@ -231,26 +255,7 @@ __global__ void __launch_bounds__(NW * 32, 1) gpflow_sf2r_kernel(const SF2Args a
     part[1] = 0.0f;
     part[2] = 0.0f;
   }
-  for (int e = lane; e < K::NPARAM; e += 32) {
-    float s = 0.0f;
-    if (e < F::OFF_W2) {  // W1 [H1][3] then b1 [H1]  ->  tile entry (m & 3, c) of the lanes (slice, ti = m >> 2)
-      const int m = e < F::OFF_B1 ? e / 3 : e - F::OFF_B1, c = e < F::OFF_B1 ? e % 3 : 3;
-      for (int sl = 0; sl < 8; ++sl) s += G[(K::G_W1 + (m & 3) * 4 + c) * 32 + sl * 4 + (m >> 2)];
-    } else if (e < F::OFF_W3) {  // W2 [H2][H1] then b2 [H2]  ->  tile entry (position k + 1, position m + 1 | 0 = bias)
-      const int pk = (e < F::OFF_B2 ? (e - F::OFF_W2) / H1 : e - F::OFF_B2) + 1;
-      const int pm = e < F::OFF_B2 ? (e - F::OFF_W2) % H1 + 1 : 0;
-      const int ln = (pk >> 2) * 4 + (pm >> 2), el = (pk & 3) * 4 + (pm & 3);
-      s = G[(K::G_W2 + el) * 32 + ln] + G[(K::G_W2 + el) * 32 + ln + 16];
-    } else if (e < F::OFF_B3) {  // W3 [2][H2]: row 0 = +, row 1 = - of the collapsed row, position k + 1
-      const int r = (e - F::OFF_W3) / H2, p = (e - F::OFF_W3) % H2 + 1;
-      for (int sl = 0; sl < 8; ++sl) s += G[(K::G_W3 + (p & 3)) * 32 + sl * 4 + (p >> 2)];
-      if (r == 1) s = -s;
-    } else {  // b3 [2]
-      for (int l = 0; l < 32; ++l) s += G[K::G_B3 * 32 + l];
-      if (e - F::OFF_B3 == 1) s = -s;
-    }
-    part[3 + e] = s;
-  }
+  for (int e = lane; e < K::NPARAM; e += 32) part[3 + e] = sf2r_partial_entry<K>(G, e);
 }
 
 // ---- host side --------------------------------------------------------------------------------------------------
@@ -283,6 +288,56 @@ struct SF2RConstGuard {
 inline SF2RConstGuard& sf2r_const_guard() {
   static SF2RConstGuard g = {};
   return g;
+}
+
+// stage the packed weights into the constant bank and launch the main kernel (`launch()`), ordered as described above
+template <class K, class F>
+int sf2r_launch_guarded(const float* params, float* packed, cudaStream_t st, F launch) {
+#if GPF_SF2R_CONST
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) {
+    cudaGetLastError();
+    return GPFLOW_ERR_CUDA;
+  }
+  SF2RConstGuard& g = sf2r_const_guard();
+  std::lock_guard<std::mutex> lk(g.mu);
+  cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+  if (cudaStreamIsCapturing(st, &cs) != cudaSuccess) {
+    cudaGetLastError();
+    cs = cudaStreamCaptureStatusNone;
+  }
+  const bool guard = cs == cudaStreamCaptureStatusNone;
+  if (guard) {
+    if (!g.have[dev]) {
+      if (cudaEventCreateWithFlags(&g.ev[dev], cudaEventDisableTiming) != cudaSuccess) {
+        cudaGetLastError();
+        return GPFLOW_ERR_CUDA;
+      }
+      g.have[dev] = true;
+    } else if (cudaStreamWaitEvent(st, g.ev[dev], 0) != cudaSuccess) {
+      cudaGetLastError();
+      return GPFLOW_ERR_CUDA;
+    }
+  }
+  sf2r_pack_kernel<K><<<5, 128, 0, st>>>(params, packed);
+  if (cudaGetLastError() != cudaSuccess) return GPFLOW_ERR_CUDA;
+  if (cudaMemcpyToSymbolAsync(sf2r_cw, packed, 640 * 4, 0, cudaMemcpyDeviceToDevice, st) != cudaSuccess) {
+    cudaGetLastError();
+    return GPFLOW_ERR_CUDA;
+  }
+  launch();
+  if (cudaGetLastError() != cudaSuccess) return GPFLOW_ERR_CUDA;
+  if (guard && cudaEventRecord(g.ev[dev], st) != cudaSuccess) {
+    cudaGetLastError();
+    return GPFLOW_ERR_CUDA;
+  }
+  return GPFLOW_OK;
+#else
+  (void)params;
+  (void)packed;
+  launch();
+  return cudaGetLastError() == cudaSuccess ? GPFLOW_OK : GPFLOW_ERR_CUDA;
+#endif
 }
 
 template <int H1, int H2>
@@ -324,51 +379,8 @@ int launch_sf2r(const GpFlowDesc* d, const Ptrs<float>& p, int64_t B, void* ws, 
   a.t0 = rev ? (float)(d->dt * (double)d->n_steps_nominal) : 0.0f;  // res_net.py:217-219
   a.sigma = (float)d->sigma;
   a.loss_scale = (float)d->loss_scale;
-#if GPF_SF2R_CONST
-  {
-    int dev = 0;
-    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) {
-      cudaGetLastError();
-      return GPFLOW_ERR_CUDA;
-    }
-    SF2RConstGuard& g = sf2r_const_guard();
-    std::lock_guard<std::mutex> lk(g.mu);
-    cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
-    if (cudaStreamIsCapturing(st, &cs) != cudaSuccess) {
-      cudaGetLastError();
-      cs = cudaStreamCaptureStatusNone;
-    }
-    const bool guard = cs == cudaStreamCaptureStatusNone;
-    if (guard) {
-      if (!g.have[dev]) {
-        if (cudaEventCreateWithFlags(&g.ev[dev], cudaEventDisableTiming) != cudaSuccess) {
-          cudaGetLastError();
-          return GPFLOW_ERR_CUDA;
-        }
-        g.have[dev] = true;
-      } else if (cudaStreamWaitEvent(st, g.ev[dev], 0) != cudaSuccess) {
-        cudaGetLastError();
-        return GPFLOW_ERR_CUDA;
-      }
-    }
-    sf2r_pack_kernel<K><<<5, 128, 0, st>>>(p.params, packed);
-    if (cudaGetLastError() != cudaSuccess) return GPFLOW_ERR_CUDA;
-    if (cudaMemcpyToSymbolAsync(sf2r_cw, packed, 640 * 4, 0, cudaMemcpyDeviceToDevice, st) != cudaSuccess) {
-      cudaGetLastError();
-      return GPFLOW_ERR_CUDA;
-    }
-    kern<<<(unsigned)grid, NW * 32, smem, st>>>(a);
-    if (cudaGetLastError() != cudaSuccess) return GPFLOW_ERR_CUDA;
-    if (guard && cudaEventRecord(g.ev[dev], st) != cudaSuccess) {
-      cudaGetLastError();
-      return GPFLOW_ERR_CUDA;
-    }
-  }
-#else
-  (void)packed;
-  kern<<<(unsigned)grid, NW * 32, smem, st>>>(a);
-  if (cudaGetLastError() != cudaSuccess) return GPFLOW_ERR_CUDA;
-#endif
+  const int rc = sf2r_launch_guarded<K>(p.params, packed, st, [&]() { kern<<<(unsigned)grid, NW * 32, smem, st>>>(a); });
+  if (rc != GPFLOW_OK) return rc;
   gpflow_finalize_kernel<float><<<(npart + 127) / 128, 128, 0, st>>>(a.partials, (int)slots, npart, npart, p.scalars_out,
                                                                      p.grads_out);
   if (cudaGetLastError() != cudaSuccess) return GPFLOW_ERR_CUDA;
