@@ -56,6 +56,11 @@ GPF_DEV float4 ldsw4(const float* p) {
   asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(smem_u32(p)));
   return v;
 }
+GPF_DEV float ldsw1(const float* p) {
+  float v;
+  asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(smem_u32(p)));
+  return v;
+}
 // GPF_SF2_CONST: 0 = packed weights in shared memory (LDS.128, 2 shared-memory wavefronts per warp-uniform load),
 // 1 = packed weights in the constant bank (no shared-memory traffic; with unrolled contractions the FFMA reads its
 // weight operand straight from c[][] and the load instruction disappears).

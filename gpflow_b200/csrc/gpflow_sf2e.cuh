@@ -18,6 +18,16 @@
 
 namespace gpflow {
 
+// rolled contraction loops of the dual evaluations: unroll factor, and where their weight rows come from (a bit of
+// GPF_SF2R_CONST: 1 = constant bank like the unrolled plain forward evaluation, 2 = shared memory).  Measured on the C4
+// Euler row (tools/sf2e_ab.sh): unroll 1 / 3 / 5 and either source are all 157.6-159.2 ms -- the kernel is bound by
+// dependency latency at 2 warps per scheduler, not by these loops.
+#ifndef GPF_SF2E_UNROLL
+#define GPF_SF2E_UNROLL 1
+#endif
+#ifndef GPF_SF2E_WBIT
+#define GPF_SF2E_WBIT 2
+#endif
 typedef float2 du;  // dual number: .x = value, .y = epsilon part
 GPF_DEV du d_make(float v, float e) { return make_float2(v, e); }
 GPF_DEV du d_add(du a, du b) { return make_float2(a.x + b.x, a.y + b.y); }
@@ -77,9 +87,12 @@ GPF_DEV void sf2e_closed_form(du X0, du X1, du psi, du G0, du G1, float bnd, du&
 // ---------------------------------------------------------------------------------------------------------
 // dual forward: V(X, ts), X = (x, direction).  Writes the dual stash row of this lane's sample.
 // ---------------------------------------------------------------------------------------------------------
+// Wrow: this lane's work row (free during the forward sweep): scratch for ws, so that the two contractions can be ROLLED
+// loops over the contraction index (the fully unrolled evaluation was 1 500 instructions; with plain + dual, forward +
+// reverse the kernel outgrew the instruction cache: no_instruction was the top stall, profiles/r2_sf2e_*).
 template <class K>
-GPF_DEV void sf2e_forward_eval(const float* __restrict__ W, float* __restrict__ Drow, int l7, du X0, du X1, float ts, float bnd,
-                               du& V0, du& V1) {
+GPF_DEV void sf2e_forward_eval(const float* __restrict__ W, float* __restrict__ Drow, float* __restrict__ Wrow, int l7, du X0,
+                               du X1, float ts, float bnd, du& V0, du& V1) {
   typedef typename K::R R;
   constexpr int H1 = K::H1, H2 = K::H2;
   du hp[16];  // by position
@@ -105,12 +118,13 @@ GPF_DEV void sf2e_forward_eval(const float* __restrict__ W, float* __restrict__ 
 #pragma unroll
     for (int k = 0; k < 16; ++k) a2[k] = d_make(b2[k], 0.0f);
   }
-#pragma unroll
+#pragma unroll GPF_SF2E_UNROLL
   for (int p = 1; p <= H1; ++p) {
     float wr[16];
-    load_w16s<1>(W, R::W2F + 16 * p, wr);
+    load_w16s<GPF_SF2E_WBIT>(W, R::W2F + 16 * p, wr);
+    const du h = *(reinterpret_cast<const float2*>(Drow + dsw_chunk(p >> 1, l7)) + (p & 1));   // hp[p], just stored
 #pragma unroll
-    for (int k = 0; k < H2; ++k) a2[k] = d_fma(wr[k], hp[p], a2[k]);
+    for (int k = 0; k < H2; ++k) a2[k] = d_fma(wr[k], h, a2[k]);
   }
   // ---- activation 2, collapsed output row
   du h2p[16], ws[16];  // by position
@@ -134,17 +148,21 @@ GPF_DEV void sf2e_forward_eval(const float* __restrict__ W, float* __restrict__ 
     }
   }
 #pragma unroll
-  for (int c = 0; c < 8; ++c) sts4(Drow + dsw_chunk(8 + c, l7), h2p[2 * c].x, h2p[2 * c].y, h2p[2 * c + 1].x, h2p[2 * c + 1].y);
+  for (int c = 0; c < 8; ++c) {
+    sts4(Drow + dsw_chunk(8 + c, l7), h2p[2 * c].x, h2p[2 * c].y, h2p[2 * c + 1].x, h2p[2 * c + 1].y);
+    sts4(Wrow + 4 * c, ws[2 * c].x, ws[2 * c].y, ws[2 * c + 1].x, ws[2 * c + 1].y);
+  }
   // ---- z = W2^T ws, by position of h1
   du z[16];
 #pragma unroll
   for (int pm = 0; pm < 16; ++pm) z[pm] = d_make(0.0f, 0.0f);
-#pragma unroll
+#pragma unroll GPF_SF2E_UNROLL
   for (int p = 1; p <= H2; ++p) {
     float wr[16];
-    load_w16s<1>(W, R::W2B + 16 * p, wr);
+    load_w16s<GPF_SF2E_WBIT>(W, R::W2B + 16 * p, wr);
+    const du wsp = *reinterpret_cast<const float2*>(Wrow + 2 * p);
 #pragma unroll
-    for (int pm = 1; pm <= H1; ++pm) z[pm] = d_fma(wr[pm], ws[p], z[pm]);
+    for (int pm = 1; pm <= H1; ++pm) z[pm] = d_fma(wr[pm], wsp, z[pm]);
   }
   // ---- grad psi = W1x^T (sp1 (.) z)
   du G0 = d_make(0.0f, 0.0f), G1 = d_make(0.0f, 0.0f);

@@ -147,7 +147,7 @@ __global__ void __launch_bounds__(NW * 32, 1) gpflow_sf2e_kernel(const SF2EArgs 
           P1 = d_fma(delta, V1, P1);
         }
         float* const reg = begin_op();
-        sf2e_forward_eval<K>(W, reg + lane * K::DROW, l7, P0, P1, second ? t + delta : t, bnd, V0, V1);
+        sf2e_forward_eval<K>(W, reg + lane * K::DROW, Wk + lane * K::WS, l7, P0, P1, second ? t + delta : t, bnd, V0, V1);
         end_op(reg, i, 4 + e);
         if (second) {
           const float a0 = (V0.y - V10.y) * rdelta, a1 = (V1.y - V11.y) * rdelta;   // eps part of a along the direction

@@ -58,44 +58,38 @@ GPF_DEV void sf2e_reverse_eval(const float* __restrict__ W, float* __restrict__ 
 #pragma unroll
   for (int pm = 0; pm < 16; ++pm) hb[pm] = z[pm] = d_make(0.0f, 0.0f);
   du psi = d_make(ldwr4<4>(W, R::B3C).x, 0.0f);
-  float ev[16];
-  ev[0] = 0.0f;
-  {
-    float w3[16];
-    load_w16s<4>(W, R::W3P, w3);
-    sts4(Wrow + K::O_L, 0.0f, 0.0f, 0.0f, 0.0f);   // position 0 of the left factor (and of ab1 / q later: unit 15 pad)
+  Wrow[K::O_E] = 0.0f;
+  sts4(Wrow + K::O_L, 0.0f, 0.0f, 0.0f, 0.0f);   // position 0 of the left factor
+  for (int p = H2 + 1; p < 16; ++p) {            // positions beyond the last unit (none for H2 = 15)
+    Wrow[K::O_E + p] = 0.0f;
+    *reinterpret_cast<float2*>(Wrow + K::O_L + 2 * p) = make_float2(0.0f, 0.0f);
+  }
+#pragma unroll GPF_SF2E_UNROLL
+  for (int p = 1; p <= H2; ++p) {   // ROLLED over the rows of W2 (code size, see sf2e_forward_eval)
+    float wr[16];
+    load_w16s<2>(W, R::W2B + 16 * p, wr);
+    du ta = d_scale(wr[1], cq[1]), tc = d_scale(wr[2], cq[2]), td = d_scale(wr[3], cq[3]);
 #pragma unroll
-    for (int p = 1; p < 16; ++p) {
-      if (p - 1 < H2) {
-        float wr[16];
-        load_w16s<2>(W, R::W2B + 16 * p, wr);
-        du ta = d_scale(wr[1], cq[1]), tc = d_scale(wr[2], cq[2]), td = d_scale(wr[3], cq[3]);
-#pragma unroll
-        for (int j = 1; j < 5; ++j) {
-          ta = d_fma(wr[3 * j + 1], cq[3 * j + 1], ta);
-          tc = d_fma(wr[3 * j + 2], cq[3 * j + 2], tc);
-          td = d_fma(wr[3 * j + 3], cq[3 * j + 3], td);
-        }
-        const du tb = d_add(d_add(ta, tc), td);
-        float2* const hslot = reinterpret_cast<float2*>(Drow + dsw_chunk(8 + (p >> 1), l7)) + (p & 1);
-        const du h2 = *hslot, sp = d_sp(h2);
-        ev[p] = fmaf(psib.x, h2.y, fmaf(psib.y, h2.x, fmaf(sp.x, tb.y, sp.y * tb.x)));   // eps part of psib h2 + sp2 tb
-        const du wsp = d_scale(w3[p], sp);
-        const du ab = d_mul(wsp, d_sub(psib, d_scale(2.0f, d_mul(h2, tb))));
-        psi = d_fma(w3[p], h2, psi);
-#pragma unroll
-        for (int pm = 1; pm <= H1; ++pm) {
-          hb[pm] = d_fma(wr[pm], ab, hb[pm]);
-          z[pm] = d_fma(wr[pm], wsp, z[pm]);
-        }
-        *hslot = wsp;                                                                   // left factor of term 2: (v, e)
-        *reinterpret_cast<float2*>(Wrow + K::O_L + 2 * p) = make_float2(ab.y, ab.x);   // left factor of term 1: (e, v)
-      } else {
-        ev[p] = 0.0f;
-        *reinterpret_cast<float2*>(Wrow + K::O_L + 2 * p) = make_float2(0.0f, 0.0f);
-      }
-      if ((p & 3) == 3) sts4(Wrow + K::O_E + (p - 3), ev[p - 3], ev[p - 2], ev[p - 1], ev[p]);
+    for (int j = 1; j < 5; ++j) {
+      ta = d_fma(wr[3 * j + 1], cq[3 * j + 1], ta);
+      tc = d_fma(wr[3 * j + 2], cq[3 * j + 2], tc);
+      td = d_fma(wr[3 * j + 3], cq[3 * j + 3], td);
     }
+    const du tb = d_add(d_add(ta, tc), td);
+    const float w3p = ldsw1(W + R::W3P + p);
+    float2* const hslot = reinterpret_cast<float2*>(Drow + dsw_chunk(8 + (p >> 1), l7)) + (p & 1);
+    const du h2 = *hslot, sp = d_sp(h2);
+    Wrow[K::O_E + p] = fmaf(psib.x, h2.y, fmaf(psib.y, h2.x, fmaf(sp.x, tb.y, sp.y * tb.x)));   // eps part of psib h2 + sp2 tb
+    const du wsp = d_scale(w3p, sp);
+    const du ab = d_mul(wsp, d_sub(psib, d_scale(2.0f, d_mul(h2, tb))));
+    psi = d_fma(w3p, h2, psi);
+#pragma unroll
+    for (int pm = 1; pm <= H1; ++pm) {
+      hb[pm] = d_fma(wr[pm], ab, hb[pm]);
+      z[pm] = d_fma(wr[pm], wsp, z[pm]);
+    }
+    *hslot = wsp;                                                                   // left factor of term 2: (v, e)
+    *reinterpret_cast<float2*>(Wrow + K::O_L + 2 * p) = make_float2(ab.y, ab.x);   // left factor of term 1: (e, v)
   }
   // ---- eps part of dW2[pk][pm] = sum_s ab2.v h1.e + ab2.e h1.v + ws.v c.e + ws.e c.v: a rank-64 update over the 16 samples
   //      with bit 0 == slice; the pair accumulators hold the two halves of each entry
