@@ -28,6 +28,7 @@ namespace gpflow {
 #ifndef GPF_SF2E_WBIT
 #define GPF_SF2E_WBIT 2
 #endif
+constexpr int kSF2EUnroll = GPF_SF2E_UNROLL;
 typedef float2 du;  // dual number: .x = value, .y = epsilon part
 GPF_DEV du d_make(float v, float e) { return make_float2(v, e); }
 GPF_DEV du d_add(du a, du b) { return make_float2(a.x + b.x, a.y + b.y); }
@@ -118,7 +119,7 @@ GPF_DEV void sf2e_forward_eval(const float* __restrict__ W, float* __restrict__ 
 #pragma unroll
     for (int k = 0; k < 16; ++k) a2[k] = d_make(b2[k], 0.0f);
   }
-#pragma unroll GPF_SF2E_UNROLL
+#pragma unroll kSF2EUnroll
   for (int p = 1; p <= H1; ++p) {
     float wr[16];
     load_w16s<GPF_SF2E_WBIT>(W, R::W2F + 16 * p, wr);
@@ -156,7 +157,7 @@ GPF_DEV void sf2e_forward_eval(const float* __restrict__ W, float* __restrict__ 
   du z[16];
 #pragma unroll
   for (int pm = 0; pm < 16; ++pm) z[pm] = d_make(0.0f, 0.0f);
-#pragma unroll GPF_SF2E_UNROLL
+#pragma unroll kSF2EUnroll
   for (int p = 1; p <= H2; ++p) {
     float wr[16];
     load_w16s<GPF_SF2E_WBIT>(W, R::W2B + 16 * p, wr);

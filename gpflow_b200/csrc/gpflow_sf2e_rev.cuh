@@ -64,7 +64,7 @@ GPF_DEV void sf2e_reverse_eval(const float* __restrict__ W, float* __restrict__ 
     Wrow[K::O_E + p] = 0.0f;
     *reinterpret_cast<float2*>(Wrow + K::O_L + 2 * p) = make_float2(0.0f, 0.0f);
   }
-#pragma unroll GPF_SF2E_UNROLL
+#pragma unroll kSF2EUnroll
   for (int p = 1; p <= H2; ++p) {   // ROLLED over the rows of W2 (code size, see sf2e_forward_eval)
     float wr[16];
     load_w16s<2>(W, R::W2B + 16 * p, wr);
