@@ -16,7 +16,12 @@ struct SF2EArgs {
   float euler_coef;
 };
 
-constexpr int kSF2EWarps = 8;   // 255 registers per thread, 28 KB of shared memory per warp
+// 8 warps: 255 registers per thread (no spills), 28 KB of shared memory per warp (two 8 KB stash regions + work rows).
+// Measured alternative (profiles/r2_sf2e_ncu_summary.txt): ONE stash region (plain evaluations alternate between its halves,
+// dual rows single-buffered) and 84-float work rows fit 12 warps at 168 registers: 155.9 vs 157.6 ms on the C4 Euler row and
+// slower at small batches -- 750 B of spills, and with 12 warps spread over 7 000 instructions of code `no_instruction` is
+// back at 0.62 stall cycles per issue (0.18 with 8 warps).  Not kept.
+constexpr int kSF2EWarps = 8;
 
 template <int H1, int H2, int NW>
 __global__ void __launch_bounds__(NW * 32, 1) gpflow_sf2e_kernel(const SF2EArgs ea) {
