@@ -47,6 +47,7 @@ struct SF2Args {
   float t0;
   float sigma;
   float loss_scale;
+  int stagger_cycles;  // sf2r: warps of the upper half start this many cycles late (GPFLOW_SF2R_STAGGER, experiments)
 };
 
 // weights never change after the prologue: volatile asm keeps each (warp-uniform) load next to its use instead of

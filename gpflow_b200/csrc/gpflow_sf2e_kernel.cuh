@@ -368,8 +368,8 @@ int launch_sf2e(const GpFlowDesc* d, const Ptrs<float>& p, int64_t B, void* ws, 
   ea.euler_coef = (float)d->euler_coef;
   const int rc = sf2r_launch_guarded<R>(p.params, packed, st, [&]() { kern<<<(unsigned)grid, NW * 32, smem, st>>>(ea); });
   if (rc != GPFLOW_OK) return rc;
-  gpflow_finalize_kernel<float><<<(npart + 127) / 128, 128, 0, st>>>(a.partials, (int)slots, npart, npart, p.scalars_out,
-                                                                     p.grads_out);
+  gpflow_finalize_wide_kernel<float><<<(npart + 31) / 32, 256, 0, st>>>(a.partials, (int)slots, npart, npart, p.scalars_out,
+                                                                        p.grads_out);
   if (cudaGetLastError() != cudaSuccess) return GPFLOW_ERR_CUDA;
   return GPFLOW_OK;
 }

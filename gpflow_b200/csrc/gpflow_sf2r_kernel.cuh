@@ -104,6 +104,13 @@ __global__ void __launch_bounds__(NW * 32, 1) gpflow_sf2r_kernel(const SF2Args a
   for (int i = 0; i < 4; ++i) acc3[i] = 0.0f;
 
   const long long ntiles = (a.B + 31) / 32;
+  if (a.stagger_cycles != 0) {
+    // > 0: odd warps start `stagger_cycles` late; < 0: warp w starts (w * 5 mod NW) / NW * |stagger_cycles| late
+    const long long wait = a.stagger_cycles > 0 ? ((warp & 1) ? a.stagger_cycles : 0)
+                                                : (long long)(-a.stagger_cycles) * ((warp * 5) % NW) / NW;
+    const long long t0 = clock64();
+    while (clock64() - t0 < wait) __nanosleep(256);
+  }
   for (long long tile = slot; tile < ntiles; tile += nslots) {
     const long long b = tile * 32 + lane;
     const bool valid = b < a.B;
@@ -379,10 +386,16 @@ int launch_sf2r(const GpFlowDesc* d, const Ptrs<float>& p, int64_t B, void* ws, 
   a.t0 = rev ? (float)(d->dt * (double)d->n_steps_nominal) : 0.0f;  // res_net.py:217-219
   a.sigma = (float)d->sigma;
   a.loss_scale = (float)d->loss_scale;
+  // All warps of an SM start their first tile together and would run the FMA-heavy forward sweeps and the shared-memory-
+  // heavy reverse sweeps in phase; spreading their start over ~half a tile time (one tile = 120 evaluations, ~50 k cycles
+  // per RK4 step) was measured at -2.4 % on a 2^21-sample launch and -0.3 % at 2^24 (GPFLOW_SF2R_STAGGER = cycles,
+  // 0 = off; negative = spread over the warps, positive = odd warps late).  Only when every warp has >= 4 tiles.
+  static const int stagger_env = [] { const char* e = getenv("GPFLOW_SF2R_STAGGER"); return e ? atoi(e) : 1; }();
+  a.stagger_cycles = stagger_env != 1 ? stagger_env : (tiles >= 4 * slots ? -26000 * d->n_steps : 0);
   const int rc = sf2r_launch_guarded<K>(p.params, packed, st, [&]() { kern<<<(unsigned)grid, NW * 32, smem, st>>>(a); });
   if (rc != GPFLOW_OK) return rc;
-  gpflow_finalize_kernel<float><<<(npart + 127) / 128, 128, 0, st>>>(a.partials, (int)slots, npart, npart, p.scalars_out,
-                                                                     p.grads_out);
+  gpflow_finalize_wide_kernel<float><<<(npart + 31) / 32, 256, 0, st>>>(a.partials, (int)slots, npart, npart, p.scalars_out,
+                                                                        p.grads_out);
   if (cudaGetLastError() != cudaSuccess) return GPFLOW_ERR_CUDA;
   return GPFLOW_OK;
 }
