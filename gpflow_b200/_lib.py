@@ -24,7 +24,7 @@ SCALAR_OT, SCALAR_REG, SCALAR_LAGR, NUM_SCALARS = 0, 1, 2, 3
 
 EXPORTS = [
     "gpflow_param_count", "gpflow_query_workspace", "gpflow_forward", "gpflow_train_step", "gpflow_backward",
-    "gpflow_velocity", "gpflow_velocity_static", "gpflow_kernel_variant", "gpflow_launch_count", "gpflow_tc_launches_total", "gpflow_tc_slab_samples", "gpflow_fp32_fma_burn", "gpflow_tf32_mma_burn", "gpflow_clock_probe",
+    "gpflow_velocity", "gpflow_velocity_static", "gpflow_potentials", "gpflow_kernel_variant", "gpflow_launch_count", "gpflow_tc_launches_total", "gpflow_tc_slab_samples", "gpflow_fp32_fma_burn", "gpflow_tf32_mma_burn", "gpflow_clock_probe",
     "gpflow_adam_step", "gpflow_bnaf_param_count", "gpflow_bnaf_forward", "gpflow_ffjord_param_count",
     "gpflow_ffjord_integrate", "gpflow_error_string",
     "gpflow_abi_version",
@@ -100,6 +100,8 @@ def load():
     lib.gpflow_velocity.argtypes = [D, ctypes.c_int64, P, P, ctypes.c_double, P, P, ctypes.c_size_t, P]
     lib.gpflow_velocity_static.restype = ctypes.c_int
     lib.gpflow_velocity_static.argtypes = [D, ctypes.c_int64, P, P, ctypes.c_double, P, P]
+    lib.gpflow_potentials.restype = ctypes.c_int
+    lib.gpflow_potentials.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.POINTER(ctypes.c_int32), ctypes.c_int64, P, P, P, P, P]
     lib.gpflow_kernel_variant.restype = ctypes.c_int
     lib.gpflow_kernel_variant.argtypes = [D, ctypes.c_int, ctypes.c_char_p, ctypes.c_size_t]
     lib.gpflow_launch_count.restype = ctypes.c_int

@@ -38,7 +38,21 @@ def velocity_static(cfg, flat_params: torch.Tensor, x: torch.Tensor, t, out: tor
     return out
 
 
-def potentials(vfield, x):
-    raise NotImplementedError(
-        "gpflow_b200: VectorField.eval/.jacobian are evaluated inside the fused velocity kernels; a standalone "
-        "potentials op is not exported")
+def potentials(vfield, x, want_f=True, want_jac=True):
+    """VectorField.eval / .jacobian (vector_field.py:75-128) on the GPU: (f [B, dim_out], J [B, dim_out, dim_in]).
+    `x` has the network's full input width (the velocity field feeds it [x; t]).  Not differentiable: the fused flow ops
+    carry the gradients of the path."""
+    x2 = ops._check_cuda("x", x if x.dim() == 2 else x.reshape(1, -1))
+    widths = (ctypes.c_int32 * len(vfield.neurons))(*vfield.neurons)
+    if x2.shape[1] != vfield.neurons[0]:
+        raise ValueError("gpflow_b200: x has %d columns, the network takes %d" % (x2.shape[1], vfield.neurons[0]))
+    flat = vfield.flat_parameters().detach().to(x2.dtype)
+    B = x2.shape[0]
+    f = torch.empty(B, vfield.neurons[-1], dtype=x2.dtype, device=x2.device) if want_f else None
+    jac = torch.empty(B, vfield.neurons[-1], vfield.neurons[0], dtype=x2.dtype, device=x2.device) if want_jac else None
+    with torch.cuda.device(x2.device):
+        _lib.check(_lib.load().gpflow_potentials(ops._dtype_code(x2.dtype), len(vfield.neurons) - 1, widths, B, ops._ptr(flat),
+                                                 ops._ptr(x2), ops._ptr(f), ops._ptr(jac), ops._stream()))
+    if x.dim() == 1:
+        f, jac = (None if f is None else f[0]), (None if jac is None else jac[0])
+    return f, jac

@@ -3,8 +3,9 @@
 Same constructor, same `denses` ModuleList of nn.Linear (so `state_dict()` keys stay
 `v.v.denses.{i}.weight|bias`, SURVEY.md section 5 "Checkpoint / resume"), same initialisation
 (N(0, 1e-3) weights, zero bias; vector_field.py:63-70).  The arithmetic (`eval`, `jacobian`,
-vector_field.py:75-128) is NOT re-implemented in torch here: it lives inside the CUDA kernels, which read
-the flat parameter vector `[W_1, b_1, ..., W_{L+1}, b_{L+1}]`.
+vector_field.py:75-128) is NOT re-implemented in torch here: it lives inside the fused CUDA kernels, which read
+the flat parameter vector `[W_1, b_1, ..., W_{L+1}, b_{L+1}]`; the standalone `eval` / `jacobian` / `__call__` of this class
+go through `gpflow_potentials` (csrc/gpflow_potentials.cu).
 """
 import torch
 import torch.nn as nn
@@ -33,11 +34,11 @@ class VectorField(nn.Module):
 
     def eval(self, x):  # noqa: A003 - reference method name
         from .ops_aux import potentials
-        return potentials(self, x)[0]
+        return potentials(self, x, want_jac=False)[0]
 
     def jacobian(self, x):
         from .ops_aux import potentials
-        return potentials(self, x)[1]
+        return potentials(self, x, want_f=False)[1]
 
     def __call__(self, x):
         return self.eval(x)

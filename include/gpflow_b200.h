@@ -152,6 +152,17 @@ int gpflow_velocity(const GpFlowDesc* desc, int64_t B, const void* params, const
                     void* workspace, size_t workspace_bytes, void* cuda_stream);
 
 /*
+ * Standalone VectorField.eval / VectorField.jacobian (src/gp_flows/vector_field.py:75-128; reference test
+ * tests/test_vector_field.py:15-25): the tanh MLP with `n_linear` nn.Linear layers of widths
+ * widths[0] (= dim_in, the velocity field passes [x; t]) ... widths[n_linear] (= dim_out), flat parameters
+ * [W_1, b_1, ...] as everywhere else.  f_out [B, dim_out] and / or jac_out [B, dim_out, dim_in] (either may be NULL).
+ * Not on the hot path: the fused kernels evaluate both inside the velocity.  One launch, no workspace;
+ * GPFLOW_ERR_UNSUPPORTED when two layers of activations + tangents exceed 200 KB of shared memory.
+ */
+int gpflow_potentials(int dtype, int n_linear, const int32_t* widths, int64_t B, const void* params, const void* x,
+                      void* f_out, void* jac_out, void* cuda_stream);
+
+/*
  * gpflow_velocity() for callers that cannot allocate or pass a workspace (code under CUDA graph capture, tight serving
  * loops, harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
  * Same inputs, outputs and results as gpflow_velocity() on the generic kernel family; the scratch is a
