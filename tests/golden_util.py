@@ -16,7 +16,7 @@ def golden_names(tag):
     the bnaf_* / ffjord_* files the frozen-map vectors (make_golden_bnaf.py, make_golden_ffjord.py), compose_* the
     nb_blocks != 1 vectors (make_golden_compose.py), measured_* the bench-configuration vectors (make_golden_measured.py)"""
     names = sorted(os.path.basename(p)[: -len("_%s.npz" % tag)] for p in glob.glob(os.path.join(GOLDEN_DIR, "*_%s.npz" % tag)))
-    return [n for n in names if not n.startswith(("train_", "bnaf_", "ffjord_", "compose_", "measured_", "ot_costs_"))]
+    return [n for n in names if not n.startswith(("train_", "train100_", "bnaf_", "ffjord_", "compose_", "measured_", "ot_costs_"))]
 
 
 def load_golden(name, tag):

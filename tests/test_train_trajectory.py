@@ -85,3 +85,47 @@ def test_cuda_path_replays_reference_training(name):
         opt.step()
     flat = torch.cat([p.detach().reshape(-1) for p in flow.parameters()]).cpu()
     assert rel(flat, g["paramsK"]) < 2e-4, rel(flat, g["paramsK"])
+
+
+# ---- the first 100 optimiser steps of C1 - C3 ------------------------------------------------------------
+# Fixtures: oracle/make_golden_train.py (train100_*: the unmodified reference, batch 256 / 256 / 64; C3 on a synthetic map
+# output because its latent pipeline is out of scope).  Over 100 Adam steps the fp32 rounding differences of the first steps
+# are carried along by the optimiser (Adam divides by sqrt(v), and at the reference's near-identity initialisation the
+# gradients are ~1e-6): measured on a B200 (tools/train100_dev.py) the per-step OT cost stays within 2.4e-5 of the
+# reference's and the parameters after 100 steps within 4.4e-4 (C1), 3.1e-6 (C2 + Euler), 2.5e-5 (C3), while they move by
+# 100 % of their norm.  Already at step 0 (identical parameters) the 256-sample OT cost is 1.9e-5 from the reference's: these
+# small batches contain tail samples whose erfinv amplifies fp32 rounding (tests/test_sf2_parity.py).
+# Bars: 5e-5 on every per-step OT cost, 2e-3 on the weights after 100 steps.
+CASES100 = ["train100_c1_eight_gaussians", "train100_c2_moons_euler", "train100_c3_latent_synthetic"]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", CASES100)
+def test_cuda_path_replays_100_reference_steps(name):
+    import gpflow_b200 as G
+    g = _load(name)
+    euler = g["euler"]
+    d, nb, hidden = int(g["d"]), int(g["nb"]), [int(h) for h in g["hidden"]]
+    flow = G.get_gp_flow(d, {"nb_neurons": hidden, "nb_div_blocks": nb}, 15,
+                         euler_dict={"use_euler": euler is not None, "case": "penalization",
+                                     "coef_penalization": euler}).cuda()
+    off, flat0 = 0, torch.from_numpy(g["params0"])
+    with torch.no_grad():
+        for p in flow.parameters():
+            p.copy_(flat0[off:off + p.numel()].view_as(p)); off += p.numel()
+    net = G.GPFlowNetwork(flow, map_module=None)
+    opt = torch.optim.Adam(flow.parameters(), lr=2e-3, betas=(0.9, 0.999), weight_decay=1e-4)   # network.py:312-317
+    K = int(g["K"])
+    assert K == 100
+    for k in range(K):
+        torch.manual_seed(5000 + k)                 # the wrapper draws z, w with the reference's RNG calls
+        loss, reg = net.fused_training_step(torch.from_numpy(g["x"][k]).cuda(), torch.from_numpy(g["x_map"][k]).cuda())
+        assert abs(float(loss) - g["ot"][k]) < 5e-5 * abs(g["ot"][k]), (k, float(loss), g["ot"][k])
+        if euler is not None:
+            assert abs(float(reg) - g["reg"][k]) < 1e-6 * abs(g["ot"][k])
+        else:
+            assert float(reg) == 0.0
+        opt.step()
+    flat = torch.cat([p.detach().reshape(-1) for p in flow.parameters()]).cpu()
+    assert rel(flat, g["paramsK"]) < 2e-3, rel(flat, g["paramsK"])
+    assert rel(flat, flat0) > 0.5                     # the parameters really moved
