@@ -517,7 +517,8 @@ inline void tc_carve(const TcDims& g, int n_steps, bool train, int sm_count, TcB
   b.scal = take(4);
   b.grads_end = off;
   // two-stage reductions over the samples (fixed order): nz splits of the slab, partials [nz][n]
-  b.nz = S / 64 < 32 ? S / 64 : 32;
+  static const int nz_max = [] { const char* e = getenv("GPFLOW_TC_NZ"); const int v = e ? atoi(e) : 0; return v >= 1 ? v : 128; }();   // C3 row: 70.8 ms at 32, 67.9 at 64, 67.6 at 128, 67.4 at 256
+  b.nz = S / 64 < nz_max ? S / 64 : nz_max;
   b.s_per_z = (S + b.nz - 1) / b.nz;
   if (train) {
     size_t n = (size_t)g.Hp[1] * (d + 2);
