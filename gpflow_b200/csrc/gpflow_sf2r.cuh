@@ -126,7 +126,7 @@ GPF_DEV void load_w16(const float* W, int off, float2 (&wp)[8]) {
 // ---------------------------------------------------------------------------------------------------------
 // forward: v(x, ts).  Writes the stash row (x0, h1 | x1, h2) of this lane's sample.
 // ---------------------------------------------------------------------------------------------------------
-template <class K>
+template <class K, bool STASH = true>
 GPF_DEV void sf2r_forward_eval(const float* __restrict__ W, float* __restrict__ Srow, int l7, float x0, float x1, float ts,
                                float bnd, float& v0, float& v1) {
   constexpr int H1 = K::H1, H2 = K::H2;
@@ -142,8 +142,10 @@ GPF_DEV void sf2r_forward_eval(const float* __restrict__ W, float* __restrict__ 
       hp[m + 1] = 0.0f;
     }
   }
+  if (STASH) {
 #pragma unroll
-  for (int c = 0; c < 4; ++c) sts4(Srow + sw_chunk(c, l7), hp[4 * c], hp[4 * c + 1], hp[4 * c + 2], hp[4 * c + 3]);
+    for (int c = 0; c < 4; ++c) sts4(Srow + sw_chunk(c, l7), hp[4 * c], hp[4 * c + 1], hp[4 * c + 2], hp[4 * c + 3]);
+  }
   // ---- layer 2 (position p unrolled): a2 = b2 + W2 h1 as packed fp32x2 FMAs, two output units per instruction
   float2 a2p[8];
   load_w16<1>(W, K::W2F, a2p);  // position 0: the bias row times 1
@@ -177,7 +179,7 @@ GPF_DEV void sf2r_forward_eval(const float* __restrict__ W, float* __restrict__ 
         h2p[p] = ws[p] = 0.0f;
       }
     }
-    sts4(Srow + sw_chunk(4 + c, l7), h2p[4 * c], h2p[4 * c + 1], h2p[4 * c + 2], h2p[4 * c + 3]);
+    if (STASH) sts4(Srow + sw_chunk(4 + c, l7), h2p[4 * c], h2p[4 * c + 1], h2p[4 * c + 2], h2p[4 * c + 3]);
   }
   // ---- z = W2^T ws (position p of h2 unrolled); zp by position of h1
   float2 zp[8];

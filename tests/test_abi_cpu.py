@@ -57,7 +57,7 @@ def test_workspace_query_and_variant_names(lib):
     c4 = FlowConfig(2, 1, (15, 15), 15)
     assert "gpflow_sf2r_kernel<f32,d=2,nb=1,H=[15,15],train>" == kernel_variant(c4)
     assert "gpflow_small_kernel<f32,d=2,nb=1,H=[15,15],train>" == kernel_variant(c4, force_v1=True)
-    assert "gpflow_sf2_kernel<f32,d=2,nb=1,H=[15,15],fwd>" == kernel_variant(c4, op=_lib.OP_FORWARD, lagrangian=True)
+    assert "gpflow_sf2r_fwd_kernel<f32,d=2,nb=1,H=[15,15],fwd>" == kernel_variant(c4, op=_lib.OP_FORWARD, lagrangian=True)
     assert "gpflow_small_kernel<f32,d=2,nb=1,H=[15,15],fwd>" == kernel_variant(c4, op=_lib.OP_FORWARD, force_v1=True)
     assert "gpflow_small_kernel<f64" in kernel_variant(c4, torch.float64, op=_lib.OP_FORWARD)
     assert "generic" in kernel_variant(c4, force_generic=True)
