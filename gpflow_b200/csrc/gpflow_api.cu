@@ -90,7 +90,7 @@ bool sf2e_match(const GpFlowDesc* d, int op) {
   SmallShape s;
   if (!small_match(d, &s) || d->dtype != GPFLOW_F32 || !sf2e_15_15_enabled()) return false;
   if (!(d->flags & GPFLOW_FLAG_EULER_PEN) || (d->flags & (GPFLOW_FLAG_FORCE_V1 | GPFLOW_FLAG_LAGRANGIAN))) return false;
-  return op != GPFLOW_OP_FORWARD && d->n_steps <= 1024;
+  return op != GPFLOW_OP_FORWARD && d->n_steps <= 512;   // 8 x 28 KB of warp buffers + the time table must fit 227 KB
 }
 
 // tc (chunked tensor-core path) takes the wide fp32 shapes without Euler penalization once the batch is large enough to

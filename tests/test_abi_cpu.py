@@ -57,6 +57,9 @@ def test_workspace_query_and_variant_names(lib):
     c4 = FlowConfig(2, 1, (15, 15), 15)
     assert "gpflow_sf2r_kernel<f32,d=2,nb=1,H=[15,15],train>" == kernel_variant(c4)
     assert "gpflow_small_kernel<f32,d=2,nb=1,H=[15,15],train>" == kernel_variant(c4, force_v1=True)
+    assert "gpflow_sf2e_kernel<f32,d=2,nb=1,H=[15,15],train,euler>" == kernel_variant(c4, euler_coef=0.3)
+    assert "gpflow_small_kernel" in kernel_variant(FlowConfig(2, 1, (15, 15), 600), euler_coef=0.3)   # buffers would not fit
+    assert "gpflow_small_kernel" in kernel_variant(c4, torch.float64, euler_coef=0.3)
     assert "gpflow_sf2r_fwd_kernel<f32,d=2,nb=1,H=[15,15],fwd>" == kernel_variant(c4, op=_lib.OP_FORWARD, lagrangian=True)
     assert "gpflow_small_kernel<f32,d=2,nb=1,H=[15,15],fwd>" == kernel_variant(c4, op=_lib.OP_FORWARD, force_v1=True)
     assert "gpflow_small_kernel<f64" in kernel_variant(c4, torch.float64, op=_lib.OP_FORWARD)
