@@ -104,6 +104,7 @@ __constant__ float sf2r_cw[640];
 #define GPF_SF2R_TANH 0
 #endif
 GPF_DEV float sf2r_tanh(float x) { return GPF_SF2R_TANH ? tanh_exp2(x) : tanh_real(x); }
+GPF_DEV float2 sf2r_tanh2(float2 x) { return GPF_SF2R_TANH ? make_float2(tanh_exp2(x.x), tanh_exp2(x.y)) : tanh_real2(x); }
 template <int BIT>
 GPF_DEV float4 ldwr4(const float* W, int off) {
   if (GPF_SF2R_CONST & BIT) return *reinterpret_cast<const float4*>(&sf2r_cw[off]);
@@ -133,13 +134,22 @@ GPF_DEV void sf2r_forward_eval(const float* __restrict__ W, float* __restrict__ 
   // ---- layer 1 (unit m unrolled): h1 = tanh(W1 [x; t] + b1)   (vector_field.py:75-90)
   float hp[16];  // by position: hp[0] = x0, hp[m + 1] = h1[m]
   hp[0] = x0;
+  {
+    float a1[16];
 #pragma unroll
-  for (int m = 0; m < 15; ++m) {
-    if (m < H1) {
-      const float4 w = ldwr4<1>(W, K::W1P + 4 * m);
-      hp[m + 1] = sf2r_tanh(fmaf(w.x, x0, fmaf(w.y, x1, fmaf(w.z, ts, w.w))));
-    } else {
-      hp[m + 1] = 0.0f;
+    for (int m = 0; m < 16; ++m) {
+      if (m < H1) {
+        const float4 w = ldwr4<1>(W, K::W1P + 4 * m);
+        a1[m] = fmaf(w.x, x0, fmaf(w.y, x1, fmaf(w.z, ts, w.w)));
+      } else {
+        a1[m] = 0.0f;
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {   // two units per packed tanh
+      const float2 h = sf2r_tanh2(make_float2(a1[2 * j], a1[2 * j + 1]));
+      if (2 * j < 15) hp[2 * j + 1] = 2 * j < H1 ? h.x : 0.0f;
+      if (2 * j + 1 < 15) hp[2 * j + 2] = 2 * j + 1 < H1 ? h.y : 0.0f;
     }
   }
   if (STASH) {
@@ -162,24 +172,32 @@ GPF_DEV void sf2r_forward_eval(const float* __restrict__ W, float* __restrict__ 
   h2p[0] = x1;
   ws[0] = 0.0f;
   float psi = ldwr4<1>(W, K::B3C).x;
+  {
+    float h2u[16];   // by unit
 #pragma unroll
-  for (int c = 0; c < 4; ++c) {
-    const float4 w3v = ldwr4<1>(W, K::W3P + 4 * c);
-    const float w3[4] = {w3v.x, w3v.y, w3v.z, w3v.w};
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      const int p = 4 * c + i, k = p - 1;
-      if (p >= 1 && k < H2) {
-        const float a = (k & 1) ? a2p[k >> 1].y : a2p[k >> 1].x;
-        const float h = sf2r_tanh(a);
-        psi = fmaf(w3[i], h, psi);
-        ws[p] = w3[i] * fmaf(-h, h, 1.0f);
-        h2p[p] = h;
-      } else if (p >= 1) {
-        h2p[p] = ws[p] = 0.0f;
-      }
+    for (int j = 0; j < 8; ++j) {
+      const float2 h = sf2r_tanh2(a2p[j]);
+      h2u[2 * j] = h.x;
+      h2u[2 * j + 1] = h.y;
     }
-    if (STASH) sts4(Srow + sw_chunk(4 + c, l7), h2p[4 * c], h2p[4 * c + 1], h2p[4 * c + 2], h2p[4 * c + 3]);
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+      const float4 w3v = ldwr4<1>(W, K::W3P + 4 * c);
+      const float w3[4] = {w3v.x, w3v.y, w3v.z, w3v.w};
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int p = 4 * c + i, k = p - 1;
+        if (p >= 1 && k < H2) {
+          const float h = h2u[k];
+          psi = fmaf(w3[i], h, psi);
+          ws[p] = w3[i] * fmaf(-h, h, 1.0f);
+          h2p[p] = h;
+        } else if (p >= 1) {
+          h2p[p] = ws[p] = 0.0f;
+        }
+      }
+      if (STASH) sts4(Srow + sw_chunk(4 + c, l7), h2p[4 * c], h2p[4 * c + 1], h2p[4 * c + 2], h2p[4 * c + 3]);
+    }
   }
   // ---- z = W2^T ws (position p of h2 unrolled); zp by position of h1
   float2 zp[8];
