@@ -62,7 +62,7 @@ __global__ void __launch_bounds__(NW * 32, 1) gpflow_sf2e_kernel(const SF2EArgs 
   float* const Reg0 = wa;                  // stash region r = Reg0 + r * REG_FL (plain rows use its first 4 KB)
   float* const Wk = wa + 2 * K::REG_FL;    // work rows (plain: [32][68], dual: [32][92])
   const int slot = warp * gridDim.x + blockIdx.x, nslots = gridDim.x * NW;
-  constexpr int G_PEN = R::NACC, NACC = R::NACC + 1;
+  constexpr int G_PEN = R::NACC, G_W2D = R::NACC + 1, NACC = R::NACC + 17;   // + penalty, + the dual evaluations' dW2 tile
   float* const G = a.g2 + (size_t)slot * NACC * 32;
   for (int i = 0; i < NACC; ++i) G[i * 32 + lane] = 0.0f;
   __syncthreads();
@@ -82,9 +82,9 @@ __global__ void __launch_bounds__(NW * 32, 1) gpflow_sf2e_kernel(const SF2EArgs 
   uint32_t phbits = 0;
   uint64_t* const mybars = &bars[warp][0];
 
-  float acc[16], accw[16], acc3[4], b3b = 0.0f;
+  float acc[16], accd[16], accw[16], acc3[4], b3b = 0.0f;   // accd: dW2 tile of the dual evaluations (their own lane layout)
 #pragma unroll
-  for (int i = 0; i < 16; ++i) acc[i] = accw[i] = 0.0f;
+  for (int i = 0; i < 16; ++i) acc[i] = accd[i] = accw[i] = 0.0f;
 #pragma unroll
   for (int i = 0; i < 4; ++i) acc3[i] = 0.0f;
 
@@ -240,7 +240,7 @@ __global__ void __launch_bounds__(NW * 32, 1) gpflow_sf2e_kernel(const SF2EArgs 
           }
           float* const rows = next_rows(8 * i + 4 + e);
           du R0, R1;
-          sf2e_reverse_eval<K>(W, rows, Wk, lane, second ? t + delta : t, bnd, S0, S1, R0, R1, acc, accw, acc3, b3b);
+          sf2e_reverse_eval<K>(W, rows, Wk, lane, second ? t + delta : t, bnd, S0, S1, R0, R1, accd, accw, acc3, b3b);
           xb0 += R0.y;
           xb1 += R1.y;
           Yb0 = R0;
@@ -276,8 +276,9 @@ __global__ void __launch_bounds__(NW * 32, 1) gpflow_sf2e_kernel(const SF2EArgs 
 #pragma unroll
     for (int i = 0; i < 16; ++i) {
       G[(R::G_W2 + i) * 32 + lane] += acc[i];
+      G[(G_W2D + i) * 32 + lane] += accd[i];
       G[(R::G_W1 + i) * 32 + lane] += accw[i];
-      acc[i] = accw[i] = 0.0f;
+      acc[i] = accd[i] = accw[i] = 0.0f;
     }
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
@@ -300,7 +301,7 @@ __global__ void __launch_bounds__(NW * 32, 1) gpflow_sf2e_kernel(const SF2EArgs 
     part[1] = pen_ws * pen_w;
     part[2] = 0.0f;
   }
-  for (int e = lane; e < R::NPARAM; e += 32) part[3 + e] = sf2r_partial_entry<R>(G, e);
+  for (int e = lane; e < R::NPARAM; e += 32) part[3 + e] = sf2r_partial_entry<R>(G, e, G + G_W2D * 32);
 }
 
 // ---- host side --------------------------------------------------------------------------------------------------
@@ -313,7 +314,7 @@ size_t sf2e_workspace(const GpFlowDesc* d, int64_t B) {
   const int64_t stash_slots = tiles < slots ? tiles : slots;
   size_t bytes = 640 * 4;
   bytes += align_up((size_t)slots * (3 + K::R::NPARAM) * 4, 256);
-  bytes += align_up((size_t)slots * (K::R::NACC + 1) * 32 * 4, 256);
+  bytes += align_up((size_t)slots * (K::R::NACC + 17) * 32 * 4, 256);
   bytes += align_up((size_t)slots * d->n_steps * 32 * 4, 256);
   bytes += (size_t)stash_slots * d->n_steps * K::STEP_BYTES;
   return bytes;
@@ -353,7 +354,7 @@ int launch_sf2e(const GpFlowDesc* d, const Ptrs<float>& p, int64_t B, void* ws, 
   a.partials = reinterpret_cast<float*>(wsp);
   wsp += align_up((size_t)slots * npart * 4, 256);
   a.g2 = reinterpret_cast<float*>(wsp);
-  wsp += align_up((size_t)slots * (R::NACC + 1) * 32 * 4, 256);
+  wsp += align_up((size_t)slots * (R::NACC + 17) * 32 * 4, 256);
   ea.qbuf = reinterpret_cast<float*>(wsp);
   wsp += align_up((size_t)slots * d->n_steps * 32 * 4, 256);
   a.stash = wsp;

@@ -96,6 +96,14 @@ GPF_DEV float sf2r_pack_value(const float* __restrict__ raw, int i) {
 #define GPF_SF2R_CONST 1   // measured at C4 (tools/sf2r_const_ab.sh): 0: 1.34e8, 1: 1.48e8, 3: 1.47e8, 7: 1.40e8 samples/s
 #endif
 __constant__ float sf2r_cw[640];
+// GPF_SF2R_MMA: 0 (default) = the rank-2 dW2 update of the reverse sweep as FFMA2 register tiles; 1 / 2 = on the tensor
+// cores (mma.sync m16n8k8, 3xTF32; split by cvt.rna / by truncation).  Parity-green and measured SLOWER at C4
+// (tools/sf2r_mma_ab.sh, same box): 111.6 ms (0), 121.8 ms (1), 114.4 ms (2) -- the FMA pipe drops from 67 % to 59 % busy but
+// the 64 fragment loads, 128 split operations and 48 mma per evaluation issue as many instructions as the 64 LDS.128 +
+// 256 FFMA2 they replace, and the kernel is issue-bound as much as FMA-bound (issue slots 67 %).
+#ifndef GPF_SF2R_MMA
+#define GPF_SF2R_MMA 0
+#endif
 // GPF_SF2R_TANH: 0 = tanh_real (<= 2 ulp relative, default), 1 = tanh_exp2 (absolute accuracy ~3e-7).  Measured at C4
 // (tools/sf2r_tanh_ab.sh): 1.46e8 vs 1.60e8 samples/s and the same errors against the fp64 oracle at weights N(0, 0.1..0.6^2),
 // but at the reference's own initialisation (weights N(0, 1e-3^2): |a| ~ 1e-3, where tanh x ~ x needs RELATIVE accuracy)

@@ -20,7 +20,7 @@ __global__ void sf2r_pack_kernel(const float* __restrict__ params, float* __rest
 
 // gradient entry e of the flat parameter vector from a warp's second-level accumulators G[NACC][32]
 template <class K>
-GPF_DEV float sf2r_partial_entry(const float* G, int e) {
+GPF_DEV float sf2r_partial_entry(const float* G, int e, const float* G2 = nullptr) {
   typedef typename K::Flat F;
   constexpr int H1 = K::H1, H2 = K::H2;
   float s = 0.0f;
@@ -30,8 +30,17 @@ GPF_DEV float sf2r_partial_entry(const float* G, int e) {
   } else if (e < F::OFF_W3) {  // W2 [H2][H1] then b2 [H2]  ->  tile entry (position k + 1, position m + 1 | 0 = bias)
     const int pk = (e < F::OFF_B2 ? (e - F::OFF_W2) / H1 : e - F::OFF_B2) + 1;
     const int pm = e < F::OFF_B2 ? (e - F::OFF_W2) % H1 + 1 : 0;
+#if GPF_SF2R_MMA
+    // C fragments of mma m16n8: lane (g = pk & 7, t = (pm & 7) >> 1), register 4 (pm >> 3) + 2 (pk >> 3) + (pm & 1)
+    s = G[(K::G_W2 + 4 * (pm >> 3) + 2 * (pk >> 3) + (pm & 1)) * 32 + (pk & 7) * 4 + ((pm & 7) >> 1)];
+#else
     const int ln = (pk >> 2) * 4 + (pm >> 2), el = (pk & 3) * 4 + (pm & 3);
     s = G[(K::G_W2 + el) * 32 + ln] + G[(K::G_W2 + el) * 32 + ln + 16];
+#endif
+    if (G2 != nullptr) {   // sf2e: the dual evaluations' tile (4 x 4 register tiles of the lanes (slice, ti, tj))
+      const int ln2 = (pk >> 2) * 4 + (pm >> 2), el2 = (pk & 3) * 4 + (pm & 3);
+      s += G2[el2 * 32 + ln2] + G2[el2 * 32 + ln2 + 16];
+    }
   } else if (e < F::OFF_B3) {  // W3 [2][H2]: row 0 = +, row 1 = - of the collapsed row, position k + 1
     const int r = (e - F::OFF_W3) / H2, p = (e - F::OFF_W3) % H2 + 1;
     for (int sl = 0; sl < 8; ++sl) s += G[(K::G_W3 + (p & 3)) * 32 + sl * 4 + (p >> 2)];

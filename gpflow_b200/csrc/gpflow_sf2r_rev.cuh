@@ -1,5 +1,6 @@
 // gpflow_b200 -- sf2r kernel, reverse sweep of one velocity evaluation for one warp tile (formulas: gpflow_sf2r.cuh).
 #pragma once
+#include "gpflow_generic_mma.cuh"   // mma_tf32 (m16n8k8 TF32 fragments)
 #include "gpflow_sf2r.cuh"
 
 namespace gpflow {
@@ -128,6 +129,72 @@ GPF_DEV void sf2r_reverse_eval(const float* __restrict__ W, const float* __restr
     xb1 += fmaf(2.0f * x1, sb1, 2.0f * psi * qb0);
   }
   __syncwarp();
+#if GPF_SF2R_MMA
+  // ---- dW2[pk][pm] += sum_s ab2_s[pk] h1_s[pm] + ws_s[pk] c_s[pm]  (h1 position 0 == 1 -> db2) on the tensor cores:
+  //      a 16 x 16 x 64 product (positions x positions x (32 samples, 2 terms)) as mma.sync m16n8k8 TF32 tiles with the
+  //      3xTF32 split (fp32-level accuracy, gpflow_generic_mma.cuh).  It takes the rank update (19 % of the FMA-pipe
+  //      cycles, 30 % of the shared-memory wavefronts) off the two pipes that bound the kernel.  Contraction index c of
+  //      k-step ks <-> sample 8 ks + 2 (c mod 4) + (c div 4): with that order every fragment load is a conflict-free
+  //      32-bit shared-memory access (work rows: stride 68 floats; stash rows: the XOR swizzle).  The products of ONE
+  //      evaluation are accumulated from zero in the fragment and then added in fp32 (no long accumulation chains inside
+  //      the tensor core).  acc[0..7] = the m16n8 C fragments of the two column tiles: lane (g, t) owns the entries
+  //      (pk in {g, g + 8}, pm in {2t, 2t + 1} + 8 nt).
+  {
+    const int g = lane >> 2, t = lane & 3;
+    float cf[4][2][4];   // four independent accumulation chains (k-step parity x term): mma latency, not throughput, binds
+#pragma unroll
+    for (int ch = 0; ch < 4; ++ch)
+#pragma unroll
+      for (int nt = 0; nt < 2; ++nt)
+#pragma unroll
+        for (int i = 0; i < 4; ++i) cf[ch][nt][i] = 0.0f;
+    auto split = [](float x, uint32_t& hi, uint32_t& lo) {
+#if GPF_SF2R_MMA == 2
+      hi = __float_as_uint(x) & 0xffffe000u;             // truncation split (ALU) instead of cvt.rna
+#else
+      asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(hi) : "f"(x));
+#endif
+      lo = __float_as_uint(x - __uint_as_float(hi));   // the tensor core reads the top 19 bits: 2^-21 relative at worst
+    };
+#pragma unroll
+    for (int ks = 0; ks < 4; ++ks) {
+      const int sa = 8 * ks + 2 * t, sb = sa + 1;
+      const float* wa = Wk + sa * K::WS;
+      const float* wb = Wk + sb * K::WS;
+      const float* da = Sbuf + sa * K::SROW;
+      const float* db = Sbuf + sb * K::SROW;
+#pragma unroll
+      for (int term = 0; term < 2; ++term) {
+        const int oa = term == 0 ? K::O_AB : K::O_WS;
+        uint32_t ah[4], al[4];
+        split(wa[oa + g], ah[0], al[0]);
+        split(wa[oa + g + 8], ah[1], al[1]);
+        split(wb[oa + g], ah[2], al[2]);
+        split(wb[oa + g + 8], ah[3], al[3]);
+#pragma unroll
+        for (int nt = 0; nt < 2; ++nt) {
+          const int pm = 8 * nt + g;
+          float b0, b1;
+          if (term == 0) {
+            b0 = da[sw_chunk(pm >> 2, sa & 7) + (pm & 3)];
+            b1 = db[sw_chunk(pm >> 2, sb & 7) + (pm & 3)];
+          } else {
+            b0 = wa[K::O_C + pm];
+            b1 = wb[K::O_C + pm];
+          }
+          uint32_t bh[2], bl[2];
+          split(b0, bh[0], bl[0]);
+          split(b1, bh[1], bl[1]);
+          mma_3xtf32(cf[2 * term + (ks & 1)][nt], ah, al, bh, bl);
+        }
+      }
+    }
+#pragma unroll
+    for (int nt = 0; nt < 2; ++nt)
+#pragma unroll
+      for (int i = 0; i < 4; ++i) acc[4 * nt + i] += (cf[0][nt][i] + cf[1][nt][i]) + (cf[2][nt][i] + cf[3][nt][i]);
+  }
+#else
   // ---- dW2[pk][pm] += sum_s ab2_s[pk] h1_s[pm] + ws_s[pk] c_s[pm]  (h1 position 0 == 1 -> db2): lane (slice, ti, tj)
   //      owns the 4x4 tile (4ti.., 4tj..) over the 16 samples with bit 2 == slice (conflict-free with the swizzle)
   {
@@ -167,6 +234,7 @@ GPF_DEV void sf2r_reverse_eval(const float* __restrict__ W, const float* __restr
       acc[4 * r + 2] = accp[r][1].x; acc[4 * r + 3] = accp[r][1].y;
     }
   }
+#endif
   __syncwarp();  // every lane is done with the other lanes' [ab2 | ws] rows
   sts4(Wrow + K::O_AB, ab1[0], ab1[1], ab1[2], ab1[3]);
   sts4(Wrow + K::O_AB + 4, ab1[4], ab1[5], ab1[6], ab1[7]);
