@@ -2,7 +2,9 @@
 pinned by tests/golden).  The shapes are chosen to reach every branch of the fp32 fast paths of gpflow_generic.cuh /
 gpflow_generic_mma.cuh: ragged mma tiles (rows 1 + d not a multiple of 16, widths not multiples of 8), the 128-bit
 last-layer passes on and off (last hidden width / parameter offset multiple of 4 or not), the on-chip (shared memory)
-and the global scratch placement, nb = 1 ... d, one to three hidden layers, batches below / above the grid size."""
+and the global scratch placement, nb = 1 ... d, one to three hidden layers, batches below / above the grid size.
+Bars: 1e-5 (fp32) / 1e-10 (fp64) on y, OT cost, Lagrangian and parameter gradients for every shape; 2e-5 on d loss / d x_map,
+which carries the erfinv conditioning factor of the wrapper (tests/test_sf2_parity.py: GX_TOL)."""
 import pytest
 import torch
 
@@ -29,7 +31,7 @@ SHAPES = [
 
 
 @pytest.mark.parametrize("d,nb,hidden,B,std", SHAPES)
-@pytest.mark.parametrize("dtype,tol", [(torch.float32, 2e-5), (torch.float64, 1e-10)])
+@pytest.mark.parametrize("dtype,tol", [(torch.float32, 1e-5), (torch.float64, 1e-10)])
 def test_train_step_shape_sweep(d, nb, hidden, B, std, dtype, tol):
     if not torch.cuda.is_available():
         pytest.skip("needs a CUDA device")
