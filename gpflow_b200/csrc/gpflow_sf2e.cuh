@@ -117,7 +117,8 @@ GPF_DEV void sf2e_forward_eval(const float* __restrict__ W, float* __restrict__ 
     float b2[16];
     load_w16s<1>(W, R::W2F, b2);
 #pragma unroll
-    for (int k = 0; k < 16; ++k) a2[k] = d_make(b2[k], 0.0f);
+    for (int k = 0; k < 15; ++k) a2[k] = d_make(b2[k + 1], 0.0f);   // W2F columns are positions (unit + 1)
+    a2[15] = d_make(0.0f, 0.0f);
   }
 #pragma unroll kSF2EUnroll
   for (int p = 1; p <= H1; ++p) {
@@ -125,7 +126,7 @@ GPF_DEV void sf2e_forward_eval(const float* __restrict__ W, float* __restrict__ 
     load_w16s<GPF_SF2E_WBIT>(W, R::W2F + 16 * p, wr);
     const du h = *(reinterpret_cast<const float2*>(Drow + dsw_chunk(p >> 1, l7)) + (p & 1));   // hp[p], just stored
 #pragma unroll
-    for (int k = 0; k < H2; ++k) a2[k] = d_fma(wr[k], h, a2[k]);
+    for (int k = 0; k < H2; ++k) a2[k] = d_fma(wr[k + 1], h, a2[k]);
   }
   // ---- activation 2, collapsed output row
   du h2p[16], ws[16];  // by position

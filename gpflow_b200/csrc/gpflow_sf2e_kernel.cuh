@@ -312,7 +312,7 @@ size_t sf2e_workspace(const GpFlowDesc* d, int64_t B) {
   const int64_t ctas = tiles < kMaxSMs ? (tiles < 1 ? 1 : tiles) : kMaxSMs;
   const int64_t slots = ctas * kSF2EWarps;
   const int64_t stash_slots = tiles < slots ? tiles : slots;
-  size_t bytes = 640 * 4;
+  size_t bytes = 704 * 4;
   bytes += align_up((size_t)slots * (3 + K::R::NPARAM) * 4, 256);
   bytes += align_up((size_t)slots * (K::R::NACC + 17) * 32 * 4, 256);
   bytes += align_up((size_t)slots * d->n_steps * 32 * 4, 256);
@@ -350,7 +350,7 @@ int launch_sf2e(const GpFlowDesc* d, const Ptrs<float>& p, int64_t B, void* ws, 
   a.y_out = p.y_out; a.grad_x_out = p.grad_x_out;
   char* wsp = reinterpret_cast<char*>(ws);
   float* packed = reinterpret_cast<float*>(wsp);
-  wsp += 640 * 4;
+  wsp += 704 * 4;
   a.partials = reinterpret_cast<float*>(wsp);
   wsp += align_up((size_t)slots * npart * 4, 256);
   a.g2 = reinterpret_cast<float*>(wsp);

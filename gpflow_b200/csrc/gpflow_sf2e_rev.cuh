@@ -133,11 +133,11 @@ GPF_DEV void sf2e_reverse_eval(const float* __restrict__ W, float* __restrict__ 
 #pragma unroll
       for (int c = 0; c < 4; ++c) acc[4 * r + c] += accp[r][c].x + accp[r][c].y;
   }
-  __syncwarp();  // every lane is done with the other lanes' ab2 / c rows: they become ab1 / q (by unit, (v, e))
+  __syncwarp();  // every lane is done with the other lanes' ab2 / c rows: they become ab1 / q (by position, (v, e))
   // ---- activation 1 + layer 1: q = sp1 z, grad psi, ab1, xbar
   du G0 = d_make(0.0f, 0.0f), G1 = G0, Xb0 = G0, Xb1 = G0;
-  sts4(Wrow + K::O_L + 28, 0.0f, 0.0f, 0.0f, 0.0f);   // unit 15 (pad) of ab1 / q
-  sts4(Wrow + K::O_C + 28, 0.0f, 0.0f, 0.0f, 0.0f);
+  sts4(Wrow + K::O_L, 0.0f, 0.0f, 0.0f, 0.0f);   // position 0 of ab1 / q (the rows of the dW1 tile are positions)
+  sts4(Wrow + K::O_C, 0.0f, 0.0f, 0.0f, 0.0f);
 #pragma unroll
   for (int c = 0; c < 8; ++c) {   // h1 again (position 0 is the constant 1 now; X0 is in a register)
     const float4 t = lds4(Drow + dsw_chunk(c, l7));
@@ -155,11 +155,11 @@ GPF_DEV void sf2e_reverse_eval(const float* __restrict__ W, float* __restrict__ 
       const du a = d_sub(d_mul(sp, hb[m + 1]), d_scale(2.0f, d_mul(d_mul(h, z[m + 1]), cq[m + 1])));
       Xb0 = d_fma(w.x, a, Xb0);
       Xb1 = d_fma(w.y, a, Xb1);
-      *reinterpret_cast<float2*>(Wrow + K::O_L + 2 * m) = a;   // by unit, (v, e)
-      *reinterpret_cast<float2*>(Wrow + K::O_C + 2 * m) = q;
+      *reinterpret_cast<float2*>(Wrow + K::O_L + 2 * (m + 1)) = a;   // by position, (v, e)
+      *reinterpret_cast<float2*>(Wrow + K::O_C + 2 * (m + 1)) = q;
     } else if (m < 15) {
-      *reinterpret_cast<float2*>(Wrow + K::O_L + 2 * m) = make_float2(0.0f, 0.0f);
-      *reinterpret_cast<float2*>(Wrow + K::O_C + 2 * m) = make_float2(0.0f, 0.0f);
+      *reinterpret_cast<float2*>(Wrow + K::O_L + 2 * (m + 1)) = make_float2(0.0f, 0.0f);
+      *reinterpret_cast<float2*>(Wrow + K::O_C + 2 * (m + 1)) = make_float2(0.0f, 0.0f);
     }
   }
   // ---- rest of A.3

@@ -42,12 +42,17 @@ struct SF2R {
   static constexpr int NPARAM = Flat::NPARAM;
   // packed weights (floats)
   static constexpr int W1P = 0;          // [16][4]  unit m: {W1[m][0], W1[m][1], W1[m][2] (time), b1[m]}; rows >= H1 zero
-  static constexpr int W2F = W1P + 64;   // [16][16] forward rows by POSITION p of h1: W2F[0][k] = b2[k], W2F[m+1][k] = W2[k][m]
+  static constexpr int W2F = W1P + 64;   // [16][16] forward rows AND columns by position: W2F[0][k+1] = b2[k],
+                                         //          W2F[m+1][k+1] = W2[k][m], column 0 = 0
   static constexpr int W2B = W2F + 256;  // [16][16] backward rows AND columns by position: W2B[k+1][m+1] = W2[k][m], row 0 =
                                          //          column 0 = 0 (register pairs line up with the position-indexed rows)
   static constexpr int W3P = W2B + 256;  // [16]     by position: W3P[0] = 0, W3P[k+1] = W3[0][k] - W3[1][k]
   static constexpr int B3C = W3P + 16;   // [4]      b3[0] - b3[1], 0, 0, 0
-  static constexpr int WEND = B3C + 4;
+  static constexpr int W1Q = B3C + 4;    // [8][8]   layer 1 by POSITION PAIRS (2j, 2j+1): {W1[.][0] x2, W1[.][1] x2, W1[.][2] x2, b1 x2};
+                                         //          position 0 and positions beyond H1 are zero (operands of packed fp32x2 FMAs)
+  static constexpr int WEND = W1Q + 64;
+  static constexpr int WPACK = 704;      // floats of the packed-weight staging buffer / constant array (>= WEND)
+  static_assert(WEND <= WPACK, "packed weights do not fit the constant array");
   // per-warp buffers (floats)
   static constexpr int SROW = 32, S_FL = 32 * SROW, STASH_BYTES = S_FL * 4;   // one evaluation of one tile: 4 KB
   static constexpr int WS = 68;                                               // work row, 17 x 16 B (odd: conflict free)
@@ -73,8 +78,9 @@ GPF_DEV float sf2r_pack_value(const float* __restrict__ raw, int i) {
     const int m = i >> 2, c = i & 3;
     if (m < H1) v = c < 3 ? raw[F::OFF_W1 + 3 * m + c] : raw[F::OFF_B1 + m];
   } else if (i < K::W2B) {
-    const int p = (i - K::W2F) >> 4, k = (i - K::W2F) & 15;
-    if (k < H2) v = p == 0 ? raw[F::OFF_B2 + k] : (p - 1 < H1 ? raw[F::OFF_W2 + k * H1 + (p - 1)] : 0.0f);
+    const int p = (i - K::W2F) >> 4, pk = (i - K::W2F) & 15;
+    if (pk >= 1 && pk - 1 < H2)
+      v = p == 0 ? raw[F::OFF_B2 + pk - 1] : (p - 1 < H1 ? raw[F::OFF_W2 + (pk - 1) * H1 + (p - 1)] : 0.0f);
   } else if (i < K::W3P) {
     const int p = (i - K::W2B) >> 4, pm = (i - K::W2B) & 15;
     if (p >= 1 && p - 1 < H2 && pm >= 1 && pm - 1 < H1) v = raw[F::OFF_W2 + (p - 1) * H1 + (pm - 1)];
@@ -83,6 +89,9 @@ GPF_DEV float sf2r_pack_value(const float* __restrict__ raw, int i) {
     if (p >= 1 && p - 1 < H2) v = raw[F::OFF_W3 + (p - 1)] - raw[F::OFF_W3 + H2 + (p - 1)];
   } else if (i == K::B3C) {
     v = raw[F::OFF_B3] - raw[F::OFF_B3 + 1];
+  } else if (i >= K::W1Q && i < K::W1Q + 64) {
+    const int j = (i - K::W1Q) >> 3, e = (i - K::W1Q) & 7, pos = 2 * j + (e & 1), c = e >> 1;   // c: x0, x1, t, bias
+    if (pos >= 1 && pos - 1 < H1) v = c < 3 ? raw[F::OFF_W1 + 3 * (pos - 1) + c] : raw[F::OFF_B1 + pos - 1];
   }
   return v;
 }
@@ -95,7 +104,7 @@ GPF_DEV float sf2r_pack_value(const float* __restrict__ raw, int i) {
 #ifndef GPF_SF2R_CONST
 #define GPF_SF2R_CONST 1   // measured at C4 (tools/sf2r_const_ab.sh): 0: 1.34e8, 1: 1.48e8, 3: 1.47e8, 7: 1.40e8 samples/s
 #endif
-__constant__ float sf2r_cw[640];
+__constant__ float sf2r_cw[704];
 // GPF_SF2R_MMA: 0 (default) = the rank-2 dW2 update of the reverse sweep as FFMA2 register tiles; 1 / 2 = on the tensor
 // cores (mma.sync m16n8k8, 3xTF32; split by cvt.rna / by truncation).  Parity-green and measured SLOWER at C4
 // (tools/sf2r_mma_ab.sh, same box): 111.6 ms (0), 121.8 ms (1), 114.4 ms (2) -- the FMA pipe drops from 67 % to 59 % busy but
@@ -139,74 +148,53 @@ template <class K, bool STASH = true>
 GPF_DEV void sf2r_forward_eval(const float* __restrict__ W, float* __restrict__ Srow, int l7, float x0, float x1, float ts,
                                float bnd, float& v0, float& v1) {
   constexpr int H1 = K::H1, H2 = K::H2;
-  // ---- layer 1 (unit m unrolled): h1 = tanh(W1 [x; t] + b1)   (vector_field.py:75-90)
-  float hp[16];  // by position: hp[0] = x0, hp[m + 1] = h1[m]
-  hp[0] = x0;
-  {
-    float a1[16];
+  // Everything is held as POSITION PAIRS (2j, 2j+1), position p = unit + 1, so that the element-wise stages are packed
+  // fp32x2 instructions too and the pairs coincide with the 128-bit stash chunks (no register shuffles).
+  // ---- layer 1: h1 = tanh(W1 [x; t] + b1)   (vector_field.py:75-90)
+  float2 hpp[8];   // hpp[0].x = x0 (position 0), then h1
+  const float2 x0d = make_float2(x0, x0), x1d = make_float2(x1, x1), tsd = make_float2(ts, ts), one2 = make_float2(1.0f, 1.0f);
 #pragma unroll
-    for (int m = 0; m < 16; ++m) {
-      if (m < H1) {
-        const float4 w = ldwr4<1>(W, K::W1P + 4 * m);
-        a1[m] = fmaf(w.x, x0, fmaf(w.y, x1, fmaf(w.z, ts, w.w)));
-      } else {
-        a1[m] = 0.0f;
-      }
-    }
-#pragma unroll
-    for (int j = 0; j < 8; ++j) {   // two units per packed tanh
-      const float2 h = sf2r_tanh2(make_float2(a1[2 * j], a1[2 * j + 1]));
-      if (2 * j < 15) hp[2 * j + 1] = 2 * j < H1 ? h.x : 0.0f;
-      if (2 * j + 1 < 15) hp[2 * j + 2] = 2 * j + 1 < H1 ? h.y : 0.0f;
-    }
+  for (int j = 0; j < 8; ++j) {
+    const float4 w0 = ldwr4<1>(W, K::W1Q + 8 * j), w1 = ldwr4<1>(W, K::W1Q + 8 * j + 4);
+    const float2 a = __ffma2_rn(make_float2(w0.x, w0.y), x0d, __ffma2_rn(make_float2(w0.z, w0.w), x1d,
+                                __ffma2_rn(make_float2(w1.x, w1.y), tsd, make_float2(w1.z, w1.w))));
+    hpp[j] = sf2r_tanh2(a);   // zero weights -> tanh(0) = 0 at the unused positions
   }
+  hpp[0].x = x0;
   if (STASH) {
 #pragma unroll
-    for (int c = 0; c < 4; ++c) sts4(Srow + sw_chunk(c, l7), hp[4 * c], hp[4 * c + 1], hp[4 * c + 2], hp[4 * c + 3]);
+    for (int c = 0; c < 4; ++c) sts4(Srow + sw_chunk(c, l7), hpp[2 * c].x, hpp[2 * c].y, hpp[2 * c + 1].x, hpp[2 * c + 1].y);
   }
-  // ---- layer 2 (position p unrolled): a2 = b2 + W2 h1 as packed fp32x2 FMAs, two output units per instruction
+  // ---- layer 2 (position p unrolled): a2 = b2 + W2 h1, two output positions per packed FMA
   float2 a2p[8];
   load_w16<1>(W, K::W2F, a2p);  // position 0: the bias row times 1
 #pragma unroll
   for (int p = 1; p <= H1; ++p) {
     float2 wp[8];
     load_w16<1>(W, K::W2F + 16 * p, wp);
-    const float2 hd = make_float2(hp[p], hp[p]);
+    const float h = (p & 1) ? hpp[p >> 1].y : hpp[p >> 1].x;
+    const float2 hd = make_float2(h, h);
 #pragma unroll
     for (int j = 0; j < 8; ++j) a2p[j] = __ffma2_rn(wp[j], hd, a2p[j]);
   }
-  // ---- activation 2, collapsed output row: psi = w3 . h2 + b3, ws = w3 (.) sp2
-  float h2p[16], ws[16];  // by position
-  h2p[0] = x1;
-  ws[0] = 0.0f;
-  float psi = ldwr4<1>(W, K::B3C).x;
-  {
-    float h2u[16];   // by unit
+  // ---- activation 2, collapsed output row: psi = w3 . h2 + b3, ws = w3 (.) sp2   (w3 = 0 at position 0)
+  float2 h2pp[8], ws2[8], psip = make_float2(ldwr4<1>(W, K::B3C).x, 0.0f);
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      const float2 h = sf2r_tanh2(a2p[j]);
-      h2u[2 * j] = h.x;
-      h2u[2 * j + 1] = h.y;
-    }
+  for (int j = 0; j < 8; ++j) h2pp[j] = sf2r_tanh2(a2p[j]);
+  h2pp[0].x = x1;
 #pragma unroll
-    for (int c = 0; c < 4; ++c) {
-      const float4 w3v = ldwr4<1>(W, K::W3P + 4 * c);
-      const float w3[4] = {w3v.x, w3v.y, w3v.z, w3v.w};
-#pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        const int p = 4 * c + i, k = p - 1;
-        if (p >= 1 && k < H2) {
-          const float h = h2u[k];
-          psi = fmaf(w3[i], h, psi);
-          ws[p] = w3[i] * fmaf(-h, h, 1.0f);
-          h2p[p] = h;
-        } else if (p >= 1) {
-          h2p[p] = ws[p] = 0.0f;
-        }
-      }
-      if (STASH) sts4(Srow + sw_chunk(4 + c, l7), h2p[4 * c], h2p[4 * c + 1], h2p[4 * c + 2], h2p[4 * c + 3]);
-    }
+  for (int c = 0; c < 4; ++c) {
+    const float4 w3v = ldwr4<1>(W, K::W3P + 4 * c);
+    const float2 w3a = make_float2(w3v.x, w3v.y), w3b = make_float2(w3v.z, w3v.w);
+    const float2 spa = __ffma2_rn(make_float2(-h2pp[2 * c].x, -h2pp[2 * c].y), h2pp[2 * c], one2);
+    const float2 spb = __ffma2_rn(make_float2(-h2pp[2 * c + 1].x, -h2pp[2 * c + 1].y), h2pp[2 * c + 1], one2);
+    psip = __ffma2_rn(w3a, h2pp[2 * c], psip);
+    psip = __ffma2_rn(w3b, h2pp[2 * c + 1], psip);
+    ws2[2 * c] = __fmul2_rn(w3a, spa);
+    ws2[2 * c + 1] = __fmul2_rn(w3b, spb);
+    if (STASH) sts4(Srow + sw_chunk(4 + c, l7), h2pp[2 * c].x, h2pp[2 * c].y, h2pp[2 * c + 1].x, h2pp[2 * c + 1].y);
   }
+  const float psi = psip.x + psip.y;
   // ---- z = W2^T ws (position p of h2 unrolled); zp by position of h1
   float2 zp[8];
 #pragma unroll
@@ -215,20 +203,21 @@ GPF_DEV void sf2r_forward_eval(const float* __restrict__ W, float* __restrict__ 
   for (int p = 1; p <= H2; ++p) {
     float2 wp[8];
     load_w16<1>(W, K::W2B + 16 * p, wp);
-    const float2 wd = make_float2(ws[p], ws[p]);
+    const float w = (p & 1) ? ws2[p >> 1].y : ws2[p >> 1].x;
+    const float2 wd = make_float2(w, w);
 #pragma unroll
     for (int j = 0; j < 8; ++j) zp[j] = __ffma2_rn(wp[j], wd, zp[j]);
   }
-  // ---- grad psi = W1x^T (sp1 (.) z)
-  float g0 = 0.0f, g1 = 0.0f;
+  // ---- grad psi = W1x^T (sp1 (.) z)   (position 0: zero weights and z = 0)
+  float2 g0p = make_float2(0.0f, 0.0f), g1p = g0p;
 #pragma unroll
-  for (int m = 0; m < H1; ++m) {
-    const float4 w = ldwr4<1>(W, K::W1P + 4 * m);
-    const float h = hp[m + 1], z = ((m + 1) & 1) ? zp[(m + 1) >> 1].y : zp[(m + 1) >> 1].x;
-    const float q = fmaf(-h, h, 1.0f) * z;
-    g0 = fmaf(w.x, q, g0);
-    g1 = fmaf(w.y, q, g1);
+  for (int j = 0; j < 8; ++j) {
+    const float4 w0 = ldwr4<1>(W, K::W1Q + 8 * j);
+    const float2 q = __fmul2_rn(__ffma2_rn(make_float2(-hpp[j].x, -hpp[j].y), hpp[j], one2), zp[j]);
+    g0p = __ffma2_rn(make_float2(w0.x, w0.y), q, g0p);
+    g1p = __ffma2_rn(make_float2(w0.z, w0.w), q, g1p);
   }
+  const float g0 = g0p.x + g0p.y, g1 = g1p.x + g1p.y;
   // ---- closed form A.2 for d = 2, nb = 1 (velocity_field.py:20-79)
   const float s0 = fmaf(x0, x0, -bnd), s1 = fmaf(x1, x1, -bnd);
   const float q0 = fmaf(2.0f * psi, x1, s1 * g1);

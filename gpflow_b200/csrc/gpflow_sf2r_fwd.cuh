@@ -119,7 +119,7 @@ __global__ void __launch_bounds__(NW * 32, 1) gpflow_sf2r_fwd_kernel(const SF2Fw
 template <int H1, int H2>
 size_t sf2r_fwd_workspace(int64_t B) {
   (void)B;
-  return 640 * 4 + align_up((size_t)kMaxSMs * kSF2FwdWarps * 3 * 4, 256);
+  return 704 * 4 + align_up((size_t)kMaxSMs * kSF2FwdWarps * 3 * 4, 256);
 }
 
 template <int H1, int H2>
@@ -144,7 +144,7 @@ int launch_sf2r_fwd(const GpFlowDesc* d, const Ptrs<float>& p, int64_t B, void* 
   memset(&a, 0, sizeof(a));
   a.params = p.params; a.x_in = p.x_in; a.y_out = p.y_out; a.logdet_out = p.logdet_out; a.traj_out = p.traj_out;
   float* packed = reinterpret_cast<float*>(ws);
-  a.partials = packed + 640;
+  a.partials = packed + 704;
   a.B = B; a.n_steps = d->n_steps; a.flags = d->flags;
   const bool rev = (d->flags & GPFLOW_FLAG_REVERSE) != 0;
   a.dt = rev ? -(float)d->dt : (float)d->dt;

@@ -15,7 +15,7 @@ namespace gpflow {
 template <class K>
 __global__ void sf2r_pack_kernel(const float* __restrict__ params, float* __restrict__ packed) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < 640) packed[i] = i < K::WEND ? sf2r_pack_value<K>(params, i) : 0.0f;
+  if (i < K::WPACK) packed[i] = i < K::WEND ? sf2r_pack_value<K>(params, i) : 0.0f;
 }
 
 // gradient entry e of the flat parameter vector from a warp's second-level accumulators G[NACC][32]
@@ -26,7 +26,8 @@ GPF_DEV float sf2r_partial_entry(const float* G, int e, const float* G2 = nullpt
   float s = 0.0f;
   if (e < F::OFF_W2) {  // W1 [H1][3] then b1 [H1]  ->  tile entry (m & 3, c) of the lanes (slice, ti = m >> 2)
     const int m = e < F::OFF_B1 ? e / 3 : e - F::OFF_B1, c = e < F::OFF_B1 ? e % 3 : 3;
-    for (int sl = 0; sl < 8; ++sl) s += G[(K::G_W1 + (m & 3) * 4 + c) * 32 + sl * 4 + (m >> 2)];
+    const int pm = m + 1;   // rows of the dW1 tile are positions
+    for (int sl = 0; sl < 8; ++sl) s += G[(K::G_W1 + (pm & 3) * 4 + c) * 32 + sl * 4 + (pm >> 2)];
   } else if (e < F::OFF_W3) {  // W2 [H2][H1] then b2 [H2]  ->  tile entry (position k + 1, position m + 1 | 0 = bias)
     const int pk = (e < F::OFF_B2 ? (e - F::OFF_W2) / H1 : e - F::OFF_B2) + 1;
     const int pm = e < F::OFF_B2 ? (e - F::OFF_W2) % H1 + 1 : 0;
@@ -282,7 +283,7 @@ size_t sf2r_workspace(const GpFlowDesc* d, int64_t B) {
   const int64_t ctas = tiles < kMaxSMs ? (tiles < 1 ? 1 : tiles) : kMaxSMs;
   const int64_t slots = ctas * kSF2MaxWarps;
   const int64_t stash_slots = tiles < slots ? tiles : slots;
-  size_t bytes = 640 * 4;  // packed weights (staging for the constant bank)
+  size_t bytes = 704 * 4;  // packed weights (staging for the constant bank)
   bytes += align_up((size_t)slots * (3 + K::NPARAM) * 4, 256);
   bytes += align_up((size_t)slots * K::NACC * 32 * 4, 256);
   bytes += (size_t)stash_slots * 4 * d->n_steps * K::STASH_BYTES;
@@ -335,9 +336,9 @@ int sf2r_launch_guarded(const float* params, float* packed, cudaStream_t st, F l
       return GPFLOW_ERR_CUDA;
     }
   }
-  sf2r_pack_kernel<K><<<5, 128, 0, st>>>(params, packed);
+  sf2r_pack_kernel<K><<<(K::WPACK + 127) / 128, 128, 0, st>>>(params, packed);
   if (cudaGetLastError() != cudaSuccess) return GPFLOW_ERR_CUDA;
-  if (cudaMemcpyToSymbolAsync(sf2r_cw, packed, 640 * 4, 0, cudaMemcpyDeviceToDevice, st) != cudaSuccess) {
+  if (cudaMemcpyToSymbolAsync(sf2r_cw, packed, K::WPACK * 4, 0, cudaMemcpyDeviceToDevice, st) != cudaSuccess) {
     cudaGetLastError();
     return GPFLOW_ERR_CUDA;
   }
@@ -383,7 +384,7 @@ int launch_sf2r(const GpFlowDesc* d, const Ptrs<float>& p, int64_t B, void* ws, 
   a.y_out = p.y_out; a.grad_x_out = p.grad_x_out;
   char* wsp = reinterpret_cast<char*>(ws);
   float* packed = reinterpret_cast<float*>(wsp);
-  wsp += 640 * 4;
+  wsp += 704 * 4;
   a.partials = reinterpret_cast<float*>(wsp);
   wsp += align_up((size_t)slots * npart * 4, 256);
   a.g2 = reinterpret_cast<float*>(wsp);

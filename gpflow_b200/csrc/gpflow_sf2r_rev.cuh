@@ -8,7 +8,7 @@ namespace gpflow {
 // Given the stash rows of one evaluation and the cotangent (vb0, vb1) of v, returns xbar = J_v^T vbar and accumulates
 // every parameter gradient:
 //   acc[16]   lane-owned 4x4 tile (positions 4ti.., 4tj..) of dW2 (+ db2 in column 0); rank-64 update over the tile
-//   accw[16]  lane-owned 4x4 tile {dW1[m][0], dW1[m][1], dW1[m][2] (time), db1[m]}, m = 4 (lane & 3) + r
+//   accw[16]  lane-owned 4x4 tile {dW1[m][0], dW1[m][1], dW1[m][2] (time), db1[m]}, POSITION m + 1 = 4 (lane & 3) + r
 //   acc3[4]   dw3 of the collapsed output row at positions 4 (lane & 3) + r (dW3[0] = +, dW3[1] = -);  b3b lane-private
 template <class K>
 GPF_DEV void sf2r_reverse_eval(const float* __restrict__ W, const float* __restrict__ Sbuf, float* __restrict__ Wk, int lane,
@@ -18,41 +18,35 @@ GPF_DEV void sf2r_reverse_eval(const float* __restrict__ W, const float* __restr
   const int l7 = lane & 7;
   const float* Srow = Sbuf + lane * K::SROW;
   float* Wrow = Wk + lane * K::WS;
-  float hp[16];  // by position: x0, h1[0..14]
+  float2 hpp[8];  // position pairs: hpp[0].x = x0, then h1
 #pragma unroll
   for (int c = 0; c < 4; ++c) {
     const float4 t = lds4(Srow + sw_chunk(c, l7));
-    hp[4 * c] = t.x; hp[4 * c + 1] = t.y; hp[4 * c + 2] = t.z; hp[4 * c + 3] = t.w;
+    hpp[2 * c] = make_float2(t.x, t.y);
+    hpp[2 * c + 1] = make_float2(t.z, t.w);
   }
-  const float x0 = hp[0], x1 = Srow[sw_chunk(4, l7)];
+  const float x0 = hpp[0].x, x1 = Srow[sw_chunk(4, l7)];
   // ---- A.3, the part that does not need psi / grad psi
   const float s0 = fmaf(x0, x0, -bnd), s1 = fmaf(x1, x1, -bnd);
   const float qb0 = vb0 * s0, qb1 = vb1 * s1;
   const float psib = 2.0f * (x1 * qb0 - x0 * qb1);
   const float gb1 = s1 * qb0, gb0 = -s0 * qb1;
   b3b += psib;
-  // ---- c = sp1 (.) (W1x gb), by POSITION (c[0] = 0) so that its register pairs are those of the 128-bit stores and of
-  //      the position-indexed weight rows; the work row also gets (x0 x1 gb0 gb1).  Position 0 of this sample's stash row
-  //      (x0, already read) becomes 1.0: the bias column of the dW2 update below
-  float cq[16];
-  cq[0] = 0.0f;
+  // ---- c = sp1 (.) (W1x gb) as position pairs (the layer-1 weights of position 0 are zero, so c[0] = 0): the pairs are those
+  //      of the 128-bit stores and of the position-indexed weight rows; the work row also gets (x0 x1 gb0 gb1).  Position 0
+  //      of this sample's stash row (x0, already read) becomes 1.0: the bias column of the dW2 update below
+  const float2 one2 = make_float2(1.0f, 1.0f), gb0d = make_float2(gb0, gb0), gb1d = make_float2(gb1, gb1);
+  float2 cp[8], sp1[8];
 #pragma unroll
-  for (int m = 0; m < 15; ++m) {
-    if (m < H1) {
-      const float4 w = ldwr4<4>(W, K::W1P + 4 * m);
-      const float h = hp[m + 1];
-      cq[m + 1] = fmaf(-h, h, 1.0f) * fmaf(w.x, gb0, w.y * gb1);
-    } else {
-      cq[m + 1] = 0.0f;
-    }
+  for (int j = 0; j < 8; ++j) {
+    const float4 w0 = ldwr4<4>(W, K::W1Q + 8 * j);
+    sp1[j] = __ffma2_rn(make_float2(-hpp[j].x, -hpp[j].y), hpp[j], one2);
+    cp[j] = __fmul2_rn(sp1[j], __ffma2_rn(make_float2(w0.x, w0.y), gb0d, __fmul2_rn(make_float2(w0.z, w0.w), gb1d)));
   }
 #pragma unroll
-  for (int c = 0; c < 4; ++c) sts4(Wrow + K::O_C + 4 * c, cq[4 * c], cq[4 * c + 1], cq[4 * c + 2], cq[4 * c + 3]);
+  for (int c = 0; c < 4; ++c) sts4(Wrow + K::O_C + 4 * c, cp[2 * c].x, cp[2 * c].y, cp[2 * c + 1].x, cp[2 * c + 1].y);
   sts4(Wrow + K::O_XG, x0, x1, gb0, gb1);
   const_cast<float*>(Srow)[sw_chunk(0, l7)] = 1.0f;
-  float2 cp[8];
-#pragma unroll
-  for (int j = 0; j < 8; ++j) cp[j] = make_float2(cq[2 * j], cq[2 * j + 1]);
   // ---- one pass over the rows of W2 (position p of h2, rolled by chunk): tb = W2 c (dot), then hb += W2[k,:] ab2[k],
   //      z += W2[k,:] ws[k].  Position 0 (the x1 slot) has a zero weight row and w3 = 0: it contributes nothing.
   float2 hbp[8], zp[8];
@@ -98,28 +92,26 @@ GPF_DEV void sf2r_reverse_eval(const float* __restrict__ W, const float* __restr
     sts4(Wrow + K::O_WS + 4 * c, wsv[0], wsv[1], wsv[2], wsv[3]);
     sts4(Wrow + K::O_E + 4 * c, ev[0], ev[1], ev[2], ev[3]);
   }
-  // ---- activation 1 + layer 1 (unit m unrolled): q = sp1 z, grad psi, ab1, xbar
-  float g0 = 0.0f, g1 = 0.0f, xb0 = 0.0f, xb1 = 0.0f;
-  float ab1[16], qv[16];
+  // ---- activation 1 + layer 1 as position pairs: q = sp1 z, grad psi, ab1 = sp1 hb - 2 h1 z c, xbar
+  //      (position 0: z = hb = c = 0 and zero layer-1 weights, so its ab1 = q = 0)
+  float2 g0p = make_float2(0.0f, 0.0f), g1p = g0p, xb0p = g0p, xb1p = g0p;
+  float2 ab1[8], qv[8];
 #pragma unroll
-  for (int m = 0; m < 16; ++m) {
-    if (m < H1) {
-      const float4 w = ldwr4<4>(W, K::W1P + 4 * m);
-      const float h = hp[m + 1], sp = fmaf(-h, h, 1.0f);
-      const float z = ((m + 1) & 1) ? zp[(m + 1) >> 1].y : zp[(m + 1) >> 1].x;
-      const float hb = ((m + 1) & 1) ? hbp[(m + 1) >> 1].y : hbp[(m + 1) >> 1].x;
-      const float q = sp * z;
-      g0 = fmaf(w.x, q, g0);
-      g1 = fmaf(w.y, q, g1);
-      const float a = fmaf(-2.0f * h * z, cq[m + 1], sp * hb);   // ab1 = sp1 (hb - 2 h1 z qbar), c = sp1 qbar
-      xb0 = fmaf(w.x, a, xb0);
-      xb1 = fmaf(w.y, a, xb1);
-      ab1[m] = a;
-      qv[m] = q;
-    } else {
-      ab1[m] = qv[m] = 0.0f;
-    }
+  for (int j = 0; j < 8; ++j) {
+    const float4 w0 = ldwr4<4>(W, K::W1Q + 8 * j);
+    const float2 wa = make_float2(w0.x, w0.y), wb = make_float2(w0.z, w0.w);
+    const float2 q = __fmul2_rn(sp1[j], zp[j]);
+    g0p = __ffma2_rn(wa, q, g0p);
+    g1p = __ffma2_rn(wb, q, g1p);
+    const float2 hz = __fmul2_rn(__fmul2_rn(hpp[j], zp[j]), make_float2(-2.0f, -2.0f));
+    const float2 a = __ffma2_rn(hz, cp[j], __fmul2_rn(sp1[j], hbp[j]));
+    xb0p = __ffma2_rn(wa, a, xb0p);
+    xb1p = __ffma2_rn(wb, a, xb1p);
+    ab1[j] = a;
+    qv[j] = q;
   }
+  const float g0 = g0p.x + g0p.y, g1 = g1p.x + g1p.y;
+  float xb0 = xb0p.x + xb0p.y, xb1 = xb1p.x + xb1p.y;
   // ---- rest of A.3
   {
     const float q0 = fmaf(2.0f * psi, x1, s1 * g1);
@@ -236,17 +228,14 @@ GPF_DEV void sf2r_reverse_eval(const float* __restrict__ W, const float* __restr
   }
 #endif
   __syncwarp();  // every lane is done with the other lanes' [ab2 | ws] rows
-  sts4(Wrow + K::O_AB, ab1[0], ab1[1], ab1[2], ab1[3]);
-  sts4(Wrow + K::O_AB + 4, ab1[4], ab1[5], ab1[6], ab1[7]);
-  sts4(Wrow + K::O_AB + 8, ab1[8], ab1[9], ab1[10], ab1[11]);
-  sts4(Wrow + K::O_AB + 12, ab1[12], ab1[13], ab1[14], ab1[15]);
-  sts4(Wrow + K::O_WS, qv[0], qv[1], qv[2], qv[3]);
-  sts4(Wrow + K::O_WS + 4, qv[4], qv[5], qv[6], qv[7]);
-  sts4(Wrow + K::O_WS + 8, qv[8], qv[9], qv[10], qv[11]);
-  sts4(Wrow + K::O_WS + 12, qv[12], qv[13], qv[14], qv[15]);
+#pragma unroll
+  for (int c = 0; c < 4; ++c) {   // by position (row 0 of the dW1 tile is dead)
+    sts4(Wrow + K::O_AB + 4 * c, ab1[2 * c].x, ab1[2 * c].y, ab1[2 * c + 1].x, ab1[2 * c + 1].y);
+    sts4(Wrow + K::O_WS + 4 * c, qv[2 * c].x, qv[2 * c].y, qv[2 * c + 1].x, qv[2 * c + 1].y);
+  }
   __syncwarp();
   // ---- dW1[m][:] += sum_s ab1_s[m] [x0, x1, t, 1]_s + q_s[m] [gb0, gb1, 0, 0]_s;  dw3[p] += sum_s e_s[p]:
-  //      lane (slice, ti) owns units / positions 4ti.. over the samples s = slice (mod 8)
+  //      lane (slice, ti) owns positions 4ti.. (unit + 1) over the samples s = slice (mod 8)
   {
     const int ti = lane & 3, slice = lane >> 2;
 #pragma unroll
