@@ -328,6 +328,103 @@ struct OpW3 {
 };
 
 // ---------------------------------------------------------------------------------------------------------------
+// The same product for a 64-wide last hidden layer (C3: d = 10, nb = 9, H = 64), on the CUDA cores.  There the GEMM above
+// runs 128-row output tiles for groups of at most d rows and spends its time in the fp32 operand fetch (175 us per launch,
+// 14 % of the C3 step); the arithmetic itself is 2e8 FMAs.  Here a CTA owns (16 output rows of one family / group, one
+// sample split): the coefficients of 64 samples are built once in shared memory, each lane keeps two hidden units
+// (one 8-byte load per sample row) and 8 output rows in registers; the 4 sample quarters of the CTA are summed in a fixed
+// order and added to the split's partial plane -- rows of one family are owned by one CTA per split, so no atomics.
+// ---------------------------------------------------------------------------------------------------------------
+inline bool tc_w3_small_enabled() {   // GPFLOW_TC_W3_SMALL=0: the tensor-core GEMM for every width (A/B switch)
+  static const bool on = [] { const char* e = getenv("GPFLOW_TC_W3_SMALL"); return !(e && e[0] == '0'); }();
+  return on;
+}
+constexpr int W3S_ROWS = 16, W3S_CHUNK = 64, W3S_MAXSPLIT = 64;
+struct W3SmallParams {
+  const float *TL, *R, *Qb, *SX, *SQ, *x, *sj;
+  float* gW3;    // [3 families][nsplit][nout][64]
+  int d, nb, nout, S, nF, nDt, nGt, nsplit, spb;
+};
+__global__ void __launch_bounds__(256) tc_w3_small_kernel(const W3SmallParams p) {
+  constexpr int K = 64;
+  __shared__ __align__(16) float coef[2][W3S_ROWS][W3S_CHUNK];
+  __shared__ __align__(16) float red[4][W3S_ROWS][K];
+  const int S = p.S, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int rgrp = warp & 1, sq = warp >> 1;
+  int o = blockIdx.x, fam, idx, row0;
+  if (o < p.nF) { fam = 0; idx = 0; row0 = o * W3S_ROWS; }
+  else if (o < p.nF + p.d * p.nDt) { o -= p.nF; fam = 1; idx = o / p.nDt; row0 = (o % p.nDt) * W3S_ROWS; }
+  else { o -= p.nF + p.d * p.nDt; fam = 2; idx = o / p.nGt; row0 = (o % p.nGt) * W3S_ROWS; }
+  const int cnt_all = fam == 0 ? p.nout : (fam == 1 ? (idx < p.nb - 1 ? idx : p.nb - 1) + 1 : p.d - idx);
+  const int cnt = cnt_all - row0 < W3S_ROWS ? cnt_all - row0 : W3S_ROWS;
+  const int s_begin = blockIdx.y * p.spb, s_end = s_begin + p.spb < S ? s_begin + p.spb : S;
+  if (cnt <= 0 || s_begin >= S) return;
+  const float* X = fam == 0 ? p.TL + (size_t)p.d * S * K : (fam == 1 ? p.TL + (size_t)idx * S * K : p.R + (size_t)idx * S * K);
+  // coefficient of (row r, sample s): thread (s = tid & 63) fills rows tid >> 6, + 4, + 8, + 12
+  const int cs = tid & 63, cr = tid >> 6;
+  auto fill = [&](int buf, int s0) {
+    const int sg = s0 + cs;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int r = cr + 4 * j, q = row0 + r;
+      float v = 0.f;
+      if (r < cnt) {
+        if (fam == 0) {
+          const int i = q / p.nb, n = q - i * p.nb;
+          if (n <= i)
+            v = 2.f * (__ldg(p.Qb + (size_t)i * S + sg) * __ldg(p.SX + (size_t)n * S + sg) -
+                       __ldg(p.x + (size_t)i * S + sg) * __ldg(p.SQ + (size_t)n * S + sg));
+        } else if (fam == 1) {
+          v = -__ldg(p.sj + (size_t)idx * S + sg) * __ldg(p.SQ + (size_t)q * S + sg);
+        } else {
+          v = __ldg(p.Qb + (size_t)(idx + q) * S + sg);
+        }
+      }
+      coef[buf][r][cs] = v;
+    }
+  };
+  float2 acc[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) acc[j] = make_float2(0.f, 0.f);
+  fill(0, s_begin);
+  __syncthreads();
+  int buf = 0;
+  for (int s0 = s_begin; s0 < s_end; s0 += W3S_CHUNK, buf ^= 1) {
+    if (s0 + W3S_CHUNK < s_end) fill(buf ^ 1, s0 + W3S_CHUNK);
+    const float* xr = X + (size_t)(s0 + sq * 16) * K + 2 * lane;
+#pragma unroll
+    for (int g4 = 0; g4 < 4; ++g4) {
+      float2 xv[4];
+#pragma unroll
+      for (int e = 0; e < 4; ++e) xv[e] = __ldg(reinterpret_cast<const float2*>(xr + (size_t)(4 * g4 + e) * K));
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float4 c = *reinterpret_cast<const float4*>(&coef[buf][rgrp * 8 + j][sq * 16 + 4 * g4]);
+        acc[j].x = fmaf(c.x, xv[0].x, acc[j].x); acc[j].y = fmaf(c.x, xv[0].y, acc[j].y);
+        acc[j].x = fmaf(c.y, xv[1].x, acc[j].x); acc[j].y = fmaf(c.y, xv[1].y, acc[j].y);
+        acc[j].x = fmaf(c.z, xv[2].x, acc[j].x); acc[j].y = fmaf(c.z, xv[2].y, acc[j].y);
+        acc[j].x = fmaf(c.w, xv[3].x, acc[j].x); acc[j].y = fmaf(c.w, xv[3].y, acc[j].y);
+      }
+    }
+    __syncthreads();
+  }
+#pragma unroll
+  for (int j = 0; j < 8; ++j) *reinterpret_cast<float2*>(&red[sq][rgrp * 8 + j][2 * lane]) = acc[j];
+  __syncthreads();
+  float* plane = p.gW3 + (size_t)(fam * p.nsplit + blockIdx.y) * p.nout * K;
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const int e = tid + 256 * j, r = e >> 6, k = e & 63;
+    if (r < cnt) {
+      const int q = row0 + r;
+      const int prow = fam == 0 ? q : (fam == 1 ? idx * p.nb + q : (idx + q) * p.nb + idx);
+      const float v = ((red[0][r][k] + red[1][r][k]) + red[2][r][k]) + red[3][r][k];
+      plane[(size_t)prow * K + k] += v;
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------------
 // hidden layer weight gradient: dW_l[k][m] += sum_r Ub_l[r][k] T_{l-1}[r][m], r over the (d+1) S rows of the slab
 // (tangent rows and, in row block d, ab_l against h_{l-1}).  Split-K over the CTAs: CTA b = (128-row tile km, split sp)
 // owns the partial gWp[b] and adds its segments to it in order.
@@ -437,6 +534,7 @@ struct TcBuf {   // offsets in floats
   size_t stash, sj, sp[TC_MAXL + 1], T[TC_MAXL + 1], Ub[TC_MAXL + 1], R, Rb, hbp, F, G, D, SX, FX, SD, Q, v, ksum;
   size_t vbar, Qb, SQ, SXb, ybar, ybsum, ybprev, xb, ot_s, lg_s, total;
   int nseg_hb, nchunk_p, npad[TC_MAXL + 1], npadT[TC_MAXL + 1], wsplit_G[TC_MAXL + 1], w3_nsplit, nz, s_per_z;
+  bool w3_small;
 };
 
 inline size_t tc_per_sample_floats(const TcDims& g, int n_steps, bool train) {
@@ -510,6 +608,8 @@ inline void tc_carve(const TcDims& g, int n_steps, bool train, int sm_count, TcB
       b.w3_nsplit = 2 * n_out > sm_count ? 4 : sm_count / n_out;   // many tiles: 4 splits even out the rounds
       if (b.w3_nsplit > nseg) b.w3_nsplit = nseg;
       if (b.w3_nsplit < 1) b.w3_nsplit = 1;
+      b.w3_small = tc_w3_small_enabled() && HL == 64;
+      if (b.w3_small) b.w3_nsplit = S / W3S_CHUNK < W3S_MAXSPLIT ? S / W3S_CHUNK : W3S_MAXSPLIT;
     }
     b.gW3 = take((size_t)3 * b.w3_nsplit * g.nout * HL);
     b.gb3 = take(g.nout);
@@ -704,7 +804,17 @@ int tc_run(const GpFlowDesc* d, int op, const float* params, const float* x_in, 
       p.nseg = b.nseg_hb; p.nchunk_p = b.nchunk_p;
       TC_CK(launch_gemm<LBOp>(p, (b.nseg_hb + nb + dd) * mt, sm_count, st));
     }
-    {
+    if (b.w3_small) {
+      W3SmallParams p;
+      p.TL = P(b.T[L]); p.R = P(b.R); p.Qb = P(b.Qb); p.SX = P(b.SX); p.SQ = P(b.SQ); p.x = xpt; p.sj = P(b.sj);
+      p.gW3 = P(b.gW3);
+      p.d = dd; p.nb = nb; p.nout = g.nout; p.S = S;
+      p.nF = (g.nout + W3S_ROWS - 1) / W3S_ROWS; p.nDt = (nb + W3S_ROWS - 1) / W3S_ROWS; p.nGt = (dd + W3S_ROWS - 1) / W3S_ROWS;
+      p.nsplit = b.w3_nsplit;
+      p.spb = ((S + p.nsplit - 1) / p.nsplit + W3S_CHUNK - 1) / W3S_CHUNK * W3S_CHUNK;
+      tc_w3_small_kernel<<<dim3(p.nF + dd * p.nDt + nb * p.nGt, p.nsplit), 256, 0, st>>>(p);
+      TC_KCK();
+    } else {
       typename W3Op::Params p;
       p.TL = P(b.T[L]); p.R = P(b.R); p.Qb = P(b.Qb); p.SX = P(b.SX); p.SQ = P(b.SQ); p.x = xpt; p.sj = P(b.sj);
       p.gW3 = P(b.gW3);

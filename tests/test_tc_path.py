@@ -21,6 +21,7 @@ SHAPES = [
     (17, 16, (100, 70), 260, 3, 0.02),       # 256-wide tile instantiation, widths padded to 128
     (3, 1, (33, 200), 129, 3, 0.06),         # nb = 1, narrow -> wide
     (12, 5, (128, 64), 257, 3, 0.03),        # wide -> narrow (Ub_1 does not alias T_2)
+    (18, 17, (48,), 140, 3, 0.02),           # 64-wide last layer with nb, d > 16: several row tiles per group in tc_w3_small_kernel
 ]
 
 
