@@ -150,29 +150,33 @@ __global__ void tc_prep_last_kernel(TcDims g, const float* __restrict__ p, TcWei
 // ---------------------------------------------------------------------------------------------------------------
 // first layer (vector_field.py:84-88,109-118 for l = 1): a = W1x x + w1t t + b1, h = tanh a, sp = 1 - h^2, tangent rows
 // T1[j] = sp (.) W1x[:, j] (U_1 = W1x is the same for every sample), s_j = x_j^2 - (1 - eps).  Block = 8 samples x Hp1 units.
+// DB: compile-time bound on d (the per-direction loops are unrolled and predicated: at d = 10 a bound of 64 made the kernel
+// instruction-bound, ncu: issue slots 53 % busy at 24 % occupancy); SPB: samples per block (fewer = more blocks in flight).
+template <int DB, int SPB>
 __global__ void tc_layer1_kernel(TcDims g, const float* __restrict__ W1T, const float* __restrict__ b1,
                                  const float* __restrict__ x /*CL [d][S]*/, float t, float bnd, float* __restrict__ T1 /*[(d+1) S][Hp1]*/,
                                  float* __restrict__ sp1 /*[S][Hp1]*/, float* __restrict__ sj /*CL [d][S]*/,
                                  int write_tangents /* 0: the consumers regenerate T1[j] = sp1 (.) W1x[:, j] on the fly */) {
-  __shared__ float xs[TC_DMAX][TC_L1_SPB];
+  __shared__ float xs[DB][SPB];
   const int H = g.Hp[1], d = g.d, S = g.S;
-  const int s0 = blockIdx.x * TC_L1_SPB, k = threadIdx.x;
-  for (int e = threadIdx.x; e < d * TC_L1_SPB; e += blockDim.x) {
-    const int j = e / TC_L1_SPB, q = e % TC_L1_SPB;
+  const int s0 = blockIdx.x * SPB, k = threadIdx.x;
+  for (int e = threadIdx.x; e < d * SPB; e += blockDim.x) {
+    const int j = e / SPB, q = e % SPB;
     const float xv = x[(size_t)j * S + s0 + q];
     xs[j][q] = xv;
     sj[(size_t)j * S + s0 + q] = xv * xv - bnd;
   }
   __syncthreads();
-  float w[TC_DMAX];
+  float w[DB];
 #pragma unroll
-  for (int j = 0; j < TC_DMAX; ++j) w[j] = j < d ? W1T[j * H + k] : 0.f;
+  for (int j = 0; j < DB; ++j) w[j] = j < d ? W1T[j * H + k] : 0.f;
   const float a0 = fmaf(W1T[d * H + k], t, b1[k]);
-  for (int q = 0; q < TC_L1_SPB; ++q) {
+#pragma unroll
+  for (int q = 0; q < SPB; ++q) {
     const int s = s0 + q;
     float a = a0;
 #pragma unroll
-    for (int j = 0; j < TC_DMAX; ++j)
+    for (int j = 0; j < DB; ++j)
       if (j < d) a = fmaf(w[j], xs[j][q], a);
     const float h = act_tanh(a);
     const float sp = 1.f - h * h;
@@ -180,7 +184,7 @@ __global__ void tc_layer1_kernel(TcDims g, const float* __restrict__ W1T, const 
     T1[((size_t)d * S + s) * H + k] = h;
     if (write_tangents) {
 #pragma unroll
-      for (int j = 0; j < TC_DMAX; ++j)
+      for (int j = 0; j < DB; ++j)
         if (j < d) T1[((size_t)j * S + s) * H + k] = sp * w[j];
     }
   }
@@ -382,7 +386,9 @@ __global__ void tc_layer1_bwd_a_kernel(TcDims g, const float* __restrict__ W1T, 
 }
 // part b: dW1x[:, j] += sum_s (ab_1 x_j + sp Tb_1[j]),  dw1t += sum_s ab_1 t,  db1 += sum_s ab_1.
 // Grid (Hp1 / 32, ceil(d / 8), nz): a block reduces 8 tangent directions over its sample range (8 warps stride the
-// samples), partials [nz][Hp1][d + 2] are summed in a fixed order by tc_reduce_add_kernel.
+// samples) and ADDS the result to its entry of the per-split planes [nz][Hp1][d + 2] (one owner thread per entry, calls
+// are stream-ordered: deterministic); the planes live for the whole call (zeroed with the gradient accumulators) and are
+// summed once, in a fixed order, by tc_reduce_add_kernel -- not once per evaluation (240 single-block launches per C3 step).
 __global__ void __launch_bounds__(256) tc_layer1_bwd_b_kernel(TcDims g, const float* __restrict__ sp1, const float* __restrict__ Ub,
                                                                const float* __restrict__ x, float t, int s_per_z, float* __restrict__ part) {
   __shared__ float red[8][10][33];
@@ -412,9 +418,66 @@ __global__ void __launch_bounds__(256) tc_layer1_bwd_b_kernel(TcDims g, const fl
     for (int e = 0; e < 10; ++e) {
       float v = 0.f;
       for (int r = 0; r < 8; ++r) v += red[r][e][lane];
-      if (e < 8) { if (j0 + e < d) o[j0 + e] = v; }
-      else if (blockIdx.y == 0) o[d + (e - 8)] = v;
+      if (e < 8) { if (j0 + e < d) o[j0 + e] += v; }
+      else if (blockIdx.y == 0) o[d + (e - 8)] += v;
     }
+  }
+}
+// The same for a 64-wide first layer and d <= DB (C3).  The kernel above keeps 4 096 warps on a serial chain of 4 load
+// batches (ncu at C3: 67 us per launch, long_scoreboard 84 % of the stall samples, 22 % occupancy).  Here a block owns
+// TC_L1B_CH = 32 samples and one plane: thread = (4 units, 1 of 16 sample rows), every load is a float4 and all the loads of a
+// thread (2 samples x (d + 2)) are independent; the 16 sample rows are summed by one shuffle and a fixed-order pass over
+// the 8 warps.  Grid S / 32.
+constexpr int TC_L1B_CH = 32;
+template <int DB>
+__global__ void __launch_bounds__(256) tc_layer1_bwd_b_small_kernel(TcDims g, const float* __restrict__ sp1, const float* __restrict__ Ub,
+                                                                     const float* __restrict__ x, float t, float* __restrict__ part) {
+  constexpr int H = 64;
+  __shared__ float xs[DB][TC_L1B_CH];
+  __shared__ float4 red[8][DB + 2][16];
+  const int d = g.d, S = g.S, tid = threadIdx.x, k4 = tid & 15, sr = tid >> 4, lane = tid & 31, warp = tid >> 5;
+  const int s0 = blockIdx.x * TC_L1B_CH;
+  for (int e = tid; e < d * TC_L1B_CH; e += 256) {
+    const int j = e / TC_L1B_CH, q = e % TC_L1B_CH;
+    xs[j][q] = x[(size_t)j * S + s0 + q];
+  }
+  __syncthreads();
+  float4 acc[DB], gb = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+  for (int j = 0; j < DB; ++j) acc[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+  for (int i = 0; i < TC_L1B_CH / 16; ++i) {
+    const int q = sr + 16 * i, s = s0 + q;
+    const float4 sp = __ldg(reinterpret_cast<const float4*>(sp1 + (size_t)s * H) + k4);
+    const float4 ab = __ldg(reinterpret_cast<const float4*>(Ub + ((size_t)d * S + s) * H) + k4);
+    gb.x += ab.x; gb.y += ab.y; gb.z += ab.z; gb.w += ab.w;
+#pragma unroll
+    for (int j = 0; j < DB; ++j)
+      if (j < d) {
+        const float4 u = __ldg(reinterpret_cast<const float4*>(Ub + ((size_t)j * S + s) * H) + k4);
+        const float xj = xs[j][q];
+        acc[j].x += fmaf(ab.x, xj, sp.x * u.x); acc[j].y += fmaf(ab.y, xj, sp.y * u.y);
+        acc[j].z += fmaf(ab.z, xj, sp.z * u.z); acc[j].w += fmaf(ab.w, xj, sp.w * u.w);
+      }
+  }
+  auto fold = [&](float4 v, int o) {   // the two sample rows of a warp, then its slot
+    v.x += __shfl_xor_sync(0xffffffffu, v.x, 16); v.y += __shfl_xor_sync(0xffffffffu, v.y, 16);
+    v.z += __shfl_xor_sync(0xffffffffu, v.z, 16); v.w += __shfl_xor_sync(0xffffffffu, v.w, 16);
+    if (lane < 16) red[warp][o][k4] = v;
+  };
+#pragma unroll
+  for (int j = 0; j < DB; ++j)
+    if (j < d) fold(acc[j], j);
+  fold(make_float4(gb.x * t, gb.y * t, gb.z * t, gb.w * t), d);
+  fold(gb, d + 1);
+  __syncthreads();
+  const float* rf = reinterpret_cast<const float*>(&red[0][0][0]);
+  for (int e = tid; e < (d + 2) * H; e += 256) {
+    const int o = e / H, k = e % H;
+    float v = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) v += rf[(w * (DB + 2) + o) * H + k];
+    part[((size_t)blockIdx.x * H + k) * (d + 2) + o] += v;
   }
 }
 // acc[e] += sum_z part[z][e]  (fixed order)
@@ -439,18 +502,18 @@ __global__ void tc_colsum_kernel(int S, int H, int s_per_z, const float* __restr
   if (y == 0 && k < H) {
     float t = 0.f;
     for (int q = 0; q < 8; ++q) t += red[q][threadIdx.x];
-    part[(size_t)blockIdx.y * H + k] = t;
+    part[(size_t)blockIdx.y * H + k] += t;   // persistent per-split plane, see tc_layer1_bwd_b_kernel
   }
 }
 // db_{L+1}[(i,n)] = sum_s fb_(i,n)[s],  fb = 2 (Qb_i SX_n - x_i SQ_n), kept rows only: partial sums over 256-sample
-// splits, part[z][i nb + n].  Grid (ceil(nb / 16), ceil(d / 16), S / 256), block 16 x 16 (i, n).
+// splits, part[z][i nb + n].  Grid (ceil(nb / 16), ceil(d / 16), S / chunk), block 16 x 16 (i, n); chunk = 64 or 256.
 __global__ void tc_db3_kernel(TcDims g, const float* __restrict__ Qb, const float* __restrict__ x, const float* __restrict__ SX,
-                              const float* __restrict__ SQ, float* __restrict__ part) {
+                              const float* __restrict__ SQ, int chunk, float* __restrict__ part) {
   __shared__ float a[4][16][65];
   const int S = g.S, i = blockIdx.y * 16 + threadIdx.y, n = blockIdx.x * 16 + threadIdx.x;
   const int tid = threadIdx.y * 16 + threadIdx.x;
   float acc = 0.f;
-  for (int s0 = blockIdx.z * 256; s0 < blockIdx.z * 256 + 256; s0 += 64) {
+  for (int s0 = blockIdx.z * chunk; s0 < blockIdx.z * chunk + chunk; s0 += 64) {
     for (int e = tid; e < 4 * 16 * 64; e += 256) {
       const int arr = e / 1024, r = (e / 64) % 16, c = e % 64;
       const int row = (arr < 2 ? blockIdx.y : blockIdx.x) * 16 + r;
@@ -464,7 +527,7 @@ __global__ void tc_db3_kernel(TcDims g, const float* __restrict__ Qb, const floa
       acc += a[0][threadIdx.y][c] * a[2][threadIdx.x][c] - a[1][threadIdx.y][c] * a[3][threadIdx.x][c];
     __syncthreads();
   }
-  if (i < g.d && n < g.nb) part[(size_t)blockIdx.z * g.nout + i * g.nb + n] = n <= i ? 2.f * acc : 0.f;
+  if (i < g.d && n < g.nb && n <= i) part[(size_t)blockIdx.z * g.nout + i * g.nb + n] += 2.f * acc;   // persistent plane
 }
 
 // ---------------------------------------------------------------------------------------------------------------

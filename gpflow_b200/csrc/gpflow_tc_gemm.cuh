@@ -289,14 +289,24 @@ struct EpiCtx {
 template <class Op, class = void> struct OpATma { static constexpr bool value = false; };
 template <class Op> struct OpATma<Op, decltype((void)Op::A_TMA)> { static constexpr bool value = Op::A_TMA; };
 
+// Op::N_CAT (optional, default false; needs NT <= 128): the hi and lo tiles of B lie back to back in a stage, so ONE
+// instruction of N = NT + n multiplies A_hi by both: D[:, 0:NT) += A_hi B_hi, D[:, NT:NT+n) += A_hi B_lo, then A_lo B_hi
+// goes into the first block -- 2 instructions per K step instead of 3, and the epilogue adds the two column blocks.
+// A tcgen05.mma from shared-memory operands costs ~107 cycles at N = 64 and ~114 at N = 128 (measured: the A tile is
+// re-read for every instruction), so a 64-wide layer is bound by the instruction count, not by the flops.
+template <class Op, class = void> struct OpNCat { static constexpr bool value = false; };
+template <class Op> struct OpNCat<Op, decltype((void)Op::N_CAT)> { static constexpr bool value = Op::N_CAT; };
+
 template <class Op>
 struct GemmSmem {
+  static constexpr uint32_t kAccCols = OpNCat<Op>::value ? 2 * Op::NT : Op::NT;   // TMEM columns of one accumulator buffer
+  static_assert(!OpNCat<Op>::value || Op::NT <= 128, "N_CAT: NT + n <= 256");
   static constexpr uint32_t kBTileBytes = Op::NT * 128;
   static constexpr uint32_t kStageBytes = 2 * kATileBytes + 2 * kBTileBytes;
   static constexpr uint32_t kEpiOff = Op::STAGES * kStageBytes;
   static constexpr uint32_t kBarOff = kEpiOff + kEpiWarps * 4096;
   static constexpr uint32_t kBytes = kBarOff + 256 + 1024;   // + barriers + slack for the 1024-byte alignment
-  static constexpr uint32_t kTmemCols = 2 * Op::NT <= 32 ? 32 : 2 * Op::NT <= 64 ? 64 : 2 * Op::NT <= 128 ? 128 : 2 * Op::NT <= 256 ? 256 : 512;
+  static constexpr uint32_t kTmemCols = 2 * kAccCols <= 32 ? 32 : 2 * kAccCols <= 64 ? 64 : 2 * kAccCols <= 128 ? 128 : 2 * kAccCols <= 256 ? 256 : 512;
   static_assert(Op::NT % 16 == 0 && Op::NT >= 16 && Op::NT <= 256, "N tile");
   static_assert(kBytes <= 227 * 1024, "shared memory");
 };
@@ -381,14 +391,25 @@ __global__ void __launch_bounds__(kThreads, 1) tc_gemm_kernel(const __grid_const
         if (tile.nk == 0) continue;
         { const long long c0_ = clock64(); mbar_wait_bounded(&accempty_bar[acc], acc_phase ^ 1); prof_wait_acc += clock64() - c0_; }
         tcgen05_fence_after();
-        const uint32_t tmem_d = tmem_base + acc * Op::NT;
+        const uint32_t tmem_d = tmem_base + acc * SM::kAccCols;
         const uint32_t idesc = make_idesc_tf32(MT, tile.n);
+        const uint32_t idesc_cat = make_idesc_tf32(MT, Op::NT + tile.n);
+        (void)idesc_cat;
         for (int kc = 0; kc < tile.nk; ++kc) {
           GPF_TC_WAIT(&full_bar[stage], phase);
           tcgen05_fence_after();
           const uint32_t sa = smem_u32(smem + stage * SM::kStageBytes);
           const uint64_t da_hi = make_desc_sw128(sa), da_lo = make_desc_sw128(sa + kATileBytes);
           const uint64_t db_hi = make_desc_sw128(sa + 2 * kATileBytes), db_lo = make_desc_sw128(sa + 2 * kATileBytes + SM::kBTileBytes);
+          if constexpr (OpNCat<Op>::value) {
+#pragma unroll
+            for (int k = 0; k < KC / 8; ++k) {
+              const uint64_t adv = (uint64_t)(k * 2);
+              umma_tf32(tmem_d, da_hi + adv, db_hi + adv, idesc_cat, (kc | k) != 0);   // B rows: NT of the hi tile, n of the lo tile
+              umma_tf32(tmem_d, da_lo + adv, db_hi + adv, idesc, 1u);
+            }
+            (void)db_lo;
+          } else {
           // the two correction products first (they are ~2^-11 of the main one), then hi x hi
 #pragma unroll
           for (int k = 0; k < KC / 8; ++k) {
@@ -400,6 +421,7 @@ __global__ void __launch_bounds__(kThreads, 1) tc_gemm_kernel(const __grid_const
           for (int k = 0; k < KC / 8; ++k) {
             const uint64_t adv = (uint64_t)(k * 2);
             umma_tf32(tmem_d, da_hi + adv, db_hi + adv, idesc, 1u);
+          }
           }
           umma_commit(&empty_bar[stage]);   // frees the smem stage when these MMAs have read it
           if (++stage == Op::STAGES) { stage = 0; phase ^= 1; }
@@ -429,12 +451,19 @@ __global__ void __launch_bounds__(kThreads, 1) tc_gemm_kernel(const __grid_const
       if (tile.nk == 0) continue;
       GPF_TC_WAIT(&accfull_bar[acc], acc_phase);
       tcgen05_fence_after();
-      const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + acc * Op::NT;
+      const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + acc * SM::kAccCols;
       for (int c0 = 0; c0 < tile.n; c0 += 32) {
         float v[32];
         const int nc = tile.n - c0 < 32 ? tile.n - c0 : 32;   // 16 or 32
         if (nc == 32) tmem_ld32(taddr + c0, v);
         else tmem_ld16(taddr + c0, v);
+        if constexpr (OpNCat<Op>::value) {   // + the A_hi B_lo block
+          float u[32];
+          if (nc == 32) tmem_ld32(taddr + Op::NT + c0, u);
+          else tmem_ld16(taddr + Op::NT + c0, u);
+#pragma unroll
+          for (int i = 0; i < 32; ++i) v[i] += (i < nc) ? u[i] : 0.f;
+        }
         Op::epilogue(p, tile, ctx, row, c0, nc, v);
       }
       tcgen05_fence_before();

@@ -5,6 +5,15 @@
 
 #include "gpflow_tc.cuh"
 
+// 1: the 64-wide layer GEMMs issue 2 instead of 3 tcgen05.mma per K step (Op::N_CAT, gpflow_tc_gemm.cuh).  Parity-green,
+// measured on the engine test at M = 180 224, N = K = 64 (the C3 tangent layer): 30 us against 28 us, C3 step 60.7 against
+// 60.1 ms -- the MMA thread is then idle waiting for the epilogue, which reads twice the TMEM columns; the tile time at this
+// width (~3.7 kclk per 128 x 64 x 64) is set by the shared-memory path (operand stores, MMA operand reads, epilogue
+// staging), not by the instruction count.  Kept as a build switch.
+#ifndef GPF_TC_NCAT
+#define GPF_TC_NCAT 0
+#endif
+
 namespace gpflow {
 namespace tc {
 
@@ -19,6 +28,7 @@ template <int NT_, int ST_>
 struct OpLayer {
   static constexpr int NT = NT_, STAGES = ST_;
   static constexpr bool B_TMA = true;
+  static constexpr bool N_CAT = NT_ <= 64 && GPF_TC_NCAT;   // narrow layers are bound by the MMA instruction count
   static constexpr int A_MODE = MODE_ROWS, B_MODE = MODE_ROWS;
   struct Params {
     CUtensorMap map;
@@ -530,11 +540,12 @@ struct TcPlan {
 };
 struct TcBuf {   // offsets in floats
   size_t W1T, bp[TC_MAXL + 1], Ws[TC_MAXL + 1], WTs[TC_MAXL + 1], W3s, W3Gs, W3Ts, W3GTs, W3JTs, weights_end;
-  size_t gW1, zpart, gWp[TC_MAXL + 1], gb[TC_MAXL + 1], gW3, gb3, scal, grads_end;
+  size_t gW1, zW1, zb[TC_MAXL + 1], zb3, gWp[TC_MAXL + 1], gb[TC_MAXL + 1], gW3, gb3, scal, grads_end;
   size_t stash, sj, sp[TC_MAXL + 1], T[TC_MAXL + 1], Ub[TC_MAXL + 1], R, Rb, hbp, F, G, D, SX, FX, SD, Q, v, ksum;
   size_t vbar, Qb, SQ, SXb, ybar, ybsum, ybprev, xb, ot_s, lg_s, total;
   int nseg_hb, nchunk_p, npad[TC_MAXL + 1], npadT[TC_MAXL + 1], wsplit_G[TC_MAXL + 1], w3_nsplit, nz, s_per_z;
-  bool w3_small;
+  bool w3_small, l1b_small;
+  int nz1;
 };
 
 inline size_t tc_per_sample_floats(const TcDims& g, int n_steps, bool train) {
@@ -594,8 +605,18 @@ inline void tc_carve(const TcDims& g, int n_steps, bool train, int sm_count, TcB
   b.W3GTs = take((size_t)g.nb * 2 * g.HTp * g.dpad);
   b.W3JTs = take((size_t)g.d * 2 * g.HTp * g.nbpad);
   b.weights_end = off;
+  // two-stage reductions over the samples (fixed order): nz splits of the slab, per-split planes [nz][n] that the kernels
+  // add to during the whole call, summed once at the end (tc_reduce_add_kernel)
+  static const int nz_max = [] { const char* e = getenv("GPFLOW_TC_NZ"); const int v = e ? atoi(e) : 0; return v >= 1 ? v : 128; }();   // C3 row: 70.8 ms at 32, 67.9 at 64, 67.6 at 128, 67.4 at 256
+  b.nz = S / 64 < nz_max ? S / 64 : nz_max;
+  b.s_per_z = (S + b.nz - 1) / b.nz;
   if (train) {
     b.gW1 = take((size_t)g.Hp[1] * (d + 2));
+    b.l1b_small = g.Hp[1] == 64 && d <= 16;            // tc_layer1_bwd_b_small_kernel: one plane per 32 samples
+    b.nz1 = b.l1b_small ? S / TC_L1B_CH : b.nz;
+    b.zW1 = take((size_t)b.nz1 * g.Hp[1] * (d + 2));
+    b.zb3 = take((size_t)(S / 64) * g.nout);
+    for (int l = 2; l <= L; ++l) b.zb[l] = take((size_t)b.nz * g.Hp[l]);
     for (int l = 2; l <= L; ++l) {
       const int mt = (g.Hp[l] + MT - 1) / MT;
       b.wsplit_G[l] = (sm_count / mt < 1 ? 1 : sm_count / mt) * mt;   // upper bound on CTAs = partial buffers
@@ -616,16 +637,6 @@ inline void tc_carve(const TcDims& g, int n_steps, bool train, int sm_count, TcB
   }
   b.scal = take(4);
   b.grads_end = off;
-  // two-stage reductions over the samples (fixed order): nz splits of the slab, partials [nz][n]
-  static const int nz_max = [] { const char* e = getenv("GPFLOW_TC_NZ"); const int v = e ? atoi(e) : 0; return v >= 1 ? v : 128; }();   // C3 row: 70.8 ms at 32, 67.9 at 64, 67.6 at 128, 67.4 at 256
-  b.nz = S / 64 < nz_max ? S / 64 : nz_max;
-  b.s_per_z = (S + b.nz - 1) / b.nz;
-  if (train) {
-    size_t n = (size_t)g.Hp[1] * (d + 2);
-    for (int l = 2; l <= L; ++l) n = (size_t)g.Hp[l] > n ? g.Hp[l] : n;
-    const size_t n3 = (size_t)(S / 256) * g.nout;
-    b.zpart = take((size_t)b.nz * n > n3 ? (size_t)b.nz * n : n3);
-  }
   b.stash = take((size_t)(4 * n_steps + 1) * d * S);
   b.sj = take((size_t)d * S);
   for (int l = 1; l <= L; ++l) {
@@ -747,7 +758,10 @@ int tc_run(const GpFlowDesc* d, int op, const float* params, const float* x_in, 
 
   // ---- one velocity evaluation, forward: activations of the slab at the stage point xpt, time t (up to SX / FX / SD) ----
   auto eval_forward = [&](const float* xpt, float t) -> int {
-    tc_layer1_kernel<<<S / TC_L1_SPB, g.Hp[1], 0, st>>>(g, w.W1T, w.bp[1], xpt, t, bnd, P(b.T[1]), P(b.sp[1]), P(b.sj), (L == 1 || !gen_t1) ? 1 : 0);
+    if (dd <= 16)
+      tc_layer1_kernel<16, 4><<<S / 4, g.Hp[1], 0, st>>>(g, w.W1T, w.bp[1], xpt, t, bnd, P(b.T[1]), P(b.sp[1]), P(b.sj), (L == 1 || !gen_t1) ? 1 : 0);
+    else
+      tc_layer1_kernel<TC_DMAX, TC_L1_SPB><<<S / TC_L1_SPB, g.Hp[1], 0, st>>>(g, w.W1T, w.bp[1], xpt, t, bnd, P(b.T[1]), P(b.sp[1]), P(b.sj), (L == 1 || !gen_t1) ? 1 : 0);
     TC_KCK();
     for (int l = 2; l <= L; ++l) {
       typename LayerOp::Params p;
@@ -834,9 +848,7 @@ int tc_run(const GpFlowDesc* d, int op, const float* params, const float* x_in, 
       tc_gemm_kernel<W3Op><<<p.G, kThreads, SMW::kBytes, st>>>(p);
       TC_KCK();
     }
-    tc_db3_kernel<<<dim3((nb + 15) / 16, (dd + 15) / 16, S / 256), dim3(16, 16), 0, st>>>(g, P(b.Qb), xpt, P(b.SX), P(b.SQ), P(b.zpart));
-    TC_KCK();
-    tc_reduce_add_kernel<<<(g.nout + 255) / 256, 256, 0, st>>>(S / 256, g.nout, P(b.zpart), P(b.gb3));
+    tc_db3_kernel<<<dim3((nb + 15) / 16, (dd + 15) / 16, S / 64), dim3(16, 16), 0, st>>>(g, P(b.Qb), xpt, P(b.SX), P(b.SQ), 64, P(b.zb3));
     TC_KCK();
     tc_tb_last_kernel<<<S, HL, 0, st>>>(g, P(b.T[L]), P(b.sp[L]), P(b.Rb), P(b.hbp), b.nseg_hb, P(b.sj), xpt, P(b.Ub[L]),
                                         P(b.ybar), L == 1 ? 1 : 0);
@@ -862,9 +874,7 @@ int tc_run(const GpFlowDesc* d, int op, const float* params, const float* x_in, 
         TC_KCK();
       }
       tc_colsum_kernel<<<dim3((g.Hp[l] + 31) / 32, b.nz), dim3(32, 8), 0, st>>>(S, g.Hp[l], b.s_per_z,
-                                                                                P(b.Ub[l]) + (size_t)dd * S * g.Hp[l], P(b.zpart));
-      TC_KCK();
-      tc_reduce_add_kernel<<<(g.Hp[l] + 255) / 256, 256, 0, st>>>(b.nz, g.Hp[l], P(b.zpart), P(b.gb[l]));
+                                                                                P(b.Ub[l]) + (size_t)dd * S * g.Hp[l], P(b.zb[l]));
       TC_KCK();
       {
         typename LayerOp::Params p;
@@ -881,11 +891,11 @@ int tc_run(const GpFlowDesc* d, int op, const float* params, const float* x_in, 
     }
     tc_layer1_bwd_a_kernel<<<S / TC_L1B_SPB, g.Hp[1], 0, st>>>(g, w.W1T, P(b.T[1]), P(b.sp[1]), P(b.Ub[1]), P(b.ybar));
     TC_KCK();
-    tc_layer1_bwd_b_kernel<<<dim3(g.Hp[1] / 32, (dd + 7) / 8, b.nz), dim3(32, 8), 0, st>>>(g, P(b.sp[1]), P(b.Ub[1]), xpt, t,
-                                                                                       b.s_per_z, P(b.zpart));
-    TC_KCK();
-    const int n1 = g.Hp[1] * (dd + 2);
-    tc_reduce_add_kernel<<<(n1 + 255) / 256, 256, 0, st>>>(b.nz, n1, P(b.zpart), P(b.gW1));
+    if (b.l1b_small)
+      tc_layer1_bwd_b_small_kernel<16><<<S / TC_L1B_CH, 256, 0, st>>>(g, P(b.sp[1]), P(b.Ub[1]), xpt, t, P(b.zW1));
+    else
+      tc_layer1_bwd_b_kernel<<<dim3(g.Hp[1] / 32, (dd + 7) / 8, b.nz), dim3(32, 8), 0, st>>>(g, P(b.sp[1]), P(b.Ub[1]), xpt, t,
+                                                                                         b.s_per_z, P(b.zW1));
     TC_KCK();
     return GPFLOW_OK;
   };
@@ -965,6 +975,16 @@ int tc_run(const GpFlowDesc* d, int op, const float* params, const float* x_in, 
     memset(&tabs, 0, sizeof(tabs));
     if (train)
     {
+      // the per-split planes of the bias / first-layer gradients, summed once per call in a fixed order
+      const int n1 = g.Hp[1] * (dd + 2);
+      tc_reduce_add_kernel<<<(n1 + 255) / 256, 256, 0, st>>>(b.nz1, n1, P(b.zW1), P(b.gW1));
+      TC_KCK();
+      tc_reduce_add_kernel<<<(g.nout + 255) / 256, 256, 0, st>>>(S / 64, g.nout, P(b.zb3), P(b.gb3));
+      TC_KCK();
+      for (int l = 2; l <= L; ++l) {
+        tc_reduce_add_kernel<<<(g.Hp[l] + 255) / 256, 256, 0, st>>>(b.nz, g.Hp[l], P(b.zb[l]), P(b.gb[l]));
+        TC_KCK();
+      }
       for (int l = 2; l <= L; ++l) { tabs.gWp[l] = P(b.gWp[l]); tabs.gb[l] = P(b.gb[l]); tabs.ns[l] = wsplit_ns[l]; }
       tabs.ns3 = 3 * b.w3_nsplit;
     }

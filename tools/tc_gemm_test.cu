@@ -5,6 +5,7 @@
 #include <stdio.h>
 #include <stdlib.h>
 
+#include <type_traits>
 #include <vector>
 
 #define GPF_TC_PROF 1
@@ -130,7 +131,10 @@ __global__ void split_kernel(const float* w, float* out, int n_rows, int K, int 
 
 static double frand() { return (double)rand() / RAND_MAX * 2.0 - 1.0; }
 
-template <int NT, int ST>
+template <int NT_, int ST_>
+struct OpPlainCat : OpPlain<NT_, ST_> { static constexpr bool N_CAT = true; };   // 2 instructions per K step (engine header)
+
+template <int NT, int ST, bool CAT = false>
 static int run_plain(int M, int N, int K, int sm, bool timing) {
   std::vector<float> A((size_t)M * K), W((size_t)N * K);
   for (auto& x : A) x = (float)frand();
@@ -144,7 +148,7 @@ static int run_plain(int M, int N, int K, int sm, bool timing) {
   CK(cudaMemcpy(dA, A.data(), A.size() * 4, cudaMemcpyHostToDevice));
   CK(cudaMemcpy(dW, W.data(), W.size() * 4, cudaMemcpyHostToDevice));
   split_kernel<<<(N * K + 255) / 256, 256>>>(dW, dWs, N, K, npad);
-  using Op = OpPlain<NT, ST>;
+  using Op = typename std::conditional<CAT, OpPlainCat<NT, ST>, OpPlain<NT, ST>>::type;
   typename Op::Params p;
   if (!make_tmap_2d(&p.map, dWs, (uint64_t)2 * npad, (uint64_t)K, (uint64_t)K, NT)) { printf("tensor map failed\n"); return 1; }
   p.A = dA; p.D = dD; p.M = M; p.N = N; p.K = K; p.npad = npad; p.prof = nullptr; p.dbg = 0;
@@ -162,7 +166,7 @@ static int run_plain(int M, int N, int K, int sm, bool timing) {
       if (!(e <= max_err)) max_err = e;   // NaN-propagating
       if (fabs(r) > max_ref) max_ref = fabs(r);
     }
-  printf("plain NT=%d ST=%d M=%d N=%d K=%d: max abs err %.3e / max |ref| %.3e = %.3e\n", NT, ST, M, N, K, max_err, max_ref,
+  printf("plain%s NT=%d ST=%d M=%d N=%d K=%d: max abs err %.3e / max |ref| %.3e = %.3e\n", CAT ? " N_CAT" : "", NT, ST, M, N, K, max_err, max_ref,
          max_err / max_ref);
   int bad = !(max_err / max_ref < 2e-6 + 2e-8 * K);
   if (timing) {
@@ -251,6 +255,12 @@ int main() {
   bad += run_plain<128, 3>(128 * 600, 256, 256, sm, true);
   bad += run_plain<64, 4>(128 * 600, 64, 256, sm, true);
   bad += run_plain<64, 4>(128 * 600, 64, 64, sm, true);
+  bad += run_plain<64, 4, true>(300, 40, 256, sm, false);
+  bad += run_plain<64, 4, true>(1000, 64, 72, sm, false);
+  bad += run_plain<64, 4, true>(128 * 600, 64, 256, sm, true);
+  bad += run_plain<64, 4, true>(128 * 600, 64, 64, sm, true);
+  bad += run_plain<64, 4, true>(128 * 1408, 64, 64, sm, true);
+  bad += run_plain<64, 4>(128 * 1408, 64, 64, sm, true);
   bad += run_trans<128, 3>(256, 128, 96, sm);
   bad += run_trans<256, 2>(200, 250, 1000, sm);
   bad += run_trans<64, 4>(128, 64, 4096, sm);
