@@ -353,42 +353,58 @@ constexpr int W3S_ROWS = 16, W3S_CHUNK = 64, W3S_MAXSPLIT = 64;
 struct W3SmallParams {
   const float *TL, *R, *Qb, *SX, *SQ, *x, *sj;
   float* gW3;    // [3 families][nsplit][nout][64]
-  int d, nb, nout, S, nF, nDt, nGt, nsplit, spb;
+  int d, nb, nout, S, nF, nkept, nDt, nGt, nsplit, spb;
 };
 __global__ void __launch_bounds__(256) tc_w3_small_kernel(const W3SmallParams p) {
   constexpr int K = 64;
   __shared__ __align__(16) float coef[2][W3S_ROWS][W3S_CHUNK];
   __shared__ __align__(16) float red[4][W3S_ROWS][K];
+  __shared__ int rmap[W3S_ROWS][3];   // tile row -> (first index, second index, output row)
   const int S = p.S, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int rgrp = warp & 1, sq = warp >> 1;
+  const int rgrp = warp & 1, sq = warp >> 1;   // tile rows r = 2 j + rgrp: a short group loads both row groups evenly
   int o = blockIdx.x, fam, idx, row0;
   if (o < p.nF) { fam = 0; idx = 0; row0 = o * W3S_ROWS; }
   else if (o < p.nF + p.d * p.nDt) { o -= p.nF; fam = 1; idx = o / p.nDt; row0 = (o % p.nDt) * W3S_ROWS; }
   else { o -= p.nF + p.d * p.nDt; fam = 2; idx = o / p.nGt; row0 = (o % p.nGt) * W3S_ROWS; }
-  const int cnt_all = fam == 0 ? p.nout : (fam == 1 ? (idx < p.nb - 1 ? idx : p.nb - 1) + 1 : p.d - idx);
+  // F: only the kept rows (i, n <= min(i, nb - 1)) are enumerated -- the others have a zero coefficient
+  const int cnt_all = fam == 0 ? p.nkept : (fam == 1 ? (idx < p.nb - 1 ? idx : p.nb - 1) + 1 : p.d - idx);
   const int cnt = cnt_all - row0 < W3S_ROWS ? cnt_all - row0 : W3S_ROWS;
   const int s_begin = blockIdx.y * p.spb, s_end = s_begin + p.spb < S ? s_begin + p.spb : S;
   if (cnt <= 0 || s_begin >= S) return;
   const float* X = fam == 0 ? p.TL + (size_t)p.d * S * K : (fam == 1 ? p.TL + (size_t)idx * S * K : p.R + (size_t)idx * S * K);
+  if (tid < cnt) {
+    const int q = row0 + tid;
+    int a, b, prow;
+    if (fam == 0) {
+      int i = 0, before = 0;
+      for (;; ++i) {
+        const int c = (i < p.nb - 1 ? i : p.nb - 1) + 1;
+        if (q < before + c) break;
+        before += c;
+      }
+      a = i; b = q - before; prow = i * p.nb + b;
+    } else if (fam == 1) { a = idx; b = q; prow = idx * p.nb + q; }
+    else { a = idx + q; b = idx; prow = (idx + q) * p.nb + idx; }
+    rmap[tid][0] = a; rmap[tid][1] = b; rmap[tid][2] = prow;
+  }
+  __syncthreads();
   // coefficient of (row r, sample s): thread (s = tid & 63) fills rows tid >> 6, + 4, + 8, + 12
   const int cs = tid & 63, cr = tid >> 6;
   auto fill = [&](int buf, int s0) {
     const int sg = s0 + cs;
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
-      const int r = cr + 4 * j, q = row0 + r;
+      const int r = cr + 4 * j;
       float v = 0.f;
       if (r < cnt) {
-        if (fam == 0) {
-          const int i = q / p.nb, n = q - i * p.nb;
-          if (n <= i)
-            v = 2.f * (__ldg(p.Qb + (size_t)i * S + sg) * __ldg(p.SX + (size_t)n * S + sg) -
-                       __ldg(p.x + (size_t)i * S + sg) * __ldg(p.SQ + (size_t)n * S + sg));
-        } else if (fam == 1) {
-          v = -__ldg(p.sj + (size_t)idx * S + sg) * __ldg(p.SQ + (size_t)q * S + sg);
-        } else {
-          v = __ldg(p.Qb + (size_t)(idx + q) * S + sg);
-        }
+        const int a = rmap[r][0], b = rmap[r][1];
+        if (fam == 0)
+          v = 2.f * (__ldg(p.Qb + (size_t)a * S + sg) * __ldg(p.SX + (size_t)b * S + sg) -
+                     __ldg(p.x + (size_t)a * S + sg) * __ldg(p.SQ + (size_t)b * S + sg));
+        else if (fam == 1)
+          v = -__ldg(p.sj + (size_t)a * S + sg) * __ldg(p.SQ + (size_t)b * S + sg);
+        else
+          v = __ldg(p.Qb + (size_t)a * S + sg);
       }
       coef[buf][r][cs] = v;
     }
@@ -408,28 +424,27 @@ __global__ void __launch_bounds__(256) tc_w3_small_kernel(const W3SmallParams p)
 #pragma unroll
       for (int e = 0; e < 4; ++e) xv[e] = __ldg(reinterpret_cast<const float2*>(xr + (size_t)(4 * g4 + e) * K));
 #pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        const float4 c = *reinterpret_cast<const float4*>(&coef[buf][rgrp * 8 + j][sq * 16 + 4 * g4]);
-        acc[j].x = fmaf(c.x, xv[0].x, acc[j].x); acc[j].y = fmaf(c.x, xv[0].y, acc[j].y);
-        acc[j].x = fmaf(c.y, xv[1].x, acc[j].x); acc[j].y = fmaf(c.y, xv[1].y, acc[j].y);
-        acc[j].x = fmaf(c.z, xv[2].x, acc[j].x); acc[j].y = fmaf(c.z, xv[2].y, acc[j].y);
-        acc[j].x = fmaf(c.w, xv[3].x, acc[j].x); acc[j].y = fmaf(c.w, xv[3].y, acc[j].y);
-      }
+      for (int j = 0; j < 8; ++j)
+        if (2 * j + rgrp < cnt) {   // warp-uniform
+          const float4 c = *reinterpret_cast<const float4*>(&coef[buf][2 * j + rgrp][sq * 16 + 4 * g4]);
+          acc[j].x = fmaf(c.x, xv[0].x, acc[j].x); acc[j].y = fmaf(c.x, xv[0].y, acc[j].y);
+          acc[j].x = fmaf(c.y, xv[1].x, acc[j].x); acc[j].y = fmaf(c.y, xv[1].y, acc[j].y);
+          acc[j].x = fmaf(c.z, xv[2].x, acc[j].x); acc[j].y = fmaf(c.z, xv[2].y, acc[j].y);
+          acc[j].x = fmaf(c.w, xv[3].x, acc[j].x); acc[j].y = fmaf(c.w, xv[3].y, acc[j].y);
+        }
     }
     __syncthreads();
   }
 #pragma unroll
-  for (int j = 0; j < 8; ++j) *reinterpret_cast<float2*>(&red[sq][rgrp * 8 + j][2 * lane]) = acc[j];
+  for (int j = 0; j < 8; ++j) *reinterpret_cast<float2*>(&red[sq][2 * j + rgrp][2 * lane]) = acc[j];
   __syncthreads();
   float* plane = p.gW3 + (size_t)(fam * p.nsplit + blockIdx.y) * p.nout * K;
 #pragma unroll
   for (int j = 0; j < 4; ++j) {
     const int e = tid + 256 * j, r = e >> 6, k = e & 63;
     if (r < cnt) {
-      const int q = row0 + r;
-      const int prow = fam == 0 ? q : (fam == 1 ? idx * p.nb + q : (idx + q) * p.nb + idx);
       const float v = ((red[0][r][k] + red[1][r][k]) + red[2][r][k]) + red[3][r][k];
-      plane[(size_t)prow * K + k] += v;
+      plane[(size_t)rmap[r][2] * K + k] += v;
     }
   }
 }
@@ -823,7 +838,9 @@ int tc_run(const GpFlowDesc* d, int op, const float* params, const float* x_in, 
       p.TL = P(b.T[L]); p.R = P(b.R); p.Qb = P(b.Qb); p.SX = P(b.SX); p.SQ = P(b.SQ); p.x = xpt; p.sj = P(b.sj);
       p.gW3 = P(b.gW3);
       p.d = dd; p.nb = nb; p.nout = g.nout; p.S = S;
-      p.nF = (g.nout + W3S_ROWS - 1) / W3S_ROWS; p.nDt = (nb + W3S_ROWS - 1) / W3S_ROWS; p.nGt = (dd + W3S_ROWS - 1) / W3S_ROWS;
+      p.nkept = 0;
+      for (int i = 0; i < dd; ++i) p.nkept += (i < nb - 1 ? i : nb - 1) + 1;
+      p.nF = (p.nkept + W3S_ROWS - 1) / W3S_ROWS; p.nDt = (nb + W3S_ROWS - 1) / W3S_ROWS; p.nGt = (dd + W3S_ROWS - 1) / W3S_ROWS;
       p.nsplit = b.w3_nsplit;
       p.spb = ((S + p.nsplit - 1) / p.nsplit + W3S_CHUNK - 1) / W3S_CHUNK * W3S_CHUNK;
       tc_w3_small_kernel<<<dim3(p.nF + dd * p.nDt + nb * p.nGt, p.nsplit), 256, 0, st>>>(p);
