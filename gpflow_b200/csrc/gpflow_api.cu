@@ -93,6 +93,70 @@ bool sf2e_match(const GpFlowDesc* d, int op) {
   return op != GPFLOW_OP_FORWARD && d->n_steps <= 512;   // 8 x 28 KB of warp buffers + the time table must fit 227 KB
 }
 
+// Narrower 2-D nets (d = 2, nb = 1, two hidden layers of width <= 15, fp32) run on the same [15,15] kernels with the
+// parameters ZERO-PADDED to that shape: a padded unit has a = 0, h = tanh 0 = 0, and every weight that leaves it is 0, so
+// it contributes nothing to psi, grad psi or any kept gradient entry.  Two tiny kernels around the call re-lay the flat
+// parameter vector ([H1][3] | [H1] | [H2][H1] | [H2] | [2][H2] | [2], vector_field.py:44-73) and gather the gradient back.
+// Without this, e.g. H = [10,10] fell to the generic kernel (30 x slower).  Shapes the sf2 / sf2e kernels do not take at
+// [15,15] (fp64, Lagrangian in the train step, FORCE_V1) stay on the generic kernel.
+bool pad2d_match(const GpFlowDesc* d, int op, GpFlowDesc* d15) {
+  if (d->flags & (GPFLOW_FLAG_FORCE_GENERIC | GPFLOW_FLAG_FORCE_TC)) return false;
+  if (d->dtype != GPFLOW_F32 || d->d != 2 || d->nb != 1 || d->n_hidden != 2) return false;
+  if (d->hidden[0] > 15 || d->hidden[1] > 15 || (d->hidden[0] == 15 && d->hidden[1] == 15)) return false;
+  GpFlowDesc t = *d;
+  t.hidden[0] = t.hidden[1] = 15;
+  if (!sf2_match(&t, op) && !sf2e_match(&t, op)) return false;
+  if (d15) *d15 = t;
+  return true;
+}
+constexpr int kPad2dParams = 332;                 // parameter count of the [15,15] shape
+constexpr size_t kPad2dHead = 2 * 1536;           // padded parameters | padded gradient, 256-byte aligned
+// index of entry e of the (h1, h2) layout in the [15,15] layout
+__host__ __device__ inline int pad2d_index(int e, int h1, int h2) {
+  const int o_b1 = 3 * h1, o_w2 = 4 * h1, o_b2 = o_w2 + h2 * h1, o_w3 = o_b2 + h2, o_b3 = o_w3 + 2 * h2;
+  if (e < o_b1) return e;
+  if (e < o_w2) return 45 + (e - o_b1);
+  if (e < o_b2) return 60 + ((e - o_w2) / h1) * 15 + (e - o_w2) % h1;
+  if (e < o_w3) return 285 + (e - o_b2);
+  if (e < o_b3) return 300 + ((e - o_w3) / h2) * 15 + (e - o_w3) % h2;
+  return 330 + (e - o_b3);
+}
+__global__ void pad2d_scatter_kernel(const float* __restrict__ src, float* __restrict__ dst15, int h1, int h2, int n) {
+  __shared__ float buf[kPad2dParams];
+  for (int i = threadIdx.x; i < kPad2dParams; i += blockDim.x) buf[i] = 0.0f;
+  __syncthreads();
+  for (int e = threadIdx.x; e < n; e += blockDim.x) buf[pad2d_index(e, h1, h2)] = src[e];
+  __syncthreads();
+  for (int i = threadIdx.x; i < kPad2dParams; i += blockDim.x) dst15[i] = buf[i];
+}
+__global__ void pad2d_gather_kernel(const float* __restrict__ src15, float* __restrict__ dst, int h1, int h2, int n) {
+  for (int e = threadIdx.x; e < n; e += blockDim.x) dst[e] = src15[pad2d_index(e, h1, h2)];
+}
+size_t pad2d_workspace(const GpFlowDesc* d15, int64_t B, int op) {
+  return kPad2dHead + (sf2_match(d15, op) ? sf2_15_15_workspace(d15, B, op) : sf2e_15_15_workspace(d15, B));
+}
+int pad2d_run(const GpFlowDesc* d, const GpFlowDesc* d15, int op, const Ptrs<float>& p, int64_t B, void* ws, size_t wsb,
+              cudaStream_t st, int sm) {
+  if (ws == nullptr || wsb < pad2d_workspace(d15, B, op)) return GPFLOW_ERR_WORKSPACE;
+  const int n = (int)gpflow_param_count(d);
+  float* p15 = reinterpret_cast<float*>(ws);
+  float* g15 = reinterpret_cast<float*>(reinterpret_cast<char*>(ws) + kPad2dHead / 2);
+  pad2d_scatter_kernel<<<1, 256, 0, st>>>(p.params, p15, d->hidden[0], d->hidden[1], n);
+  if (cudaGetLastError() != cudaSuccess) return GPFLOW_ERR_CUDA;
+  Ptrs<float> q = p;
+  q.params = p15;
+  if (p.grads_out != nullptr) q.grads_out = g15;
+  void* inner = reinterpret_cast<char*>(ws) + kPad2dHead;
+  const int rc = sf2_match(d15, op) ? sf2_15_15_f32(d15, op, &q, B, inner, wsb - kPad2dHead, st, sm)
+                                    : sf2e_15_15_f32(d15, op, &q, B, inner, wsb - kPad2dHead, st, sm);
+  if (rc != GPFLOW_OK) return rc;
+  if (p.grads_out != nullptr) {
+    pad2d_gather_kernel<<<1, 256, 0, st>>>(g15, p.grads_out, d->hidden[0], d->hidden[1], n);
+    if (cudaGetLastError() != cudaSuccess) return GPFLOW_ERR_CUDA;
+  }
+  return GPFLOW_OK;
+}
+
 // tc (chunked tensor-core path) takes the wide fp32 shapes without Euler penalization once the batch is large enough to
 // fill 128-row MMA tiles on every SM; GPFLOW_TC_MIN_BATCH overrides the threshold, GPFLOW_FLAG_FORCE_TC ignores it.
 // Measured crossovers (B200, train step, profiles/r2_tc_crossover.txt): d=10, H=[50,50,50] -- generic 29.6 ms vs tc 33.5 ms at
@@ -121,6 +185,8 @@ int dispatch<float>(const GpFlowDesc* d, int op, const Ptrs<float>& p, int64_t B
   if (sf2_match(d, op)) return sf2_15_15_f32(d, op, &p, B, ws, wsb, st, sm);
   if (sf2e_match(d, op)) return sf2e_15_15_f32(d, op, &p, B, ws, wsb, st, sm);
   if (small_match(d, &s)) return euler ? small_2_1_15_15_f32_euler(d, op, &p, B, ws, wsb, st, sm) : small_2_1_15_15_f32(d, op, &p, B, ws, wsb, st, sm);
+  GpFlowDesc d15;
+  if (pad2d_match(d, op, &d15)) return pad2d_run(d, &d15, op, p, B, ws, wsb, st, sm);
   if (tc_selected(d, B))
     return tc_f32(d, op, p.params, p.x_in, p.x_data, p.grad_y, p.y_out, p.logdet_out, p.traj_out, p.grad_x_out, p.grads_out,
                   p.scalars_out, B, ws, wsb, st, sm, nullptr, 0.0);
@@ -263,6 +329,11 @@ int gpflow_query_workspace(const GpFlowDesc* d, int64_t B, int op, size_t* bytes
     *bytes = small_workspace(d, B, op, (int)np);
     return GPFLOW_OK;
   }
+  GpFlowDesc d15;
+  if (pad2d_match(d, op, &d15)) {
+    *bytes = pad2d_workspace(&d15, B, op);
+    return GPFLOW_OK;
+  }
   if (d->dtype == GPFLOW_F32 && tc_selected(d, B)) {
     *bytes = tc_workspace(d, B, op);
     return GPFLOW_OK;
@@ -325,12 +396,16 @@ int gpflow_kernel_variant(const GpFlowDesc* d, int op, char* buf, size_t n) {
   const char* mode = op == GPFLOW_OP_FORWARD ? "fwd" : (op == GPFLOW_OP_TRAIN_STEP ? "train" : "bwd");
   const char* eu = (d->flags & GPFLOW_FLAG_EULER_PEN) ? ",euler" : "";
   SmallShape s;
+  GpFlowDesc d15;
   if (sf2_match(d, op))
     snprintf(buf, n, "%s<f32,d=2,nb=1,H=[15,15],%s>", sf2_15_15_kernel_name(op), mode);
   else if (sf2e_match(d, op))
     snprintf(buf, n, "gpflow_sf2e_kernel<f32,d=2,nb=1,H=[15,15],%s,euler>", mode);
   else if (small_match(d, &s))
     snprintf(buf, n, "gpflow_small_kernel<%s,d=%d,nb=%d,H=[%d,%d],%s%s>", ty, s.d, s.nb, s.h1, s.h2, mode, eu);
+  else if (pad2d_match(d, op, &d15))
+    snprintf(buf, n, "%s<f32,d=2,nb=1,H=[15,15],%s%s> (H=[%d,%d] zero-padded)",
+             sf2_match(&d15, op) ? sf2_15_15_kernel_name(op) : "gpflow_sf2e_kernel", mode, eu, d->hidden[0], d->hidden[1]);
   else if (d->dtype == GPFLOW_F32 && tc_selected(d, (d->flags & GPFLOW_FLAG_FORCE_TC) ? 0 : tc_min_batch(d)))
     snprintf(buf, n, "gpflow_tc<f32,tcgen05,%s> (batches >= %lld; generic below)", mode, (long long)tc_min_batch(d));
   else
@@ -345,6 +420,9 @@ int gpflow_launch_count(const GpFlowDesc* d, int op) {
   if (sf2_match(d, op)) return sf2_15_15_launches(op);   // [weight pack +] main kernel + deterministic finalize
   if (sf2e_match(d, op)) return 3;
   if (small_match(d, &s)) return 2;            // main kernel + deterministic finalize
+  GpFlowDesc d15;
+  if (pad2d_match(d, op, &d15))                // + parameter scatter [+ gradient gather]
+    return (sf2_match(&d15, op) ? sf2_15_15_launches(op) : 3) + (op == GPFLOW_OP_FORWARD ? 1 : 2);
   return generic_runs_padded(d) ? 4 : 3;       // [zero-padding scatter +] weight transpose + main kernel + finalize
 }
 

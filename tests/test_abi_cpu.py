@@ -63,6 +63,12 @@ def test_workspace_query_and_variant_names(lib):
     assert "gpflow_sf2r_fwd_kernel<f32,d=2,nb=1,H=[15,15],fwd>" == kernel_variant(c4, op=_lib.OP_FORWARD, lagrangian=True)
     assert "gpflow_small_kernel<f32,d=2,nb=1,H=[15,15],fwd>" == kernel_variant(c4, op=_lib.OP_FORWARD, force_v1=True)
     assert "gpflow_small_kernel<f64" in kernel_variant(c4, torch.float64, op=_lib.OP_FORWARD)
+    # narrower 2-D nets: the [15,15] kernels on zero-padded parameters (gpflow_api.cu: pad2d_match)
+    narrow = FlowConfig(2, 1, (10, 12), 15)
+    assert "gpflow_sf2r_kernel<f32,d=2,nb=1,H=[15,15],train> (H=[10,12] zero-padded)" == kernel_variant(narrow)
+    assert "gpflow_sf2e_kernel" in kernel_variant(narrow, euler_coef=0.3) and "zero-padded" in kernel_variant(narrow, euler_coef=0.3)
+    assert "gpflow_generic_kernel" in kernel_variant(narrow, torch.float64)
+    assert "zero-padded" not in kernel_variant(FlowConfig(2, 1, (16, 10), 15))      # wider than 15: tc / generic
     assert "generic" in kernel_variant(c4, force_generic=True)
     assert "generic" in kernel_variant(FlowConfig(10, 9, (50, 50, 50), 15))
     assert "euler" in kernel_variant(c4, euler_coef=0.01)
