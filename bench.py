@@ -434,7 +434,24 @@ def measure_workload(args, name, wl, euler, rank, world, local_rank, dev, steps,
         net.fused_training_step(x_data, x_map, global_batch=B_global)
         opt.step()
     torch.cuda.synchronize()
+    per_rank = None
     if world > 1:
+        # diagnostic, outside the timed region: every rank's kernel time WITHOUT the all-reduce, all GPUs of the box busy at
+        # the same time -- the synchronous step runs at the pace of the slowest of these
+        dist.barrier()
+        flat0 = flow.flat_parameters().detach().clone()
+        s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ops.fused_train_step(cfg, flat0, *bufs[0], loss_scale=1.0 / B_global)
+        s0.record()
+        for i in range(3):
+            ops.fused_train_step(cfg, flat0, *bufs[i % n_buf], loss_scale=1.0 / B_global)
+        s1.record()
+        torch.cuda.synchronize()
+        mine = torch.tensor([s0.elapsed_time(s1) / 3.0], device=dev, dtype=torch.float64)
+        allr = [torch.zeros_like(mine) for _ in range(world)]
+        dist.all_gather(allr, mine)
+        per_rank = {"solo_kernel_ms": [round(float(v), 3) for v in allr],
+                    "what": "3 train-step launches per rank without the all-reduce, all ranks at once, before the timed region"}
         dist.barrier()
     clocks = ClockSampler(local_rank)
     if rank == 0 and "noclk" not in args.dbg:
@@ -592,6 +609,7 @@ def measure_workload(args, name, wl, euler, rank, world, local_rank, dev, steps,
         "clocks": clk, "e2e": e2e, "gpu_launches": launches,
         "roofline": roofline, "cpu_baseline": cpu_baseline,
         "loss": float(loss), "reg": float(reg),
+        **({"per_rank": per_rank} if per_rank is not None else {}),
     }
 
 
