@@ -29,6 +29,10 @@ constexpr int TC_DMAX = 64;      // d <= 64: every last-layer group fits one 64-
 constexpr int TC_MAXL = GPFLOW_MAX_HIDDEN;
 constexpr int TC_SEG = 8;        // K chunks per TMEM accumulation (see header)
 constexpr int TC_L1_SPB = 8;     // samples per block of the first-layer kernels
+#ifndef GPF_TC_L1_SPB_WIDE
+#define GPF_TC_L1_SPB_WIDE 8
+#endif
+constexpr int TC_L1_SPB_WIDE = GPF_TC_L1_SPB_WIDE;   // tc_layer1_kernel for d > 16
 
 struct TcDims {
   int d, nb, L, nout, P;
@@ -423,23 +427,23 @@ __global__ void __launch_bounds__(256) tc_layer1_bwd_b_kernel(TcDims g, const fl
     }
   }
 }
-// The same for a 64-wide first layer and d <= DB (C3).  The kernel above keeps 4 096 warps on a serial chain of 4 load
-// batches (ncu at C3: 67 us per launch, long_scoreboard 84 % of the stall samples, 22 % occupancy).  Here a block owns
-// TC_L1B_CH = 32 samples and one plane: thread = (4 units, 1 of 16 sample rows), every load is a float4 and all the loads of a
-// thread (2 samples x (d + 2)) are independent; the 16 sample rows are summed by one shuffle and a fixed-order pass over
-// the 8 warps.  Grid S / 32.
+// The same with float4 loads, for first layers whose padded width is a multiple of 64.  The kernel above keeps few warps on a
+// serial chain of load batches (ncu at C3: 67 us per launch, long_scoreboard 84 % of the stall samples, 22 % occupancy).
+// Here a block owns TC_L1B_CH = 32 samples, 64 units (blockIdx.z) and DB = 16 directions (blockIdx.y) of one plane:
+// thread = (4 units, 1 of 16 sample rows), all the loads of a thread (2 samples x (DB + 2)) are independent; the 16 sample
+// rows are summed by one shuffle and a fixed-order pass over the 8 warps.  Grid (S / 32, ceil(d / 16), Hp1 / 64).
 constexpr int TC_L1B_CH = 32;
 template <int DB>
 __global__ void __launch_bounds__(256) tc_layer1_bwd_b_small_kernel(TcDims g, const float* __restrict__ sp1, const float* __restrict__ Ub,
                                                                      const float* __restrict__ x, float t, float* __restrict__ part) {
-  constexpr int H = 64;
   __shared__ float xs[DB][TC_L1B_CH];
   __shared__ float4 red[8][DB + 2][16];
-  const int d = g.d, S = g.S, tid = threadIdx.x, k4 = tid & 15, sr = tid >> 4, lane = tid & 31, warp = tid >> 5;
-  const int s0 = blockIdx.x * TC_L1B_CH;
-  for (int e = tid; e < d * TC_L1B_CH; e += 256) {
+  const int H = g.Hp[1], d = g.d, S = g.S, tid = threadIdx.x, k4 = tid & 15, sr = tid >> 4, lane = tid & 31, warp = tid >> 5;
+  const int s0 = blockIdx.x * TC_L1B_CH, j0 = blockIdx.y * DB, kb = blockIdx.z * 64;
+  const int dj = d - j0 < DB ? d - j0 : DB;   // directions of this block
+  for (int e = tid; e < dj * TC_L1B_CH; e += 256) {
     const int j = e / TC_L1B_CH, q = e % TC_L1B_CH;
-    xs[j][q] = x[(size_t)j * S + s0 + q];
+    xs[j][q] = x[(size_t)(j0 + j) * S + s0 + q];
   }
   __syncthreads();
   float4 acc[DB], gb = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -448,13 +452,13 @@ __global__ void __launch_bounds__(256) tc_layer1_bwd_b_small_kernel(TcDims g, co
 #pragma unroll
   for (int i = 0; i < TC_L1B_CH / 16; ++i) {
     const int q = sr + 16 * i, s = s0 + q;
-    const float4 sp = __ldg(reinterpret_cast<const float4*>(sp1 + (size_t)s * H) + k4);
-    const float4 ab = __ldg(reinterpret_cast<const float4*>(Ub + ((size_t)d * S + s) * H) + k4);
+    const float4 sp = __ldg(reinterpret_cast<const float4*>(sp1 + (size_t)s * H + kb) + k4);
+    const float4 ab = __ldg(reinterpret_cast<const float4*>(Ub + ((size_t)d * S + s) * H + kb) + k4);
     gb.x += ab.x; gb.y += ab.y; gb.z += ab.z; gb.w += ab.w;
 #pragma unroll
     for (int j = 0; j < DB; ++j)
-      if (j < d) {
-        const float4 u = __ldg(reinterpret_cast<const float4*>(Ub + ((size_t)j * S + s) * H) + k4);
+      if (j < dj) {
+        const float4 u = __ldg(reinterpret_cast<const float4*>(Ub + ((size_t)(j0 + j) * S + s) * H + kb) + k4);
         const float xj = xs[j][q];
         acc[j].x += fmaf(ab.x, xj, sp.x * u.x); acc[j].y += fmaf(ab.y, xj, sp.y * u.y);
         acc[j].z += fmaf(ab.z, xj, sp.z * u.z); acc[j].w += fmaf(ab.w, xj, sp.w * u.w);
@@ -467,17 +471,19 @@ __global__ void __launch_bounds__(256) tc_layer1_bwd_b_small_kernel(TcDims g, co
   };
 #pragma unroll
   for (int j = 0; j < DB; ++j)
-    if (j < d) fold(acc[j], j);
-  fold(make_float4(gb.x * t, gb.y * t, gb.z * t, gb.w * t), d);
-  fold(gb, d + 1);
+    if (j < dj) fold(acc[j], j);
+  fold(make_float4(gb.x * t, gb.y * t, gb.z * t, gb.w * t), DB);
+  fold(gb, DB + 1);
   __syncthreads();
   const float* rf = reinterpret_cast<const float*>(&red[0][0][0]);
-  for (int e = tid; e < (d + 2) * H; e += 256) {
-    const int o = e / H, k = e % H;
+  const int nout = dj + (blockIdx.y == 0 ? 2 : 0);   // the time-column and bias sums are written by the first direction tile
+  for (int e = tid; e < nout * 64; e += 256) {
+    const int oo = e / 64, k = e % 64;
+    const int slot = oo < dj ? oo : DB + (oo - dj), col = oo < dj ? j0 + oo : d + (oo - dj);
     float v = 0.f;
 #pragma unroll
-    for (int w = 0; w < 8; ++w) v += rf[(w * (DB + 2) + o) * H + k];
-    part[((size_t)blockIdx.x * H + k) * (d + 2) + o] += v;
+    for (int w = 0; w < 8; ++w) v += rf[(w * (DB + 2) + slot) * 64 + k];
+    part[((size_t)blockIdx.x * H + kb + k) * (d + 2) + col] += v;
   }
 }
 // acc[e] += sum_z part[z][e]  (fixed order)

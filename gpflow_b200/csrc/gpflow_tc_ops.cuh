@@ -345,6 +345,10 @@ struct OpW3 {
 // (one 8-byte load per sample row) and 8 output rows in registers; the 4 sample quarters of the CTA are summed in a fixed
 // order and added to the split's partial plane -- rows of one family are owned by one CTA per split, so no atomics.
 // ---------------------------------------------------------------------------------------------------------------
+inline bool tc_l1b_small_enabled() {   // GPFLOW_TC_L1B_SMALL=0: the round-1 first-layer gradient kernel (A/B switch)
+  static const bool on = [] { const char* e = getenv("GPFLOW_TC_L1B_SMALL"); return !(e && e[0] == '0'); }();
+  return on;
+}
 inline bool tc_w3_small_enabled() {   // GPFLOW_TC_W3_SMALL=0: the tensor-core GEMM for every width (A/B switch)
   static const bool on = [] { const char* e = getenv("GPFLOW_TC_W3_SMALL"); return !(e && e[0] == '0'); }();
   return on;
@@ -627,7 +631,9 @@ inline void tc_carve(const TcDims& g, int n_steps, bool train, int sm_count, TcB
   b.s_per_z = (S + b.nz - 1) / b.nz;
   if (train) {
     b.gW1 = take((size_t)g.Hp[1] * (d + 2));
-    b.l1b_small = g.Hp[1] == 64 && d <= 16;            // tc_layer1_bwd_b_small_kernel: one plane per 32 samples
+    // tc_layer1_bwd_b_small_kernel (one plane per 32 samples): narrow first layers only -- measured at C5 (d = 64, 256 wide,
+    // 4 x 4 direction / unit tiles per sample block): 1056 ms per step against 993 ms with the kernel above
+    b.l1b_small = g.Hp[1] == 64 && d <= 16 && tc_l1b_small_enabled();
     b.nz1 = b.l1b_small ? S / TC_L1B_CH : b.nz;
     b.zW1 = take((size_t)b.nz1 * g.Hp[1] * (d + 2));
     b.zb3 = take((size_t)(S / 64) * g.nout);
@@ -776,7 +782,7 @@ int tc_run(const GpFlowDesc* d, int op, const float* params, const float* x_in, 
     if (dd <= 16)
       tc_layer1_kernel<16, 4><<<S / 4, g.Hp[1], 0, st>>>(g, w.W1T, w.bp[1], xpt, t, bnd, P(b.T[1]), P(b.sp[1]), P(b.sj), (L == 1 || !gen_t1) ? 1 : 0);
     else
-      tc_layer1_kernel<TC_DMAX, TC_L1_SPB><<<S / TC_L1_SPB, g.Hp[1], 0, st>>>(g, w.W1T, w.bp[1], xpt, t, bnd, P(b.T[1]), P(b.sp[1]), P(b.sj), (L == 1 || !gen_t1) ? 1 : 0);
+      tc_layer1_kernel<TC_DMAX, TC_L1_SPB_WIDE><<<S / TC_L1_SPB_WIDE, g.Hp[1], 0, st>>>(g, w.W1T, w.bp[1], xpt, t, bnd, P(b.T[1]), P(b.sp[1]), P(b.sj), (L == 1 || !gen_t1) ? 1 : 0);
     TC_KCK();
     for (int l = 2; l <= L; ++l) {
       typename LayerOp::Params p;
@@ -909,7 +915,7 @@ int tc_run(const GpFlowDesc* d, int op, const float* params, const float* x_in, 
     tc_layer1_bwd_a_kernel<<<S / TC_L1B_SPB, g.Hp[1], 0, st>>>(g, w.W1T, P(b.T[1]), P(b.sp[1]), P(b.Ub[1]), P(b.ybar));
     TC_KCK();
     if (b.l1b_small)
-      tc_layer1_bwd_b_small_kernel<16><<<S / TC_L1B_CH, 256, 0, st>>>(g, P(b.sp[1]), P(b.Ub[1]), xpt, t, P(b.zW1));
+      tc_layer1_bwd_b_small_kernel<16><<<dim3(S / TC_L1B_CH, (dd + 15) / 16, g.Hp[1] / 64), 256, 0, st>>>(g, P(b.sp[1]), P(b.Ub[1]), xpt, t, P(b.zW1));
     else
       tc_layer1_bwd_b_kernel<<<dim3(g.Hp[1] / 32, (dd + 7) / 8, b.nz), dim3(32, 8), 0, st>>>(g, P(b.sp[1]), P(b.Ub[1]), xpt, t,
                                                                                          b.s_per_z, P(b.zW1));
