@@ -30,15 +30,33 @@ namespace gpflow {
 #endif
 constexpr int kSF2EUnroll = GPF_SF2E_UNROLL;
 typedef float2 du;  // dual number: .x = value, .y = epsilon part
+// GPF_SF2E_PACKED = 1: the element-wise dual operations as packed fp32x2 instructions as well (the scalar forms are 17 % FMUL +
+// FADD of the executed instructions, profiles/r2_sf2e_ncu_summary.txt).  Measured on the C4 Euler row, same box, alternating
+// builds (tools/sf2e_packed_ab.sh, profiles/r2_sf2e_packed_ab.txt): 152.8 / 155.9 ms packed against 139.4 / 140.7 ms scalar --
+// a packed instruction holds the FMA pipe for two cycles and needs aligned register pairs (extra moves at 255 registers),
+// so fewer instructions do not pay here.  Default 0.
+#ifndef GPF_SF2E_PACKED
+#define GPF_SF2E_PACKED 0
+#endif
 GPF_DEV du d_make(float v, float e) { return make_float2(v, e); }
+GPF_DEV du d_fma(float s, du a, du c) { return __ffma2_rn(make_float2(s, s), a, c); }   // s a + c, s a plain scalar
+#if GPF_SF2E_PACKED
+GPF_DEV du d_add(du a, du b) { return __fadd2_rn(a, b); }
+GPF_DEV du d_sub(du a, du b) { return __ffma2_rn(make_float2(-1.0f, -1.0f), b, a); }
+GPF_DEV du d_neg(du a) { return make_float2(-a.x, -a.y); }
+GPF_DEV du d_mul(du a, du b) { return __ffma2_rn(make_float2(a.x, a.x), b, make_float2(0.0f, a.y * b.x)); }
+GPF_DEV du d_scale(float s, du a) { return __fmul2_rn(make_float2(s, s), a); }
+GPF_DEV du d_sp(du h) { return __ffma2_rn(make_float2(-h.x, -h.x), make_float2(h.x, 2.0f * h.y), make_float2(1.0f, 0.0f)); }  // 1 - h^2
+GPF_DEV du d_sq_minus(du x, float b) { return __ffma2_rn(make_float2(x.x, x.x), make_float2(x.x, 2.0f * x.y), make_float2(-b, 0.0f)); }  // x^2 - b
+#else
 GPF_DEV du d_add(du a, du b) { return make_float2(a.x + b.x, a.y + b.y); }
 GPF_DEV du d_sub(du a, du b) { return make_float2(a.x - b.x, a.y - b.y); }
 GPF_DEV du d_neg(du a) { return make_float2(-a.x, -a.y); }
 GPF_DEV du d_mul(du a, du b) { return make_float2(a.x * b.x, fmaf(a.x, b.y, a.y * b.x)); }
 GPF_DEV du d_scale(float s, du a) { return make_float2(s * a.x, s * a.y); }
-GPF_DEV du d_fma(float s, du a, du c) { return __ffma2_rn(make_float2(s, s), a, c); }   // s a + c, s a plain scalar
 GPF_DEV du d_sp(du h) { return make_float2(fmaf(-h.x, h.x, 1.0f), -2.0f * h.x * h.y); }  // 1 - h^2
 GPF_DEV du d_sq_minus(du x, float b) { return make_float2(fmaf(x.x, x.x, -b), 2.0f * x.x * x.y); }  // x^2 - b
+#endif
 
 template <int H1_, int H2_, int NW_>
 struct SF2E {
