@@ -194,6 +194,120 @@ __global__ void tc_layer1_kernel(TcDims g, const float* __restrict__ W1T, const 
   }
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// 64-wide nets (every Hp_l = 64, d <= DB; C3): the VALUE rows of all layers in one launch, on the CUDA cores in plain fp32.
+//   h_1 = tanh(W1x x + w1t t + b1),  h_l = tanh(W_l h_{l-1} + b_l),  sp_l = 1 - h_l^2,  s_j,  [T_1[j] = sp_1 (.) W1x[:, j]]
+// As GEMMs these are S x 64 x 64: 128 tiles, one per CTA, 13 us of launch / pipeline-fill latency each and two of them per
+// evaluation on the critical path (the tangent GEMM of layer l needs sp_l).  Here a block takes 64 samples through the chain:
+// weights transposed in shared memory ([k][unit], 16 KB per layer), activations ping-pong as [unit][sample]; thread =
+// (4 units, 4 samples), per k one 16-byte load of each and 16 FMAs.
+// ---------------------------------------------------------------------------------------------------------------
+struct TcChainPtrs {
+  float* T[TC_MAXL + 1];          // T_l: h_l goes to row block d
+  float* sp[TC_MAXL + 1];
+  const float* bp[TC_MAXL + 1];   // zero-padded biases
+};
+constexpr int TC_CH_S = 64, TC_CH_HS = 68;   // samples per block, row stride of the activation buffers
+inline size_t tc_chain_smem(int L) { return ((size_t)(L - 1) * 64 * 64 + 2 * 64 * TC_CH_HS) * sizeof(float); }
+template <int DB>
+__global__ void __launch_bounds__(256) tc_value_chain_kernel(TcDims g, const float* __restrict__ params, const float* __restrict__ W1T,
+                                                              TcChainPtrs q, const float* __restrict__ x /*CL [d][S]*/, float t, float bnd,
+                                                              float* __restrict__ sj, int write_tangents) {
+  extern __shared__ __align__(16) float chain_smem[];
+  __shared__ float xs[DB][TC_CH_S];
+  constexpr int H = 64;
+  const int d = g.d, S = g.S, L = g.L, tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+  const int s0 = blockIdx.x * TC_CH_S;
+  float* Wt = chain_smem;                               // [L - 1][k][unit]
+  float* hT = chain_smem + (size_t)(L - 1) * H * H;     // [2][unit][TC_CH_HS]
+  for (int e = tid; e < d * TC_CH_S; e += 256) {
+    const int j = e / TC_CH_S, c = e % TC_CH_S;
+    const float xv = x[(size_t)j * S + s0 + c];
+    xs[j][c] = xv;
+    sj[(size_t)j * S + s0 + c] = xv * xv - bnd;
+  }
+  for (int l = 2; l <= L; ++l)
+    for (int e = tid; e < H * H; e += 256) {              // e = unit * 64 + k: coalesced reads of W_l[unit][:]
+      const int u = e >> 6, k = e & 63;
+      Wt[(size_t)(l - 2) * H * H + k * H + u] = tc_w(g, params, l - 1, u, k);
+    }
+  __syncthreads();
+  float a[4][4];   // [sample][unit]
+  {
+    float4 w1[DB];
+#pragma unroll
+    for (int j = 0; j < DB; ++j) w1[j] = j < d ? __ldg(reinterpret_cast<const float4*>(W1T + j * H) + tx) : make_float4(0.f, 0.f, 0.f, 0.f);
+    const float4 wt = __ldg(reinterpret_cast<const float4*>(W1T + d * H) + tx), b1 = __ldg(reinterpret_cast<const float4*>(q.bp[1]) + tx);
+    const float a0[4] = {fmaf(wt.x, t, b1.x), fmaf(wt.y, t, b1.y), fmaf(wt.z, t, b1.z), fmaf(wt.w, t, b1.w)};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      a[i][0] = a0[0]; a[i][1] = a0[1]; a[i][2] = a0[2]; a[i][3] = a0[3];
+    }
+#pragma unroll
+    for (int j = 0; j < DB; ++j)
+      if (j < d) {
+        const float4 xv = *reinterpret_cast<const float4*>(&xs[j][4 * ty]);
+        const float xi[4] = {xv.x, xv.y, xv.z, xv.w};
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          a[i][0] = fmaf(w1[j].x, xi[i], a[i][0]); a[i][1] = fmaf(w1[j].y, xi[i], a[i][1]);
+          a[i][2] = fmaf(w1[j].z, xi[i], a[i][2]); a[i][3] = fmaf(w1[j].w, xi[i], a[i][3]);
+        }
+      }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int s = s0 + 4 * ty + i;
+      float4 h, sp;
+      h.x = act_tanh(a[i][0]); h.y = act_tanh(a[i][1]); h.z = act_tanh(a[i][2]); h.w = act_tanh(a[i][3]);
+      sp.x = 1.f - h.x * h.x; sp.y = 1.f - h.y * h.y; sp.z = 1.f - h.z * h.z; sp.w = 1.f - h.w * h.w;
+      a[i][0] = h.x; a[i][1] = h.y; a[i][2] = h.z; a[i][3] = h.w;
+      reinterpret_cast<float4*>(q.sp[1] + (size_t)s * H)[tx] = sp;
+      reinterpret_cast<float4*>(q.T[1] + ((size_t)d * S + s) * H)[tx] = h;
+      if (write_tangents) {
+#pragma unroll
+        for (int j = 0; j < DB; ++j)
+          if (j < d)
+            reinterpret_cast<float4*>(q.T[1] + ((size_t)j * S + s) * H)[tx] =
+                make_float4(sp.x * w1[j].x, sp.y * w1[j].y, sp.z * w1[j].z, sp.w * w1[j].w);
+      }
+    }
+  }
+  int cur = 0;
+  for (int l = 2; l <= L; ++l, cur ^= 1) {
+    float* hb = hT + (size_t)cur * H * TC_CH_HS;
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+      *reinterpret_cast<float4*>(hb + (size_t)(4 * tx + u) * TC_CH_HS + 4 * ty) = make_float4(a[0][u], a[1][u], a[2][u], a[3][u]);
+    __syncthreads();   // (the other buffer was last read two layers ago)
+    const float4 bl = __ldg(reinterpret_cast<const float4*>(q.bp[l]) + tx);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) { a[i][0] = bl.x; a[i][1] = bl.y; a[i][2] = bl.z; a[i][3] = bl.w; }
+    const float* wl = Wt + (size_t)(l - 2) * H * H + 4 * tx;
+    const float* hr = hb + 4 * ty;
+#pragma unroll 8
+    for (int k = 0; k < H; ++k) {
+      const float4 w4 = *reinterpret_cast<const float4*>(wl + k * H);
+      const float4 h4 = *reinterpret_cast<const float4*>(hr + k * TC_CH_HS);
+      const float hi[4] = {h4.x, h4.y, h4.z, h4.w};
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        a[i][0] = fmaf(w4.x, hi[i], a[i][0]); a[i][1] = fmaf(w4.y, hi[i], a[i][1]);
+        a[i][2] = fmaf(w4.z, hi[i], a[i][2]); a[i][3] = fmaf(w4.w, hi[i], a[i][3]);
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int s = s0 + 4 * ty + i;
+      float4 h, sp;
+      h.x = act_tanh(a[i][0]); h.y = act_tanh(a[i][1]); h.z = act_tanh(a[i][2]); h.w = act_tanh(a[i][3]);
+      sp.x = 1.f - h.x * h.x; sp.y = 1.f - h.y * h.y; sp.z = 1.f - h.z * h.z; sp.w = 1.f - h.w * h.w;
+      a[i][0] = h.x; a[i][1] = h.y; a[i][2] = h.z; a[i][3] = h.w;
+      reinterpret_cast<float4*>(q.sp[l] + (size_t)s * H)[tx] = sp;
+      reinterpret_cast<float4*>(q.T[l] + ((size_t)d * S + s) * H)[tx] = h;
+    }
+  }
+}
+
 // suffix sums over the tangent directions: R[n][s][k] = sum_{j >= n} s_j[s] T_L[j][s][k], n < nb.  Block = one sample.
 __global__ void tc_rsum_kernel(TcDims g, const float* __restrict__ TL, const float* __restrict__ sj, float* __restrict__ R) {
   const int H = g.Hp[g.L], S = g.S, s = blockIdx.x, k = threadIdx.x;

@@ -778,8 +778,24 @@ int tc_run(const GpFlowDesc* d, int op, const float* params, const float* x_in, 
   const int g_dS = (dd * S + eb - 1) / eb, g_nS = (nb * S + eb - 1) / eb, g_S = (S + eb - 1) / eb;
 
   // ---- one velocity evaluation, forward: activations of the slab at the stage point xpt, time t (up to SX / FX / SD) ----
+  // 64-wide nets: tc_value_chain_kernel replaces tc_layer1_kernel and the value-row GEMM of every hidden layer
+  static const bool chain_on = [] { const char* e = getenv("GPFLOW_TC_CHAIN"); return !(e && e[0] == '0'); }();   // A/B switch
+  bool chain = chain_on && dd <= 16 && L >= 2 && L <= 4;
+  for (int l = 1; l <= L; ++l) chain = chain && g.Hp[l] == 64;
+  TcChainPtrs cq;
+  memset(&cq, 0, sizeof(cq));
+  for (int l = 1; l <= L; ++l) { cq.T[l] = P(b.T[l]); cq.sp[l] = P(b.sp[l]); cq.bp[l] = w.bp[l]; }
+  if (chain) {
+    static bool attr = false;
+    if (!attr) {
+      if (cudaFuncSetAttribute(tc_value_chain_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tc_chain_smem(4)) != cudaSuccess) return GPFLOW_ERR_CUDA;
+      attr = true;
+    }
+  }
   auto eval_forward = [&](const float* xpt, float t) -> int {
-    if (dd <= 16)
+    if (chain)
+      tc_value_chain_kernel<16><<<S / TC_CH_S, 256, tc_chain_smem(L), st>>>(g, params, w.W1T, cq, xpt, t, bnd, P(b.sj), (L == 1 || !gen_t1) ? 1 : 0);
+    else if (dd <= 16)
       tc_layer1_kernel<16, 4><<<S / 4, g.Hp[1], 0, st>>>(g, w.W1T, w.bp[1], xpt, t, bnd, P(b.T[1]), P(b.sp[1]), P(b.sj), (L == 1 || !gen_t1) ? 1 : 0);
     else
       tc_layer1_kernel<TC_DMAX, TC_L1_SPB_WIDE><<<S / TC_L1_SPB_WIDE, g.Hp[1], 0, st>>>(g, w.W1T, w.bp[1], xpt, t, bnd, P(b.T[1]), P(b.sp[1]), P(b.sj), (L == 1 || !gen_t1) ? 1 : 0);
@@ -791,7 +807,7 @@ int tc_run(const GpFlowDesc* d, int op, const float* params, const float* x_in, 
       p.bias = w.bp[l]; p.aux = P(b.sp[l]); p.out2 = P(b.sp[l]);
       p.gen_sp = nullptr; p.gen_w = nullptr;
       p.A = P(b.T[l - 1]) + (size_t)dd * S * p.K; p.M = S; p.mode = 0; p.out = P(b.T[l]) + (size_t)dd * S * p.N;
-      TC_CK(launch_gemm<LayerOp>(p, mt, sm_count, st));
+      if (!chain) TC_CK(launch_gemm<LayerOp>(p, mt, sm_count, st));
       p.A = P(b.T[l - 1]); p.M = (long long)dd * S; p.mode = 1; p.out = P(b.T[l]);
       if (l == 2 && gen_t1) { p.gen_sp = P(b.sp[1]); p.gen_w = w.W1T; }   // T_1 is not materialised
       TC_CK(launch_gemm<LayerOp>(p, dd * mt, sm_count, st));
