@@ -175,3 +175,35 @@ def test_measured_configuration_vs_fp64_oracle(name, B):
     assert abs(float(res["scalars"][0]) - float(r["ot"])) < 1e-5 * float(r["ot"])
     assert rel(res["grads"].cpu(), r["grads"]) < 1e-5, rel(res["grads"].cpu(), r["grads"])
     assert rel(res["grad_x"].cpu(), r["grad_x"]) < 2e-5
+
+
+@pytest.mark.parametrize("d,nb,hidden,w_std,n_sub", [(10, 9, (50, 50, 50), 0.05, 32), (64, 63, (256, 256), 0.02, 4)])
+def test_bench_rows_at_full_size_2p14_properties(d, nb, hidden, w_std, n_sub):
+    """The C3 / C5 rows of bench.py at their full per-GPU size (2^14 samples, N = 15, bench weights), through size-independent
+    properties: (i) the fused [grads | ot] buffer of the batch equals the SUM of the buffers of its two halves computed with
+    loss_scale = 1/2^14 (what the data-parallel all-reduce computes; different slab counts / split sizes on both sides);
+    (ii) y of a strided subsample equals the fp64 oracle on those samples; (iii) the OT scalar equals the mean over the
+    transported points the kernels wrote; (iv) a second launch is bit-identical."""
+    import gpflow_b200 as G
+    B, N = 1 << 14, 15
+    spec = O.FlowSpec(d=d, nb=nb, hidden=list(hidden), n_steps=N)
+    params = O.init_params(spec, w_std, 0, torch.float32)
+    flat = O.flatten_params(params).cuda()
+    g = torch.Generator(device="cuda").manual_seed(1234)
+    x_map = torch.randn(B, d, generator=g, device="cuda")
+    x_data = 0.9 * x_map.roll(1, dims=1) + 0.1
+    cfg = G.FlowConfig(d=d, nb=nb, hidden=tuple(hidden), n_steps=N)
+    assert "gpflow_tc" in G.kernel_variant(cfg)
+    full = G.fused_train_step(cfg, flat, x_data, x_map, want_y=True)
+    again = G.fused_train_step(cfg, flat, x_data, x_map)["buf"].clone()
+    assert torch.equal(again, full["buf"])
+    acc = torch.zeros_like(full["buf"], dtype=torch.float64)
+    for r in range(2):
+        lo, hi = r * (B // 2), (r + 1) * (B // 2)
+        acc += G.fused_train_step(cfg, flat, x_data[lo:hi], x_map[lo:hi], loss_scale=1.0 / B)["buf"].double()
+    assert rel(acc.cpu(), full["buf"].double().cpu()) < 5e-6, rel(acc.cpu(), full["buf"].double().cpu())
+    idx = torch.arange(0, B, B // n_sub, device="cuda")
+    r64 = O.train_step([p.double() for p in params], x_data[idx].cpu().double(), x_map[idx].cpu().double(), spec)
+    assert rel(full["y"][idx].cpu(), r64["y"]) < 1e-5
+    ot = ((x_data.double() - full["y"].double()) ** 2).sum(1).mean()
+    assert abs(float(full["scalars"][0]) - float(ot)) < 2e-6 * float(ot)
