@@ -435,7 +435,7 @@ def measure_workload(args, name, wl, euler, rank, world, local_rank, dev, steps,
         opt.step()
     torch.cuda.synchronize()
     per_rank = None
-    if world > 1:
+    if world > 1 and euler is None:
         # diagnostic, outside the timed region: every rank's kernel time WITHOUT the all-reduce, all GPUs of the box busy at
         # the same time -- the synchronous step runs at the pace of the slowest of these
         dist.barrier()
@@ -452,6 +452,7 @@ def measure_workload(args, name, wl, euler, rank, world, local_rank, dev, steps,
         dist.all_gather(allr, mine)
         per_rank = {"solo_kernel_ms": [round(float(v), 3) for v in allr],
                     "what": "3 train-step launches per rank without the all-reduce, all ranks at once, before the timed region"}
+    if world > 1:
         dist.barrier()
     clocks = ClockSampler(local_rank)
     if rank == 0 and "noclk" not in args.dbg:
