@@ -579,11 +579,14 @@ inline size_t tc_per_sample_floats(const TcDims& g, int n_steps, bool train) {
   if (train) f += (size_t)7 * g.d + 2 * g.nb;
   return f + 2;
 }
-// slab size: a multiple of 256 samples, the per-slab buffers bounded by ~880 MB (C5: 2048 samples), equal slabs
+// slab size: a multiple of 256 samples, the per-slab buffers bounded by a budget, equal slabs.  The budget is sized for
+// 180 GB of HBM: 7 GB lets C5 (395 KB per sample) run its 2^14-sample batch as ONE slab.  Measured at C5, 2^14 samples
+// (GPFLOW_TC_SLAB_MB = 880 / 1760 / 3520 / 7040 -> slabs of 2048 / 4096 / 8192 / 16384): 1000 / 906 / 856 / 834 ms per step --
+// larger slabs mean 8 x fewer launches and value-row / reduction launches that fill the chip (a 2048-row GEMM is 16 tiles).
 inline int tc_slab_size(const GpFlowDesc* d, int64_t B, int op) {
   const TcDims g = tc_make_dims(d, 256);
   const size_t per = tc_per_sample_floats(g, d->n_steps, op != GPFLOW_OP_FORWARD) * 4;
-  size_t budget_mb = 880;
+  size_t budget_mb = 7040;
   if (const char* e = getenv("GPFLOW_TC_SLAB_MB")) {   // experiment knob: per-slab buffer budget
     const long long v = atoll(e);
     if (v >= 64 && v <= 65536) budget_mb = (size_t)v;
