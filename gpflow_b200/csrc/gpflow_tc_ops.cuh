@@ -349,6 +349,10 @@ inline bool tc_l1b_small_enabled() {   // GPFLOW_TC_L1B_SMALL=0: the round-1 fir
   static const bool on = [] { const char* e = getenv("GPFLOW_TC_L1B_SMALL"); return !(e && e[0] == '0'); }();
   return on;
 }
+inline bool tc_l1b_small_forced() {    // GPFLOW_TC_L1B_SMALL=2: also for wide first layers (experiment)
+  static const bool on = [] { const char* e = getenv("GPFLOW_TC_L1B_SMALL"); return e && e[0] == '2'; }();
+  return on;
+}
 inline bool tc_w3_small_enabled() {   // GPFLOW_TC_W3_SMALL=0: the tensor-core GEMM for every width (A/B switch)
   static const bool on = [] { const char* e = getenv("GPFLOW_TC_W3_SMALL"); return !(e && e[0] == '0'); }();
   return on;
@@ -636,7 +640,7 @@ inline void tc_carve(const TcDims& g, int n_steps, bool train, int sm_count, TcB
     b.gW1 = take((size_t)g.Hp[1] * (d + 2));
     // tc_layer1_bwd_b_small_kernel (one plane per 32 samples): narrow first layers only -- measured at C5 (d = 64, 256 wide,
     // 4 x 4 direction / unit tiles per sample block): 1056 ms per step against 993 ms with the kernel above
-    b.l1b_small = g.Hp[1] == 64 && d <= 16 && tc_l1b_small_enabled();
+    b.l1b_small = ((g.Hp[1] == 64 && d <= 16) || tc_l1b_small_forced()) && g.Hp[1] % 64 == 0 && tc_l1b_small_enabled();
     b.nz1 = b.l1b_small ? S / TC_L1B_CH : b.nz;
     b.zW1 = take((size_t)b.nz1 * g.Hp[1] * (d + 2));
     b.zb3 = take((size_t)(S / 64) * g.nout);
