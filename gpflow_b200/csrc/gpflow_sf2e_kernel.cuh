@@ -89,6 +89,11 @@ __global__ void __launch_bounds__(NW * 32, 1) gpflow_sf2e_kernel(const SF2EArgs 
   for (int i = 0; i < 4; ++i) acc3[i] = 0.0f;
 
   const long long ntiles = (a.B + 31) / 32;
+  if (a.stagger_cycles != 0) {   // warp w starts (w * 5 mod NW) / NW * |stagger_cycles| late, see gpflow_sf2r_kernel
+    const long long wait = (long long)(a.stagger_cycles < 0 ? -a.stagger_cycles : a.stagger_cycles) * ((warp * 5) % NW) / NW;
+    const long long t0 = clock64();
+    while (clock64() - t0 < wait) __nanosleep(256);
+  }
   for (long long tile = slot; tile < ntiles; tile += nslots) {
     const long long b = tile * 32 + lane;
     const bool valid = b < a.B;
@@ -367,6 +372,11 @@ int launch_sf2e(const GpFlowDesc* d, const Ptrs<float>& p, int64_t B, void* ws, 
   ea.zw = p.zw;
   ea.reg_cot = p.reg_cot;
   ea.euler_coef = (float)d->euler_coef;
+  // staggered warp start (GPFLOW_SF2E_STAGGER = cycles spread over the 8 warps; default 0 = off).  Measured on the C4 Euler row
+  // (tools/sf2e_stagger_ab.sh, profiles/r2_sf2e_stagger_and_batch_sweep.txt): 0 / 4e4 / 1.6e5 / 6.4e5 / 2.5e6 cycles ->
+  // 141.5 / 141.0 / 147.0 / 144.6 / 138.5 ms, i.e. run-to-run noise: unlike sf2r the 8 warps do not gain from being out of phase.
+  static const int stagger_env = [] { const char* e = getenv("GPFLOW_SF2E_STAGGER"); return e ? atoi(e) : 0; }();
+  a.stagger_cycles = tiles >= 4 * slots ? stagger_env : 0;
   const int rc = sf2r_launch_guarded<R>(p.params, packed, st, [&]() { kern<<<(unsigned)grid, NW * 32, smem, st>>>(ea); });
   if (rc != GPFLOW_OK) return rc;
   gpflow_finalize_wide_kernel<float><<<(npart + 31) / 32, 256, 0, st>>>(a.partials, (int)slots, npart, npart, p.scalars_out,
