@@ -48,6 +48,7 @@ struct SF2Args {
   float sigma;
   float loss_scale;
   int stagger_cycles;  // sf2r: warps of the upper half start this many cycles late (GPFLOW_SF2R_STAGGER, experiments)
+  int cta_align;        // sf2e: 1 = named barrier over the CTA's active warps before every RK4 step (keeps them in phase)
 };
 
 // weights never change after the prologue: volatile asm keeps each (warp-uniform) load next to its use instead of

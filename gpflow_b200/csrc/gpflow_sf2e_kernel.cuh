@@ -103,6 +103,15 @@ __global__ void __launch_bounds__(NW * 32, 1) gpflow_sf2e_kernel(const SF2EArgs 
       xin1 = a.x_in[2 * b + 1];
     }
     float x0 = wrap ? erf_real(xin0 * rsq2s) : xin0, x1 = wrap ? erf_real(xin1 * rsq2s) : xin1;
+    // The CTA's warps run the same 2 N steps per tile on different samples.  A named barrier over the warps that have a tile
+    // in this round (a prefix of the warps: slot = warp * grid + block) keeps them within one RK4 step of each other, so that
+    // they share the instruction-cache footprint of the 7 000-instruction kernel (the generic kernel does the same).
+    long long n_act = (ntiles - (tile - slot) - blockIdx.x + gridDim.x - 1) / gridDim.x;
+    if (n_act > NW) n_act = NW;
+    const unsigned n_act_threads = 32u * (unsigned)n_act;
+    auto cta_align = [&]() {
+      if (a.cta_align && n_act_threads > 32u) asm volatile("bar.sync 1, %0;" ::"r"(n_act_threads) : "memory");
+    };
 
     // ---------------- forward sweep ----------------
     float pen = 0.0f;
@@ -125,6 +134,7 @@ __global__ void __launch_bounds__(NW * 32, 1) gpflow_sf2e_kernel(const SF2EArgs 
     };
 #pragma unroll 1
     for (int i = 0; i < N; ++i) {
+      cta_align();
       const float t = times[i];
       float ys0 = x0, ys1 = x1, ks0 = 0.f, ks1 = 0.f;
 #pragma unroll 1
@@ -223,6 +233,7 @@ __global__ void __launch_bounds__(NW * 32, 1) gpflow_sf2e_kernel(const SF2EArgs 
     }
 #pragma unroll 1
     for (int i = N - 1; i >= 0; --i) {
+      cta_align();
       const float t = times[i];
       // ---- penalty: d(pen_w q^2) at (x_{i+1}, t_i); operations 7, 6 (direction z) then 5, 4 (direction w)
       {
@@ -377,6 +388,12 @@ int launch_sf2e(const GpFlowDesc* d, const Ptrs<float>& p, int64_t B, void* ws, 
   // 141.5 / 141.0 / 147.0 / 144.6 / 138.5 ms, i.e. run-to-run noise: unlike sf2r the 8 warps do not gain from being out of phase.
   static const int stagger_env = [] { const char* e = getenv("GPFLOW_SF2E_STAGGER"); return e ? atoi(e) : 0; }();
   a.stagger_cycles = tiles >= 4 * slots ? stagger_env : 0;
+  // phase alignment of the CTA's warps (GPFLOW_SF2E_ALIGN=0: free-running).  Measured on the C4 Euler row, same box, alternating:
+  // 138.7 / 139.9 ms free-running, 103.2 / 103.2 ms aligned (2.99e7 -> 4.06e7 samples/s).  The row also ran 16 % slower per
+  // sample at 2^22 than at 2^19 samples (profiles/r2_sf2e_stagger_and_batch_sweep.txt): free-running warps drift apart over
+  // a long launch and each then misses the instruction cache on its own (7 080 SASS instructions = 113 KB).
+  static const int align_env = [] { const char* e = getenv("GPFLOW_SF2E_ALIGN"); return e ? atoi(e) : 1; }();
+  a.cta_align = align_env;
   const int rc = sf2r_launch_guarded<R>(p.params, packed, st, [&]() { kern<<<(unsigned)grid, NW * 32, smem, st>>>(ea); });
   if (rc != GPFLOW_OK) return rc;
   gpflow_finalize_wide_kernel<float><<<(npart + 31) / 32, 256, 0, st>>>(a.partials, (int)slots, npart, npart, p.scalars_out,

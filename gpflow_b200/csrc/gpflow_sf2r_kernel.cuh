@@ -130,12 +130,21 @@ __global__ void __launch_bounds__(NW * 32, 1) gpflow_sf2r_kernel(const SF2Args a
       xin1 = a.x_in[2 * b + 1];
     }
     float x0 = wrap ? erf_real(xin0 * rsq2s) : xin0, x1 = wrap ? erf_real(xin1 * rsq2s) : xin1;
+    // optional phase alignment of the CTA's warps, one named barrier per RK4 step (see gpflow_sf2e_kernel, where it is worth
+    // +36 %; measured here: see launch_sf2r)
+    long long n_act = (ntiles - (tile - slot) - blockIdx.x + gridDim.x - 1) / gridDim.x;
+    if (n_act > NW) n_act = NW;
+    const unsigned n_act_threads = 32u * (unsigned)n_act;
+    auto cta_align = [&]() {
+      if (a.cta_align && n_act_threads > 32u) asm volatile("bar.sync 1, %0;" ::"r"(n_act_threads) : "memory");
+    };
 
     // ---------------- forward sweep: 4N velocity evaluations, classical RK4 (ode_order_method.py:66-71) ----------
     float ys0 = x0, ys1 = x1, ks0 = 0.f, ks1 = 0.f;
 #pragma unroll 1
     for (int e = 0; e < E; ++e) {
       const int sg = e & 3, buf = e & 1;
+      if (sg == 0) cta_align();
       const float4 sc = ldsw4(sct + 4 * sg);
       const float ts = times[e >> 2] + sc.x;  // t, t + dt/2, t + dt/2, t + dt
       float* const Sb = Sbuf0 + buf * K::S_FL;
@@ -209,6 +218,7 @@ __global__ void __launch_bounds__(NW * 32, 1) gpflow_sf2r_kernel(const SF2Args a
 #pragma unroll 1
     for (int e = E - 1; e >= 0; --e) {
       const int sg = e & 3, buf = e & 1;
+      if (sg == 3) cta_align();
       const float4 sc = ldsw4(sct + 4 * sg);
       const float ts = times[e >> 2] + sc.x;
       // prefetch the rows of evaluation e-1 into the other buffer (its previous user, e+1, is complete); the same
@@ -402,6 +412,12 @@ int launch_sf2r(const GpFlowDesc* d, const Ptrs<float>& p, int64_t B, void* ws, 
   // 0 = off; negative = spread over the warps, positive = odd warps late).  Only when every warp has >= 4 tiles.
   static const int stagger_env = [] { const char* e = getenv("GPFLOW_SF2R_STAGGER"); return e ? atoi(e) : 1; }();
   a.stagger_cycles = stagger_env != 1 ? stagger_env : (tiles >= 4 * slots ? -26000 * d->n_steps : 0);
+  // GPFLOW_SF2R_ALIGN=1: one named barrier per RK4 step over the CTA's warps.  Worth +36 % in gpflow_sf2e_kernel (instruction
+  // cache); measured here on the C4 headline, alternating: 108.6 / 108.8 ms free-running, 124.5 / 124.5 ms aligned -- this
+  // kernel fits the instruction cache and is bound by the FMA and shared-memory pipes, which aligned warps hit in phase.
+  static const int align_env = [] { const char* e = getenv("GPFLOW_SF2R_ALIGN"); return e ? atoi(e) : 0; }();
+  a.cta_align = align_env;
+  if (a.cta_align) a.stagger_cycles = 0;   // aligned warps start together
   const int rc = sf2r_launch_guarded<K>(p.params, packed, st, [&]() { kern<<<(unsigned)grid, NW * 32, smem, st>>>(a); });
   if (rc != GPFLOW_OK) return rc;
   gpflow_finalize_wide_kernel<float><<<(npart + 31) / 32, 256, 0, st>>>(a.partials, (int)slots, npart, npart, p.scalars_out,
