@@ -18,15 +18,18 @@
 
 namespace gpflow {
 
-// rolled contraction loops of the dual evaluations: unroll factor, and where their weight rows come from (a bit of
-// GPF_SF2R_CONST: 1 = constant bank like the unrolled plain forward evaluation, 2 = shared memory).  Measured on the C4
-// Euler row (tools/sf2e_ab.sh): unroll 1 / 3 / 5 and either source are all 157.6-159.2 ms -- the kernel is bound by
-// dependency latency at 2 warps per scheduler, not by these loops.
+// contraction loops of the dual evaluations: unroll factor, and where their weight rows come from (a bit of GPF_SF2R_CONST:
+// 1 = constant bank like the unrolled plain forward evaluation, 2 = shared memory).  Measured on the C4 Euler row.  With
+// free-running warps (first build) unroll 1 / 3 / 5 and either source were all 157.6-159.2 ms -- every warp missed the
+// instruction cache on its own whatever the code size.  Since the CTA's warps are kept in phase (gpflow_sf2e_kernel.cuh,
+// cta_align) they share the instruction stream and the unrolled form pays (tools/sf2e_ab2.sh, sf2e_ab3.sh,
+// profiles/r2_sf2e_aligned_ab.txt): unroll 1 / 3 / 5 / 15 from shared memory 103.2 / 101.6 / 101.2 / 97.9 ms, unroll 15 from
+// the constant bank 95.9 ms (4.37e7 samples/s).
 #ifndef GPF_SF2E_UNROLL
-#define GPF_SF2E_UNROLL 1
+#define GPF_SF2E_UNROLL 15
 #endif
 #ifndef GPF_SF2E_WBIT
-#define GPF_SF2E_WBIT 2
+#define GPF_SF2E_WBIT 1
 #endif
 constexpr int kSF2EUnroll = GPF_SF2E_UNROLL;
 typedef float2 du;  // dual number: .x = value, .y = epsilon part
@@ -34,7 +37,7 @@ typedef float2 du;  // dual number: .x = value, .y = epsilon part
 // FADD of the executed instructions, profiles/r2_sf2e_ncu_summary.txt).  Measured on the C4 Euler row, same box, alternating
 // builds (tools/sf2e_packed_ab.sh, profiles/r2_sf2e_packed_ab.txt): 152.8 / 155.9 ms packed against 139.4 / 140.7 ms scalar --
 // a packed instruction holds the FMA pipe for two cycles and needs aligned register pairs (extra moves at 255 registers),
-// so fewer instructions do not pay here.  Default 0.
+// so fewer instructions do not pay here (with aligned warps and unrolled loops: 98.3 against 97.9 ms, still no gain).  Default 0.
 #ifndef GPF_SF2E_PACKED
 #define GPF_SF2E_PACKED 0
 #endif

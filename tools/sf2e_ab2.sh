@@ -1,0 +1,8 @@
+# after the phase alignment of the warps: the unroll factor of the dual contraction loops again (GPF_SF2E_UNROLL), C4 Euler row
+for u in 1 3 5 15; do
+  GPFLOW_NVCC_EXTRA="-DGPF_SF2E_UNROLL=$u" python -m gpflow_b200.build --force > /dev/null 2>&1
+  python bench.py --rows c4_2d_euler_5e-4 --no-cpu-baseline --no-e2e --steps 5 2>/dev/null | python -c "
+import json,sys
+j=json.loads(sys.stdin.read().strip().splitlines()[-1])
+for r in j['rows']: print('unroll $u', r['value'], r['ms_per_step'])"
+done
