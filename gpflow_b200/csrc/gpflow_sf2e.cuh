@@ -32,6 +32,12 @@ namespace gpflow {
 #define GPF_SF2E_WBIT 1
 #endif
 constexpr int kSF2EUnroll = GPF_SF2E_UNROLL;
+// pair-accumulator rank update of sf2e_reverse_eval (14 % of the instructions, top stall short_scoreboard on its LDS.128): unroll
+// 2 / 4 / 16 -> 96.1 / 96.4 / 91.7 ms on the C4 Euler row (tools/sf2e_ab4.sh; 56 B of spills at 4 and 16)
+#ifndef GPF_SF2E_RANK_UNROLL
+#define GPF_SF2E_RANK_UNROLL 16
+#endif
+constexpr int kSF2ERankUnroll = GPF_SF2E_RANK_UNROLL;   // pair-accumulator rank update of sf2e_reverse_eval
 typedef float2 du;  // dual number: .x = value, .y = epsilon part
 // GPF_SF2E_PACKED = 1: the element-wise dual operations as packed fp32x2 instructions as well (the scalar forms are 17 % FMUL +
 // FADD of the executed instructions, profiles/r2_sf2e_ncu_summary.txt).  Measured on the C4 Euler row, same box, alternating

@@ -103,7 +103,7 @@ GPF_DEV void sf2e_reverse_eval(const float* __restrict__ W, float* __restrict__ 
     const float* wl = Wk + slice * K::WS + K::O_L + 8 * ti;
     const float* wc = Wk + slice * K::WS + K::O_C + 8 * tj;
     __syncwarp();
-#pragma unroll 2
+#pragma unroll kSF2ERankUnroll
     for (int q = 0; q < 16; ++q) {
       const int s = slice + 2 * q;
       const float* dr = Dbuf + s * K::DROW;
