@@ -8,7 +8,8 @@ torch.manual_seed(0)
 flat = (0.3 * torch.randn(cfg.n_params)).cuda()
 for B in (1024, 4096, 65536):
     xm = torch.randn(B, 2, device="cuda"); xd = 1.2 * xm.flip(-1) + 0.3
-    for name, kw in (("sf2", {}), ("v1", {"force_v1": True}), ("v1+euler", {"force_v1": True, "euler_coef": 5e-4, "zw": torch.randn(15, 2, 2)})):
+    for name, kw in (("sf2", {}), ("v1", {"force_v1": True}), ("v1+euler", {"force_v1": True, "euler_coef": 5e-4, "zw": torch.randn(15, 2, 2)}),
+                     ("sf2e euler", {"euler_coef": 5e-4, "zw": torch.randn(15, 2, 2)})):
         for _ in range(5): ops.fused_train_step(cfg, flat, xd, xm, **kw)
         ts = []
         for _ in range(20):
@@ -16,7 +17,7 @@ for B in (1024, 4096, 65536):
             e0.record(); ops.fused_train_step(cfg, flat, xd, xm, **kw); e1.record(); e1.synchronize()
             ts.append(e0.elapsed_time(e1))
         ts.sort()
-        print("B=%6d %-9s median %.3f ms  -> %.3g samples/s" % (B, name, ts[10], B / ts[10] * 1e3), flush=True)
+        print("B=%6d %-10s median %.3f ms  -> %.3g samples/s" % (B, name, ts[10], B / ts[10] * 1e3), flush=True)
 
 # whole optimisation step at B = 1024 (C1): module API, wall clock over 300 steps (host launch overhead included)
 import time
