@@ -160,13 +160,16 @@ int pad2d_run(const GpFlowDesc* d, const GpFlowDesc* d15, int op, const Ptrs<flo
 // tc (chunked tensor-core path) takes the wide fp32 shapes without Euler penalization once the batch is large enough to
 // fill 128-row MMA tiles on every SM; GPFLOW_TC_MIN_BATCH overrides the threshold, GPFLOW_FLAG_FORCE_TC ignores it.
 // Measured crossovers (B200, train step, profiles/r2_tc_crossover.txt): d=10, H=[50,50,50] -- generic 29.6 ms vs tc 33.5 ms at
-// B = 4096, 58.4 vs 47.2 ms at 8192; d=64, H=[256,256] -- tc 8x faster already at B = 256.
+// B = 4096, 58.4 vs 47.2 ms at 8192; d=64, H=[256,256] -- tc 8x faster already at B = 256.  Re-measured after the narrow-width
+// work on the tc path (tools/tc_crossover.sh, profiles/r2_tc_crossover_v2.txt): d=10 -- generic 14.9 / 28.5 / 29.6 / 44.1 / 58.5 ms
+// against tc 19.3 / 20.6 / 23.5 / 27.7 / 32.1 ms at B = 2048 / 3072 / 4096 / 6144 / 8192 (the generic kernel steps up with every
+// 2368 samples = one round of its warp slots).
 int64_t tc_min_batch(const GpFlowDesc* d) {
   static const int64_t env = [] { const char* e = getenv("GPFLOW_TC_MIN_BATCH"); return e ? (int64_t)atoll(e) : (int64_t)-1; }();
   if (env >= 0) return env;
   int hmax = 0;
   for (int i = 0; i < d->n_hidden; ++i) hmax = d->hidden[i] > hmax ? d->hidden[i] : hmax;
-  return hmax <= 64 ? 6144 : 128;
+  return hmax <= 64 ? 2400 : 128;   // narrow nets: from the batch that needs a second round of the generic kernel's 148 x 16 warp slots
 }
 bool tc_selected(const GpFlowDesc* d, int64_t B) {
   if (d->flags & (GPFLOW_FLAG_FORCE_GENERIC | GPFLOW_FLAG_EULER_PEN)) return false;

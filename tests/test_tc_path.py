@@ -116,7 +116,7 @@ def test_tc_is_the_default_for_large_wide_batches():
     spec, params, x_data, x_map = _inputs(10, 9, (50, 50, 50), 6144, 2, 0.03)
     flat = O.flatten_params(params).float().cuda()
     cfg2 = G.FlowConfig(d=10, nb=9, hidden=(50, 50, 50), n_steps=2)
-    a = G.fused_train_step(cfg2, flat, x_data.float().cuda(), x_map.float().cuda())                      # default: tc from B = 6144 for this shape
+    a = G.fused_train_step(cfg2, flat, x_data.float().cuda(), x_map.float().cuda())                      # default: tc from B = 2400 for this shape
     b = G.fused_train_step(cfg2, flat, x_data.float().cuda(), x_map.float().cuda(), force_tc=True)
     c = G.fused_train_step(cfg2, flat, x_data.float().cuda(), x_map.float().cuda(), force_generic=True)
     assert torch.equal(a["buf"], b["buf"]) and rel(a["grads"].cpu(), c["grads"].cpu()) < 5e-6
