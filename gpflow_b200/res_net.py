@@ -21,6 +21,11 @@ from .ops import FlowConfig
 from .velocity_field import CONTINUOUS_TIME, VelocityField
 
 
+import weakref
+
+_PROBE_RINGS = weakref.WeakKeyDictionary()   # ResNet -> pinned staging buffers of draw_probes
+
+
 class Compose(torch.nn.Module):
     """compose.py:5-69 -- sequential composition of several flows (nb_blocks != 1); a thin Python loop."""
 
@@ -167,12 +172,30 @@ class ResNet(torch.nn.Module):
         """The reference draws z then w with torch.randn(1, d) once per step on the default (CPU) generator
         (res_net.py:330-333); same calls, same order -> same RNG stream."""
         d = self.dim
-        rows = []
-        for _ in range(n_steps):
-            z = torch.randn(1, d)
-            w = torch.randn(1, d)
-            rows.append(torch.stack([z[0], w[0]]))
-        return torch.stack(rows).to(device=like.device, dtype=like.dtype)
+        rows = torch.empty(n_steps, 2, d)
+        for i in range(n_steps):
+            rows[i, 0] = torch.randn(1, d)[0]
+            rows[i, 1] = torch.randn(1, d)[0]
+        if like.device.type != "cuda":
+            return rows.to(dtype=like.dtype)
+        # host -> device without stalling the host: a pageable `.to(device)` blocks until the stream has drained, which puts
+        # the host one step behind the GPU in a training loop (a gap before every kernel).  Two pinned staging buffers,
+        # each guarded by the event of its last copy.
+        ring = _PROBE_RINGS.setdefault(self, {"slots": [], "next": 0})   # outside the module: deepcopy / pickle stay clean
+        key = (n_steps, d, like.dtype, like.device)
+        if ring.get("key") != key:
+            ring["key"], ring["next"] = key, 0
+            ring["slots"] = [[torch.empty(n_steps, 2, d, dtype=like.dtype).pin_memory(), None] for _ in range(2)]
+        slot = ring["slots"][ring["next"]]
+        ring["next"] ^= 1
+        if slot[1] is not None:
+            slot[1].synchronize()            # the copy that last read this buffer (two draws ago) has completed
+        slot[0].copy_(rows)
+        out = slot[0].to(like.device, non_blocking=True)
+        ev = torch.cuda.Event()
+        ev.record(torch.cuda.current_stream(like.device))
+        slot[1] = ev
+        return out
 
     def forward(self, x, training=False, current_epoch=0, reverse=False, save_trajectories=False, id_final_layer=-1,
                 _wrap=False, _sigma=1.0):
