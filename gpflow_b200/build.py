@@ -81,8 +81,11 @@ def build(force=False, verbose=False):
                        capture_output=True, text=True)
     if r.returncode != 0:
         raise RuntimeError("link failed:\n" + r.stderr[-4000:])
+    extra = os.environ.get("GPFLOW_NVCC_EXTRA", "").strip()
     with open(HASH_FILE, "w") as f:
-        f.write(source_hash() + "\n")
+        # an experiment build (extra -D flags) is marked: up_to_date() is then false and the next plain build() restores
+        # the default library, smoke() refuses a marked one
+        f.write(source_hash() + (" +extra:" + extra if extra else "") + "\n")
     return LIB
 
 

@@ -79,7 +79,10 @@ struct SF2E {
   static constexpr int WS = 92, O_L = 0, O_C = 32, O_E = 64, O_XG = 80;
   static constexpr int WK_FL = 32 * WS;   // also holds the plain work rows (32 x 68)
   static_assert(WK_FL >= R::WK_FL, "plain work rows alias the dual ones");
-  static constexpr int WARP_FL = 2 * REG_FL + WK_FL;
+  // NW > 8: ONE stash region per warp (no overlap of a bulk copy with the next evaluation of the same warp; more warps cover it)
+  static constexpr bool SINGLE = NW_ > 8;
+  static constexpr int NREG = SINGLE ? 1 : 2;
+  static constexpr int WARP_FL = NREG * REG_FL + WK_FL;
   // stash slots of one RK4 step: 4 plain evaluations, then 4 dual ones (direction w: point 1, point 2; direction z: ...)
   static constexpr int STEP_BYTES = 4 * R::STASH_BYTES + 4 * DSTASH_BYTES;
   GPF_DEV static size_t op_offset(int step, int j) {

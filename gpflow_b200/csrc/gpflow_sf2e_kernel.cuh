@@ -21,7 +21,14 @@ struct SF2EArgs {
 // dual rows single-buffered) and 84-float work rows fit 12 warps at 168 registers: 155.9 vs 157.6 ms on the C4 Euler row and
 // slower at small batches -- 750 B of spills, and with 12 warps spread over 7 000 instructions of code `no_instruction` is
 // back at 0.62 stall cycles per issue (0.18 with 8 warps).  Not kept.
-constexpr int kSF2EWarps = 8;
+// warps per CTA (= per SM).  8: two stash regions per warp, 255 registers.  9 - 11 (GPF_SF2E_WARPS): ONE region per warp, and the
+// register file then allows 168 registers (472 B of spills).  Measured with 11 warps on the phase-aligned build, C4 Euler
+// row: 114.5 ms against 91.7 ms with 8 warps (parity green) -- the dual evaluations need their 255 registers more than the
+// schedulers need a third warp.
+#ifndef GPF_SF2E_WARPS
+#define GPF_SF2E_WARPS 8
+#endif
+constexpr int kSF2EWarps = GPF_SF2E_WARPS;
 
 template <int H1, int H2, int NW>
 __global__ void __launch_bounds__(NW * 32, 1) gpflow_sf2e_kernel(const SF2EArgs ea) {
@@ -60,7 +67,7 @@ __global__ void __launch_bounds__(NW * 32, 1) gpflow_sf2e_kernel(const SF2EArgs 
   }
   float* const wa = warp_area + (size_t)warp * K::WARP_FL;
   float* const Reg0 = wa;                  // stash region r = Reg0 + r * REG_FL (plain rows use its first 4 KB)
-  float* const Wk = wa + 2 * K::REG_FL;    // work rows (plain: [32][68], dual: [32][92])
+  float* const Wk = wa + K::NREG * K::REG_FL;    // work rows (plain: [32][68], dual: [32][92])
   const int slot = warp * gridDim.x + blockIdx.x, nslots = gridDim.x * NW;
   constexpr int G_PEN = R::NACC, G_W2D = R::NACC + 1, NACC = R::NACC + 17;   // + penalty, + the dual evaluations' dW2 tile
   float* const G = a.g2 + (size_t)slot * NACC * 32;
@@ -117,6 +124,13 @@ __global__ void __launch_bounds__(NW * 32, 1) gpflow_sf2e_kernel(const SF2EArgs 
     float pen = 0.0f;
     int op = 0;   // stash operations issued for this tile (region = op & 1)
     auto begin_op = [&]() -> float* {
+      if (K::SINGLE) {
+        if (op >= 1) {  // the bulk store of the previous operation must have read the region
+          if (lane == 0) bulk_wait_read<0>();
+          __syncwarp();
+        }
+        return Reg0;
+      }
       if (op >= 2) {  // the bulk store that read this region two operations ago must have drained
         if (lane == 0) bulk_wait_read<1>();
         __syncwarp();
@@ -213,13 +227,19 @@ __global__ void __launch_bounds__(NW * 32, 1) gpflow_sf2e_kernel(const SF2EArgs 
     }
     // ---------------- reverse sweep: stash operations 8N-1 ... 0 ----------------
     auto issue_load = [&](int o) {   // lane 0 only
-      const int r = o & 1, j = o & 7;
+      const int r = K::SINGLE ? 0 : (o & 1), j = o & 7;
       mbar_expect_tx(mybars + r, K::op_bytes(j));
       bulk_g2s(Reg0 + r * K::REG_FL, stash + K::op_offset(o >> 3, j), K::op_bytes(j), mybars + r);
     };
     auto next_rows = [&](int o) -> float* {   // rows of operation o: prefetch o - 1, wait for o
       fence_proxy_async();
       __syncwarp();
+      if (K::SINGLE) {   // the previous operation's rows are dead now: load this one's into the same region
+        if (lane == 0 && o != 8 * N - 1) issue_load(o);
+        mbar_wait(mybars, phbits & 1u);
+        phbits ^= 1u;
+        return Reg0;
+      }
       if (o > 0 && lane == 0) issue_load(o - 1);
       const int r = o & 1;
       mbar_wait(mybars + r, (phbits >> r) & 1u);
