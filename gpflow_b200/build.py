@@ -51,6 +51,9 @@ def up_to_date():
 
 
 def build(force=False, verbose=False):
+    # objects of an experiment build (GPFLOW_NVCC_EXTRA) must not be re-linked into a default library, and vice versa
+    if "+extra" in (built_hash() or "") or os.environ.get("GPFLOW_NVCC_EXTRA", "").strip():
+        force = True
     if not force and up_to_date():
         return LIB
     nvcc = os.environ.get("NVCC", "nvcc")
