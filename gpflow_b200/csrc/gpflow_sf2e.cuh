@@ -31,6 +31,12 @@ namespace gpflow {
 #ifndef GPF_SF2E_WBIT
 #define GPF_SF2E_WBIT 1
 #endif
+#ifndef GPF_SF2E_W1BIT
+#define GPF_SF2E_W1BIT 4   // layer-1 weight rows and b3 in the dual reverse sweep: 4 = shared memory (89.8 ms), 1 = constant bank (99.7 ms; tools/sf2e_ab6.sh)
+#endif
+#ifndef GPF_SF2E_RBIT
+#define GPF_SF2E_RBIT 1   // weight rows of the dual REVERSE contraction: 2 = shared memory (91.65 ms), 1 = constant bank (89.70 ms; tools/sf2e_ab5.sh)
+#endif
 constexpr int kSF2EUnroll = GPF_SF2E_UNROLL;
 // pair-accumulator rank update of sf2e_reverse_eval (14 % of the instructions, top stall short_scoreboard on its LDS.128): unroll
 // 2 / 4 / 16 -> 96.1 / 96.4 / 91.7 ms on the C4 Euler row (tools/sf2e_ab4.sh; 56 B of spills at 4 and 16)

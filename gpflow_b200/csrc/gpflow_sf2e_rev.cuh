@@ -40,7 +40,7 @@ GPF_DEV void sf2e_reverse_eval(const float* __restrict__ W, float* __restrict__ 
 #pragma unroll
   for (int m = 0; m < 15; ++m) {
     if (m < H1) {
-      const float4 w = ldwr4<4>(W, R::W1P + 4 * m);
+      const float4 w = ldwr4<GPF_SF2E_W1BIT>(W, R::W1P + 4 * m);
       cq[m + 1] = d_mul(d_sp(hp[m + 1]), d_fma(w.x, gb0, d_scale(w.y, gb1)));
     } else {
       cq[m + 1] = d_make(0.0f, 0.0f);
@@ -57,7 +57,7 @@ GPF_DEV void sf2e_reverse_eval(const float* __restrict__ W, float* __restrict__ 
   du hb[16], z[16];
 #pragma unroll
   for (int pm = 0; pm < 16; ++pm) hb[pm] = z[pm] = d_make(0.0f, 0.0f);
-  du psi = d_make(ldwr4<4>(W, R::B3C).x, 0.0f);
+  du psi = d_make(ldwr4<GPF_SF2E_W1BIT>(W, R::B3C).x, 0.0f);
   Wrow[K::O_E] = 0.0f;
   sts4(Wrow + K::O_L, 0.0f, 0.0f, 0.0f, 0.0f);   // position 0 of the left factor
   for (int p = H2 + 1; p < 16; ++p) {            // positions beyond the last unit (none for H2 = 15)
@@ -67,7 +67,7 @@ GPF_DEV void sf2e_reverse_eval(const float* __restrict__ W, float* __restrict__ 
 #pragma unroll kSF2EUnroll
   for (int p = 1; p <= H2; ++p) {   // ROLLED over the rows of W2 (code size, see sf2e_forward_eval)
     float wr[16];
-    load_w16s<2>(W, R::W2B + 16 * p, wr);
+    load_w16s<GPF_SF2E_RBIT>(W, R::W2B + 16 * p, wr);
     du ta = d_scale(wr[1], cq[1]), tc = d_scale(wr[2], cq[2]), td = d_scale(wr[3], cq[3]);
 #pragma unroll
     for (int j = 1; j < 5; ++j) {
@@ -147,7 +147,7 @@ GPF_DEV void sf2e_reverse_eval(const float* __restrict__ W, float* __restrict__ 
 #pragma unroll
   for (int m = 0; m < 16; ++m) {
     if (m < H1) {
-      const float4 w = ldwr4<4>(W, R::W1P + 4 * m);
+      const float4 w = ldwr4<GPF_SF2E_W1BIT>(W, R::W1P + 4 * m);
       const du h = hp[m + 1], sp = d_sp(h);
       const du q = d_mul(sp, z[m + 1]);
       G0 = d_fma(w.x, q, G0);
