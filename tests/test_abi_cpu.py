@@ -123,3 +123,11 @@ def test_product_never_imports_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".h")):
                 src = open(os.path.join(dp, f)).read()
                 assert "gpflow_oracle" not in src and "ref_import" not in src, f
+
+
+def test_shipped_library_is_a_default_build_of_these_sources():
+    """The in-tree .so is what the GPU box runs: it must come from the committed sources with the default flags (an
+    experiment build made with GPFLOW_NVCC_EXTRA is marked in the hash file and rejected here and by smoke())."""
+    from gpflow_b200 import build as b
+    assert b.built_hash() is not None and "+extra" not in b.built_hash()
+    assert b.built_hash() == b.source_hash()
