@@ -125,7 +125,7 @@ def test_product_never_imports_oracle():
                 assert "gpflow_oracle" not in src and "ref_import" not in src, f
 
 
-def test_shipped_library_is_a_default_build_of_these_sources():
+def test_shipped_library_is_a_default_build_of_these_sources(lib):
     """The in-tree .so is what the GPU box runs: it must come from the committed sources with the default flags (an
     experiment build made with GPFLOW_NVCC_EXTRA is marked in the hash file and rejected here and by smoke())."""
     from gpflow_b200 import build as b
