@@ -12,8 +12,11 @@ LIB_PATH = os.environ.get("GPFLOW_B200_LIB") or os.path.join(_HERE, "lib", "libg
 
 GPFLOW_ABI_VERSION = 1
 ABI_VERSION = GPFLOW_ABI_VERSION
-ERR_UNSUPPORTED = 2    # include/gpflow_b200.h: GPFLOW_ERR_UNSUPPORTED
+ERR_BAD_DESC = 1       # include/gpflow_b200.h: GPFLOW_ERR_BAD_DESC
+ERR_UNSUPPORTED = 2    # GPFLOW_ERR_UNSUPPORTED
+ERR_NULL_POINTER = 3   # GPFLOW_ERR_NULL_POINTER
 ERR_STATIC_SCRATCH = 7  # GPFLOW_ERR_STATIC_SCRATCH
+ERR_COLLECTIVE = 8  # GPFLOW_ERR_COLLECTIVE
 STATIC_SCRATCH_BYTES = 32 << 20  # GPFLOW_STATIC_SCRATCH_BYTES
 GPFLOW_MAX_HIDDEN = 8
 F32, F64 = 0, 1
@@ -28,6 +31,7 @@ EXPORTS = [
     "gpflow_adam_step", "gpflow_bnaf_param_count", "gpflow_bnaf_forward", "gpflow_ffjord_param_count",
     "gpflow_ffjord_integrate", "gpflow_error_string",
     "gpflow_abi_version",
+    "gpflow_comm_unique_id", "gpflow_comm_create", "gpflow_allreduce_grads", "gpflow_comm_destroy",
 ]
 
 
@@ -112,6 +116,14 @@ def load():
     lib.gpflow_tc_slab_samples.argtypes = [D, ctypes.c_int64, ctypes.c_int]
     lib.gpflow_clock_probe.restype = ctypes.c_int
     lib.gpflow_clock_probe.argtypes = [P, P]
+    lib.gpflow_comm_unique_id.restype = ctypes.c_int
+    lib.gpflow_comm_unique_id.argtypes = [P]
+    lib.gpflow_comm_create.restype = ctypes.c_int
+    lib.gpflow_comm_create.argtypes = [P, ctypes.c_int, ctypes.c_int, ctypes.POINTER(ctypes.c_void_p)]
+    lib.gpflow_allreduce_grads.restype = ctypes.c_int
+    lib.gpflow_allreduce_grads.argtypes = [P, ctypes.c_int64, ctypes.c_int, P, P]
+    lib.gpflow_comm_destroy.restype = ctypes.c_int
+    lib.gpflow_comm_destroy.argtypes = [P]
     BD = ctypes.POINTER(GpFlowBnafDesc)
     lib.gpflow_bnaf_param_count.restype = ctypes.c_int
     lib.gpflow_bnaf_param_count.argtypes = [BD, ctypes.POINTER(ctypes.c_int64)]

@@ -80,7 +80,7 @@ def build(force=False, verbose=False):
         list(ex.map(compile_one, zip(srcs, objs)))
     # -cudart shared: the runtime stays a separate libcudart.so (torch ships one); a static cudart would put the
     # names of CUDA runtime entry points this library never calls into the shipped binary
-    r = subprocess.run([nvcc, "-shared", "-cudart", "shared", "-o", LIB] + objs + ["-gencode", "arch=compute_100a,code=sm_100a"],
+    r = subprocess.run([nvcc, "-shared", "-cudart", "shared", "-o", LIB] + objs + ["-gencode", "arch=compute_100a,code=sm_100a", "-ldl"],
                        capture_output=True, text=True)
     if r.returncode != 0:
         raise RuntimeError("link failed:\n" + r.stderr[-4000:])

@@ -574,6 +574,8 @@ const char* gpflow_error_string(int status) {
     case GPFLOW_ERR_STATIC_SCRATCH:
       return "gpflow_velocity_static: batch / shape needs more than GPFLOW_STATIC_SCRATCH_BYTES of scratch "
              "(use gpflow_velocity with a caller-provided workspace)";
+    case GPFLOW_ERR_COLLECTIVE:
+      return "multi-GPU hook: NCCL could not be loaded at run time (libnccl.so.2 / $GPFLOW_NCCL_LIB) or returned an error";
     default: return "unknown status";
   }
 }

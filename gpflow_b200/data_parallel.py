@@ -52,3 +52,61 @@ def broadcast_probes(zw: Optional[torch.Tensor], src: int = 0, group=None) -> Op
 def split_buffer(buf: torch.Tensor, n_params: int):
     """(grads [P], ot, reg, lagr) views of the fused buffer."""
     return buf[:n_params], buf[n_params], buf[n_params + 1], buf[n_params + 2]
+
+
+class NativeAllReduce:
+    """The C ABI's own all-reduce (`gpflow_allreduce_grads`, include/gpflow_b200.h "Multi-GPU hook"): an NCCL communicator
+    created by the library itself (NCCL bound at run time), bootstrapped over an existing torch.distributed group -- rank 0's
+    128-byte id is broadcast through it -- or, for a single process, with n_ranks = 1.  `allreduce_(buf)` enqueues the
+    in-place SUM on the current CUDA stream, like `allreduce_train_buffer`.  A host without torch.distributed calls the four
+    C entry points directly and moves the id by its own means."""
+
+    def __init__(self, device, group=None):
+        import ctypes
+        from . import _lib
+        self._lib = _lib.load()
+        self.device = torch.device(device)
+        world = world_size(group)
+        rank = dist.get_rank(group) if world > 1 else 0
+        ident = torch.zeros(128, dtype=torch.uint8)
+        if rank == 0:
+            _check(self._lib.gpflow_comm_unique_id(ctypes.c_void_p(ident.data_ptr())), "gpflow_comm_unique_id")
+        if world > 1:
+            backend = dist.get_backend(group)
+            box = ident.to(self.device) if backend == "nccl" else ident
+            dist.broadcast(box, src=0, group=group)
+            ident = box.cpu()
+        comm = ctypes.c_void_p(0)
+        with torch.cuda.device(self.device):
+            _check(self._lib.gpflow_comm_create(ctypes.c_void_p(ident.data_ptr()), world, rank, ctypes.byref(comm)),
+                   "gpflow_comm_create")
+        self._comm, self.world, self.rank = comm, world, rank
+
+    def allreduce_(self, buf: torch.Tensor) -> torch.Tensor:
+        import ctypes
+        from . import _lib
+        if not buf.is_cuda or not buf.is_contiguous() or buf.dtype not in (torch.float32, torch.float64):
+            raise ValueError("NativeAllReduce: contiguous fp32 / fp64 CUDA tensor expected")
+        with torch.cuda.device(buf.device):
+            stream = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+            _check(self._lib.gpflow_allreduce_grads(ctypes.c_void_p(buf.data_ptr()), buf.numel(),
+                                                    _lib.F64 if buf.dtype == torch.float64 else _lib.F32, self._comm, stream),
+                   "gpflow_allreduce_grads")
+        return buf
+
+    def close(self):
+        if self._comm is not None and self._comm.value:
+            self._lib.gpflow_comm_destroy(self._comm)
+        self._comm = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:  # noqa: BLE001 -- interpreter shutdown
+            pass
+
+
+def _check(rc: int, what: str):
+    if rc != 0:
+        from . import _lib
+        raise RuntimeError("%s failed: %s" % (what, _lib.load().gpflow_error_string(rc).decode()))

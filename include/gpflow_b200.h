@@ -40,8 +40,9 @@ typedef enum GpFlowStatus {
   GPFLOW_ERR_WORKSPACE = 4,      /* workspace smaller than gpflow_query_workspace() reports  */
   GPFLOW_ERR_MISALIGNED = 5,     /* a buffer is not aligned to its element size              */
   GPFLOW_ERR_CUDA = 6,           /* cudaGetLastError() after a launch was not cudaSuccess    */
-  GPFLOW_ERR_STATIC_SCRATCH = 7  /* gpflow_velocity_static(): the call needs more scratch than
+  GPFLOW_ERR_STATIC_SCRATCH = 7, /* gpflow_velocity_static(): the call needs more scratch than
                                     GPFLOW_STATIC_SCRATCH_BYTES; use gpflow_velocity() with a workspace */
+  GPFLOW_ERR_COLLECTIVE = 8      /* gpflow_comm_* / gpflow_allreduce_grads: NCCL not found at run time, or it returned an error */
 } GpFlowStatus;
 
 typedef enum GpFlowDType { GPFLOW_F32 = 0, GPFLOW_F64 = 1 } GpFlowDType;
@@ -179,6 +180,26 @@ int gpflow_potentials(int dtype, int n_linear, const int32_t* widths, int64_t B,
 #define GPFLOW_STATIC_SCRATCH_BYTES (32u << 20)
 int gpflow_velocity_static(const GpFlowDesc* desc, int64_t B, const void* params, const void* x, double t, void* v_out,
                            void* cuda_stream);
+
+/*
+ * Multi-GPU hook (SURVEY.md 8b "Multi-GPU hook", 8e): the path shards by samples -- every rank runs gpflow_train_step on its
+ * contiguous batch shard with desc->loss_scale = 1 / B_global, which leaves SUMS already scaled by 1 / B_global in the fused
+ * buffer [grads (P) | ot, reg, lagr]; ONE in-place SUM all-reduce of those P + 3 elements yields the global-batch loss and
+ * gradient on every rank (gpflow_b200/data_parallel.py does the same through torch.distributed).  The reference is
+ * single-device (training.py:124-136), so there is no reference interface to replace; these four entry points let a host
+ * without torch.distributed do the exchange.  NCCL is bound at run time (dlopen "libnccl.so.2", or $GPFLOW_NCCL_LIB; an
+ * already loaded copy -- PyTorch's -- is preferred): the library itself links against the CUDA runtime only.
+ *   gpflow_comm_unique_id   rank 0: fills 128 bytes that the host distributes to the other ranks (any transport);
+ *   gpflow_comm_create      every rank, on its own device (cudaSetDevice first): collective; returns an opaque communicator;
+ *   gpflow_allreduce_grads  in-place SUM over the ranks of buf[0..count) (dtype GPFLOW_F32 / GPFLOW_F64), enqueued on
+ *                           `cuda_stream` behind the train step that wrote buf; no host synchronisation;
+ *   gpflow_comm_destroy     releases the communicator.
+ * GPFLOW_ERR_COLLECTIVE when NCCL cannot be loaded or reports an error.
+ */
+int gpflow_comm_unique_id(void* id_out_128_bytes);
+int gpflow_comm_create(const void* id_128_bytes, int n_ranks, int rank, void** comm_out);
+int gpflow_allreduce_grads(void* buf, int64_t count, int dtype, void* comm, void* cuda_stream);
+int gpflow_comm_destroy(void* comm);
 
 /* Name of the kernel family an op on this descriptor dispatches to ("small<f32,2,1,15,15>", "generic<f64>", ...). */
 int gpflow_kernel_variant(const GpFlowDesc* desc, int op, char* buf, size_t buf_len);
