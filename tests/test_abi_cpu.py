@@ -131,3 +131,23 @@ def test_shipped_library_is_a_default_build_of_these_sources(lib):
     from gpflow_b200 import build as b
     assert b.built_hash() is not None and "+extra" not in b.built_hash()
     assert b.built_hash() == b.source_hash()
+
+
+def test_draw_probes_keeps_the_reference_rng_stream():
+    """res_net.py:330-333 draws z then w with torch.randn(1, d) once per step on the default generator; the mirror must
+    consume the generator identically (the C2 training replay depends on it) whatever staging it uses for the upload."""
+    import gpflow_b200 as G
+    flow = G.get_gp_flow(3, {"nb_neurons": [5, 5], "nb_div_blocks": 2}, 7,
+                         euler_dict={"use_euler": True, "case": "penalization", "coef_penalization": 5e-4})
+    torch.manual_seed(11)
+    got = flow.draw_probes(7, torch.zeros(1, dtype=torch.float64))
+    after = torch.randn(1)
+    torch.manual_seed(11)
+    rows = []
+    for _ in range(7):
+        z = torch.randn(1, 3)
+        w = torch.randn(1, 3)
+        rows.append(torch.stack([z[0], w[0]]))
+    want = torch.stack(rows).double()
+    assert got.dtype == torch.float64 and torch.equal(got, want)
+    assert torch.equal(after, torch.randn(1))          # and leaves the generator in the same state
