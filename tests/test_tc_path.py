@@ -22,6 +22,8 @@ SHAPES = [
     (3, 1, (33, 200), 129, 3, 0.06),         # nb = 1, narrow -> wide
     (12, 5, (128, 64), 257, 3, 0.03),        # wide -> narrow (Ub_1 does not alias T_2)
     (18, 17, (48,), 140, 3, 0.02),           # 64-wide last layer with nb, d > 16: several row tiles per group in tc_w3_small_kernel
+    (4, 2, (40, 40, 40, 40), 300, 3, 0.05),   # four 64-wide layers: the value-row chain kernel at its largest shared-memory size
+    (16, 5, (48, 48), 200, 3, 0.03),          # d = 16: the upper bound of the d-bounded narrow-net kernels (chain, first-layer gradient)
 ]
 
 
