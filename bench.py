@@ -462,7 +462,7 @@ def measure_workload(args, name, wl, euler, rank, world, local_rank, dev, steps,
     kev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
     probe = torch.zeros(steps, 2, dtype=torch.int64, device=dev)
     stream_ptr = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
-    tc_l0 = int(lib.gpflow_tc_launches_total())
+    tc_l0 = ops.tc_launches_total()      # eager launches + launches inside replayed CUDA graphs
     ev0.record()
     for i in range(steps):
         x_data, x_map = bufs[i % n_buf]
@@ -475,7 +475,7 @@ def measure_workload(args, name, wl, euler, rank, world, local_rank, dev, steps,
         lib.gpflow_clock_probe(ctypes.c_void_p(probe[i].data_ptr()), stream_ptr)   # ~20 us, SM clock right after the step
     ev1.record()
     torch.cuda.synchronize()
-    tc_launches = int(lib.gpflow_tc_launches_total()) - tc_l0
+    tc_launches = ops.tc_launches_total() - tc_l0
     if world > 1:
         dist.barrier()
     ms_total = ev0.elapsed_time(ev1)

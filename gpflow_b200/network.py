@@ -16,7 +16,11 @@ import numpy as np
 import torch
 
 from . import _lib, data_parallel, ops
+import weakref
+
 from .res_net import Compose
+
+_TC_GRAPHS = weakref.WeakKeyDictionary()   # GPFlowNetwork -> captured train steps of the tensor-core path
 
 
 class GPFlowNetwork(torch.nn.Module):
@@ -105,8 +109,12 @@ class GPFlowNetwork(torch.nn.Module):
                     self._buf.device != x.device:
                 self._buf = torch.empty(P + _lib.NUM_SCALARS, dtype=x.dtype, device=x.device)
             flat, buf = flow.flat_parameters(), self._buf
-        res = ops.fused_train_step(cfg, flat, x, x_map, euler_coef=euler, zw=zw, lagrangian=with_lagrangian,
-                                   loss_scale=1.0 / gb, out=buf, force_generic=flow.force_generic)
+        res = None
+        if in_place and euler is None and not with_lagrangian and not flow.force_generic:
+            res = self._graphed_train_step(cfg, flat, x, x_map, 1.0 / gb, buf)
+        if res is None:
+            res = ops.fused_train_step(cfg, flat, x, x_map, euler_coef=euler, zw=zw, lagrangian=with_lagrangian,
+                                       loss_scale=1.0 / gb, out=buf, force_generic=flow.force_generic)
         if world > 1:
             data_parallel.allreduce_train_buffer(res["buf"], pg)
         off = 0
@@ -125,6 +133,47 @@ class GPFlowNetwork(torch.nn.Module):
         if with_lagrangian:
             flow.lagrangian = sc[_lib.SCALAR_LAGR]
         return sc[_lib.SCALAR_OT], sc[_lib.SCALAR_REG]
+
+    def _graphed_train_step(self, cfg, flat, x, x_map, loss_scale, buf):
+        """Narrow nets on the tensor-core path enqueue ~2 200 short launches per step (C3 at 2^14 samples: 51.8 ms, of which
+        ~4 ms are gaps between launches; at B = 3072 21.1 ms against 16.4 ms).  With stable parameter / gradient buffers
+        (the fused optimiser's) the call is captured ONCE per (shape, batch, buffers) into a CUDA graph and replayed; the
+        step's inputs are copied into the graph's static input buffers.  Returns None when the step does not qualify
+        (GPFLOW_TC_GRAPH=0, other kernel families, wide nets whose launches are long anyway) or the capture failed."""
+        import os
+        if os.environ.get("GPFLOW_TC_GRAPH", "1") == "0" or x.dtype != torch.float32 or max(cfg.hidden) > 64:
+            return None
+        if x.shape[0] < 2400 or "gpflow_tc" not in ops.kernel_variant(cfg, x.dtype):
+            return None
+        cache = _TC_GRAPHS.setdefault(self, {})   # outside the module's __dict__: deepcopy / pickle stay clean
+        key = (cfg, x.shape[0], x.device, flat.data_ptr(), buf.data_ptr(), float(loss_scale))
+        ent = cache.get(key)
+        if ent is None:
+            try:
+                xd, xm = torch.empty_like(x), torch.empty_like(x_map)
+                xd.copy_(x)
+                xm.copy_(x_map)
+                ops.fused_train_step(cfg, flat, xd, xm, loss_scale=loss_scale, out=buf)      # warm-up: kernel attributes, allocator
+                graph = torch.cuda.CUDAGraph()
+                n0 = int(_lib.load().gpflow_tc_launches_total())
+                with torch.cuda.graph(graph):
+                    res = ops.fused_train_step(cfg, flat, xd, xm, loss_scale=loss_scale, out=buf)
+                ent = (graph, xd, xm, res, int(_lib.load().gpflow_tc_launches_total()) - n0)
+            except Exception as e:  # noqa: BLE001 -- e.g. a capture already in progress: keep the eager CUDA path
+                import warnings
+                warnings.warn("gpflow_b200: CUDA-graph capture of the train step failed (%r); using eager launches" % (e,))
+                ent = False
+            if len(cache) >= 8:
+                cache.pop(next(iter(cache)))
+            cache[key] = ent
+        if ent is False:
+            return None
+        graph, xd, xm, res, n_launch = ent
+        xd.copy_(x)
+        xm.copy_(x_map)
+        graph.replay()
+        ops.REPLAYED_TC_LAUNCHES[0] += n_launch
+        return res
 
     def _composed_training_step(self, x, x_map, gb, world, pg):
         """nb_blocks != 1: the blocks are chained through autograd (each block's forward / backward is one fused CUDA op,

@@ -104,6 +104,16 @@ def make_desc(cfg: FlowConfig, dtype, *, wrap=False, reverse=False, training=Fal
     return d
 
 
+# kernels enqueued through CUDA-graph replays of the tensor-core path (GPFlowNetwork._graphed_train_step): the library's own
+# counter (gpflow_tc_launches_total) only sees host-side launches, i.e. the capture
+REPLAYED_TC_LAUNCHES = [0]
+
+
+def tc_launches_total() -> int:
+    """Kernels the tensor-core path has enqueued in this process: eager launches + launches inside replayed graphs."""
+    return int(_lib.load().gpflow_tc_launches_total()) + REPLAYED_TC_LAUNCHES[0]
+
+
 def kernel_variant(cfg: FlowConfig, dtype=torch.float32, op=_lib.OP_TRAIN_STEP, **kw) -> str:
     desc = make_desc(cfg, dtype, **kw)
     buf = ctypes.create_string_buffer(256)

@@ -209,3 +209,65 @@ def test_bench_rows_at_full_size_2p14_properties(d, nb, hidden, w_std, n_sub):
     assert rel(full["y"][idx].cpu(), r64["y"]) < 1e-5
     ot = ((x_data.double() - full["y"].double()) ** 2).sum(1).mean()
     assert abs(float(full["scalars"][0]) - float(ot)) < 2e-6 * float(ot)
+
+
+def test_tc_train_step_captured_in_a_cuda_graph():
+    """The tensor-core path is ~2 200 launches per step: a caller may capture the call once (after a warm-up call that sets
+    the kernel attributes) and replay it.  Replays are bit-identical to the eager call and follow new parameter values."""
+    import gpflow_b200 as G
+    d, nb, hidden, B, N, std = 10, 9, (50, 50, 50), 3072, 3, 0.03
+    spec, params, x_data, x_map = _inputs(d, nb, hidden, B, N, std)
+    cfg = G.FlowConfig(d=d, nb=nb, hidden=tuple(hidden), n_steps=N)
+    flat = O.flatten_params(params).float().cuda()
+    xd, xm = x_data.float().cuda(), x_map.float().cuda()
+    out = torch.zeros(cfg.n_params + 3, device="cuda")
+    assert "gpflow_tc" in G.kernel_variant(cfg)
+    want = G.fused_train_step(cfg, flat, xd, xm, out=out)["buf"].clone()          # warm-up outside the capture
+    torch.cuda.synchronize()
+    graph = torch.cuda.CUDAGraph()
+    out.zero_()
+    with torch.cuda.graph(graph):
+        G.fused_train_step(cfg, flat, xd, xm, out=out)
+    out.zero_()
+    graph.replay()
+    torch.cuda.synchronize()
+    assert torch.equal(out, want)
+    flat.mul_(1.1)
+    want2 = G.fused_train_step(cfg, flat, xd, xm)["buf"].clone()
+    graph.replay()
+    torch.cuda.synchronize()
+    assert torch.equal(out, want2)
+
+
+def test_module_path_replays_a_captured_graph_for_narrow_nets(monkeypatch):
+    """GPFlowNetwork.fused_training_step with the fused optimiser's stable buffers: the tensor-core train step of a narrow
+    net is captured once and replayed (network.py: _graphed_train_step).  Same losses and parameters, bit for bit, as with
+    eager launches (GPFLOW_TC_GRAPH=0); the replays are counted as launches of the path."""
+    import gpflow_b200 as G
+    from gpflow_b200 import ops
+
+    def run(graph_on):
+        monkeypatch.setenv("GPFLOW_TC_GRAPH", "1" if graph_on else "0")
+        torch.manual_seed(0)
+        flow = G.get_gp_flow(10, {"nb_neurons": [50, 50, 50], "nb_div_blocks": 9}, 3).cuda()
+        with torch.no_grad():
+            for p in flow.parameters():
+                p.normal_(0.0, 0.03)
+        net = G.GPFlowNetwork(flow, map_module=None)
+        opt = net.configure_fused_optimizer(lr=2e-3, weight_decay=1e-4)
+        g = torch.Generator(device="cuda").manual_seed(3)
+        losses = []
+        n0 = ops.tc_launches_total()
+        for i in range(4):
+            x_map = torch.randn(3072, 10, generator=g, device="cuda")
+            x_data = 0.9 * x_map.roll(1, 1) + 0.1
+            loss, _ = net.fused_training_step(x_data, x_map)
+            opt.step()
+            losses.append(loss.clone())
+        torch.cuda.synchronize()
+        return torch.stack(losses), opt.flat.clone(), ops.tc_launches_total() - n0
+
+    la, pa, na = run(True)
+    lb, pb, nb_ = run(False)
+    assert torch.equal(la, lb) and torch.equal(pa, pb)
+    assert na >= nb_ > 0            # warm-up + capture + 4 replays against 4 eager steps
