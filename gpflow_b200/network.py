@@ -156,7 +156,8 @@ class GPFlowNetwork(torch.nn.Module):
                 ops.fused_train_step(cfg, flat, xd, xm, loss_scale=loss_scale, out=buf)      # warm-up: kernel attributes, allocator
                 graph = torch.cuda.CUDAGraph()
                 n0 = int(_lib.load().gpflow_tc_launches_total())
-                with torch.cuda.graph(graph):
+                # thread_local: other threads (an NCCL watchdog, a data loader) are not policed by this capture
+                with torch.cuda.graph(graph, capture_error_mode="thread_local"):
                     res = ops.fused_train_step(cfg, flat, xd, xm, loss_scale=loss_scale, out=buf)
                 ent = (graph, xd, xm, res, int(_lib.load().gpflow_tc_launches_total()) - n0)
             except Exception as e:  # noqa: BLE001 -- e.g. a capture already in progress: keep the eager CUDA path
