@@ -145,6 +145,8 @@ class GPFlowNetwork(torch.nn.Module):
             return None
         if x.shape[0] < 2400 or "gpflow_tc" not in ops.kernel_variant(cfg, x.dtype):
             return None
+        if torch.cuda.is_current_stream_capturing():      # the caller is capturing the whole step: plain launches go into ITS graph
+            return None
         cache = _TC_GRAPHS.setdefault(self, {})   # outside the module's __dict__: deepcopy / pickle stay clean
         key = (cfg, x.shape[0], x.device, flat.data_ptr(), buf.data_ptr(), float(loss_scale))
         ent = cache.get(key)
